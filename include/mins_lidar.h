@@ -1,0 +1,203 @@
+/*
+ * mins_lidar.h — C ABI of the B200-native LiDAR measurement-update path for rpng/MINS.
+ *
+ * One opaque handle = one LiDAR id = one local map (the reference keeps one `iKDDATA` per id,
+ * mins/src/update/lidar/UpdaterLidar.cpp:43-47). Every entry point names the reference interface it replaces.
+ * Plain pointers and sizes only; the caller owns all host buffers, the library owns all device memory
+ * (pre-sized at ml_create, nothing is allocated on the per-scan path).
+ *
+ * Status convention (reference error behaviour):
+ *    0  ok
+ *   >0  soft: "cannot use this scan" (the caller returns false and retries/drops it, as UpdaterLidar.cpp:398-399)
+ *   <0  fatal: CUDA error / capacity exceeded / bad argument (the C++ shim prints and exits like UpdaterLidar.cpp:210)
+ * No C++ exception crosses this boundary. ml_last_error() gives the text of the last non-zero status.
+ *
+ * Threading: one host thread per handle, one CUDA stream per handle; different handles are independent.
+ * There is NO CPU fallback: if no CUDA device is usable ml_create fails with ML_ERR_CUDA.
+ *
+ * Point layout: float[4] = {x, y, z, intensity}; intensity carries "seconds since the first scan (FT)" exactly as
+ * LiDARData's constructor stores it (mins/src/update/lidar/LidarTypes.cpp:47).
+ */
+#ifndef MINS_LIDAR_H
+#define MINS_LIDAR_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ML_MAX_HX 64     /* max columns of the measurement Jacobian (reference: 48, 54 or 55) */
+#define ML_MAX_BLOCKS 8  /* max Jacobian blocks per interpolated pose (intr_order + 1 poses + time offset) */
+#define ML_MAX_K 10      /* max map_ngbr_num */
+
+#define ML_OK 0
+#define ML_SOFT_NO_ROWS 1   /* no point passed the gates: UpdaterLidar::update returns false (UpdaterLidar.cpp:398) */
+#define ML_SOFT_NO_MAP 2    /* map not initialised (tree->initialized() false, UpdaterLidar.cpp:91) */
+#define ML_ERR_CUDA (-1)
+#define ML_ERR_CAPACITY (-2)
+#define ML_ERR_ARG (-3)
+
+typedef struct ml_handle ml_handle;
+
+typedef struct ml_config {
+  int device;          /* CUDA device ordinal */
+  int max_scan_points; /* capacity for one raw scan */
+  int max_map_points;  /* capacity of the local map */
+  int max_grid_cells;  /* cap on cells of the dense kNN grid; 0 = default (1<<24) */
+  float grid_cell;     /* kNN grid cell edge [m]; 0 = default 0.5 */
+} ml_config;
+
+/* One block of d(interpolated pose)/d(state variable): the reference's `dTdx[j]` with `map_hx.at(order[j])`
+ * (mins/src/state/State.cpp:745-816, UpdaterLidar.cpp:343-347). D is 6 x width, row-major with row stride 6. */
+typedef struct ml_jac_block {
+  int col;   /* first column in H (map_hx) */
+  int width; /* 6 for a pose, 1 for the time offset */
+  double D[36];
+} ml_jac_block;
+
+/* Every per-scan constant UpdaterLidar::update computes before its point loop (UpdaterLidar.cpp:171-257).
+ * 3x3 matrices are row-major. Names follow the reference's local variables. */
+typedef struct ml_scan_consts {
+  double RLtoM_est[9], pLinM_est[3]; /* :246-247 */
+  double RLtoM_fej[9], pLinM_fej[3]; /* :248-249 */
+  double RGtoM_fej[9];               /* :243 */
+  double RItoG_fej[9];               /* :236 */
+  double RLtoI_fej[9], RItoL_fej[9]; /* :227-228 */
+  double RGtoA_fej[9];               /* :197 */
+  double RLtoG_fej[9];               /* :238 */
+  double pIinL_fej[3];               /* :229 */
+  double pLinI_fej[3];               /* :230 */
+  double pIinG_fej[3], pAinG_fej[3]; /* :190,:197 */
+  int nI, nA;                        /* dTdxI.size(), dTdxA.size() */
+  ml_jac_block dTdxI[ML_MAX_BLOCKS]; /* :190 */
+  ml_jac_block dTdxA[ML_MAX_BLOCKS]; /* :197 */
+  int calib_col;                     /* map_hx.at(calibration) if do_calib_ext else -1 (:181,:349) */
+  int at_clone_m, at_clone_a;        /* :251-252 */
+  double ie_o, ie_p;                 /* :253-254 */
+  int total_hx;                      /* :172 */
+  /* OptionsLidar (mins/src/options/OptionsLidar.h:38-99) */
+  double raw_noise, map_noise;
+  int map_ngbr_num;
+  double map_ngbr_max_d; /* compared against the SQUARED distance of the k-th neighbour (LidarHelper.cpp:284) */
+  double plane_max_p2pd;
+  double plane_max_condi;
+  double chi2_thr; /* chi2_mult * quantile(chi_squared(3), 0.95) = chi2_mult * 7.814727903251179 */
+} ml_scan_consts;
+
+/* What UpdaterStatistics would have accumulated (mins/src/update/UpdaterStatistics.cpp:47-83), as order-independent
+ * moments, plus why points were dropped. */
+typedef struct ml_counters {
+  int n_points;     /* points in the (down-sampled) scan */
+  int n_knn_fail;   /* LidarHelper::get_neighbors false (LidarHelper.cpp:280-285) */
+  int n_plane_fail; /* LidarHelper::compute_plane false (LidarHelper.cpp:310,322) */
+  int n_badmatch;   /* UpdaterLidar.cpp:296 */
+  int n_chi_rej;    /* Chi2Check false (incl. NaN) */
+  int n_acc;        /* accepted points (3 rows each in the reference's H_big) */
+  double sum_chi, sum_chi2; /* over all points that reached the chi2 test */
+  double sum_res, sum_res2; /* over the 3 projected residuals of those points (sum of r', sum of r'^2) */
+} ml_counters;
+
+/* per-point debug/parity export (ml_point_rows) */
+typedef struct ml_point_row {
+  int status;     /* 0 accepted, 1 knn fail, 2 plane fail, 3 bad match, 4 chi2 reject */
+  int pad;
+  double plane[4]; /* [abc, d] un-normalised (LidarHelper.cpp:315-316) */
+  double res;      /* whitened scan-point residual, row 5 (UpdaterLidar.cpp:313,358) */
+  double chi2;     /* UpdaterStatistics.cpp:110 */
+  double w;        /* ||v||^2 : weight of h h^T in H'^T H' */
+  double vr;       /* v^T r' : H'^T r' = h * vr */
+  double raw_n;    /* UpdaterLidar.cpp:353 */
+} ml_point_row;
+
+/* ---- lifetime -------------------------------------------------------------------------------------------- */
+/* replaces: iKDDATA::iKDDATA / make_shared<KD_TREE> (LidarTypes.cpp:79-83) */
+int ml_create(const ml_config *cfg, ml_handle **out);
+void ml_destroy(ml_handle *h);
+const char *ml_last_error(const ml_handle *h);
+/* text for create-time failures (no handle yet) */
+const char *ml_global_error(void);
+
+/* ---- map: replaces KD_TREE<PointXYZI> as used through iKDDATA::tree ------------------------------------- */
+/* KD_TREE::reset (ikd_Tree.h:262) */
+int ml_map_reset(ml_handle *h);
+/* KD_TREE::initialized (ikd_Tree.h:263): 1/0 */
+int ml_map_initialized(const ml_handle *h);
+/* KD_TREE::Build(PointVector) (ikd_Tree.cpp:344-356) <- LidarHelper::init_map_local (LidarHelper.cpp:103-113) */
+int ml_map_build(ml_handle *h, const float *xyzi, int n);
+/* init_map_local on the current (down-sampled) scan cloud, device-resident (UpdaterLidar.cpp:91-95) */
+int ml_map_build_from_scan(ml_handle *h);
+/* KD_TREE::Add_Points(PointVector&, bool) with set_downsample_param(ds) (ikd_Tree.cpp:401-479).
+ * n_kept (may be NULL) = live map size afterwards. */
+int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds, int *n_live);
+/* LidarHelper::register_scan (LidarHelper.cpp:196-207): transform the ORIGINAL cloud of the current scan by
+ * T_LtoM (set by ml_scan_transform) and Add_Points it. */
+int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live);
+/* LidarHelper::propagate_map_to_newest_clone (LidarHelper.cpp:209-266) minus the pose look-ups:
+ * [VoxelGrid centroid down-sample at ds if do_downsample] -> drop points with intensity + FT + decay_time < now
+ * or ||p|| > decay_dist -> p <- T(4x4 fp64, row-major) p -> rebuild. `now_minus_FT` = state->time - FT. */
+int ml_map_reanchor(ml_handle *h, const double T_old_to_new[16], double now_minus_FT, double decay_time,
+                    double decay_dist, int do_downsample, float ds, int *n_live);
+/* KD_TREE::flatten(Root_Node, Storage, NOT_RECORD) (ikd_Tree.cpp:1359-1386): copies min(n, cap) points, *n = live size */
+int ml_map_flatten(ml_handle *h, float *xyzi_out, int cap, int *n);
+/* KD_TREE::validnum */
+int ml_map_size(ml_handle *h, int *n);
+
+/* ---- scan: replaces LiDARData + the LidarHelper pre-processing ------------------------------------------ */
+/* LiDARData::LiDARData (LidarTypes.cpp:26-56): range filter (fp32 norm in [rmin, rmax]), intensity = t_rel,
+ * fills `pointcloud` and `pointcloud_original`. xyz: n points, `stride` floats apart (3 = packed, 4 = PointXYZ).
+ * n_kept may be NULL (then the call does not synchronise). */
+int ml_scan_upload(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, int *n_kept);
+/* LidarHelper::remove_motion_blur loop body (LidarHelper.cpp:71-85) with per-point transforms interpolated on the
+ * device from `n_knots` LiDAR poses T_LitoL (row-major 3x4 fp32 each) sampled uniformly over the sweep:
+ * point i uses time fraction (total - i)/total. The reference's inverted guard (:54-58) is NOT reproduced. */
+int ml_scan_deskew(ml_handle *h, const float *T_LitoL_knots, int n_knots, int total_points);
+/* LidarHelper::downsample (LidarHelper.cpp:89-94): pcl::VoxelGrid<PointXYZI> centroid filter, cubic leaf */
+int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds);
+/* LidarHelper::transform_to_map tail (LidarHelper.cpp:149-151,192): pointcloud_in_map = T_LtoM * pointcloud (fp32).
+ * T row-major 4x4. The transform is remembered for ml_map_add_scan. */
+int ml_scan_transform(ml_handle *h, const float T_LtoM[16]);
+/* which: 0 = pointcloud, 1 = pointcloud_in_map, 2 = pointcloud_original */
+int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n);
+/* test hook: replace `pointcloud` (and `pointcloud_original`) verbatim, no filtering */
+int ml_scan_set(ml_handle *h, const float *xyzi, int n);
+
+/* ---- update: replaces the point loop + stacking + compression of UpdaterLidar::update ------------------- */
+/* LidarHelper::get_neighbors / KD_TREE::Nearest_Search (LidarHelper.cpp:268-289, ikd_Tree.cpp:358-389) for every
+ * point of pointcloud_in_map. Exact k-NN on fp32 squared distance ((dx*dx + dy*dy) + dz*dz, no FMA), total order
+ * (d2, map index) ascending. idx: n*k int32 (index into ml_map_flatten order; -1 where fewer than k were found
+ * within sqrt(max_d2)), d2: n*k float. ok[i] = 1 iff get_neighbors would return true. Any output may be NULL. */
+int ml_knn(ml_handle *h, int k, float max_d2, int32_t *idx, float *d2, uint8_t *ok, int *n);
+/* UpdaterLidar.cpp:269-397 for the whole scan: match -> plane -> residual/Jacobian -> whitening -> nullspace
+ * projection -> chi2 gate -> reduction. Returns the information form of the stacked, projected system:
+ * HtH = H_big^T H_big (total_hx x total_hx, row-major), Htr = H_big^T res_big (total_hx), R = I.
+ * P: marginal covariance of H_order (total_hx x total_hx, row-major; UpdaterLidar.cpp:257).
+ * Returns ML_SOFT_NO_ROWS when no point was accepted. */
+int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt);
+/* One call for the timed path: ml_scan_upload + ml_scan_transform + ml_linsys with a single synchronisation. */
+int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax,
+                   float leaf /* <=0: no down-sampling */, const float T_LtoM[16], const ml_scan_consts *c,
+                   const double *P, double *HtH, double *Htr, ml_counters *cnt);
+/* parity export of the last ml_linsys: per-point status/plane/residual/chi2 and the whitened Jacobian row h
+ * (n x total_hx, row-major; may be NULL). */
+int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int *n);
+
+/* host-side tail (plain C++, no device work): turn (HtH, Htr) into the compressed (R_c, r_c) that
+ * StateHelper::measurement_compress_inplace would hand to EKFUpdate (StateHelper.cpp:631-643): R_c^T R_c = HtH,
+ * R_c^T r_c = Htr, rows with zero pivot dropped. Rc: total_hx x total_hx row-major, rc: total_hx. Returns rank. */
+int ml_info_to_sqrt(const double *HtH, const double *Htr, int total_hx, double *Rc, double *rc);
+
+/* device-time (ms, CUDA events on the handle's stream) of the stages of the last ml_linsys / ml_scan_update:
+ * [0] upload+filter, [1] downsample, [2] transform, [3] query binning, [4] knn, [5] rows, [6] reduce, [7] total */
+int ml_last_timing(ml_handle *h, float ms[8]);
+/* switch the per-stage CUDA-event timers on/off (default on) */
+int ml_set_timing(ml_handle *h, int on);
+/* sizeof of {ml_scan_consts, ml_point_row, ml_counters, ml_config} as compiled, for FFI layout checks */
+void ml_abi_sizes(int out[4]);
+/* number of kernel launches issued by this handle so far */
+long long ml_launch_count(const ml_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,947 @@
+// C ABI of the B200-native MINS LiDAR update path (see include/mins_lidar.h). Host-side orchestration only:
+// every numeric step is a hand-written sm_100a kernel in map.cuh / scan.cuh / update.cuh / rows.cuh.
+// There is no CPU fallback: without a usable CUDA device ml_create fails.
+#include "common.cuh"
+#include "map.cuh"
+#include "prims.cuh"
+#include "rows.cuh"
+#include "scan.cuh"
+#include "update.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace ml;
+
+static std::string g_global_error;
+
+struct ml_handle {
+  ml_config cfg;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  long long launches = 0;
+  int cap_scan = 0, cap_map = 0, cap_cells = 0, cap_all = 0;
+  double grid_cell = 0.5;
+  // map
+  float4 *map_pts[2] = {nullptr, nullptr};
+  int cur = 0;
+  int *d_map_n = nullptr;
+  int map_n = 0;
+  bool map_init = false;
+  GridDesc *d_grid = nullptr;
+  GridDesc grid_host;
+  uint32_t *d_bbox = nullptr;
+  uint32_t *cell_cnt = nullptr, *cell_start = nullptr;
+  float4 *cell_pts = nullptr;
+  uint32_t *pt_cell = nullptr, *pt_rank = nullptr;
+  uint32_t *tile_sums = nullptr;
+  VoxSlot *vox_tab = nullptr;
+  int vox_slots = 0;
+  uint32_t *add_slot = nullptr, *contender = nullptr, *keep = nullptr, *pos = nullptr;
+  int *d_ints = nullptr; // scratch ints: [0]=n_add [1]=total [2]=overflow [3]=n_tmp [4]=passthrough
+  float4 *add_pts = nullptr;
+  // scan
+  float *d_raw = nullptr;
+  float *h_raw = nullptr; // pinned staging
+  float4 *scan_pts = nullptr, *scan_orig = nullptr, *scan_map = nullptr, *scan_tmp = nullptr;
+  ScanState *d_st = nullptr;
+  int n_raw = 0;     // host-known upper bound of the scan size
+  bool have_T = false;
+  Tf32 T_LtoM;
+  uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}, *radix_table = nullptr;
+  int radix_tiles_cap = 0;
+  VoxGridDesc *d_vg = nullptr;
+  float *d_knots = nullptr;
+  size_t knots_cap = 0;
+  // update
+  QSlot *qtab = nullptr;
+  int q_slots = 0;
+  uint32_t *q_slot = nullptr, *q_rank = nullptr;
+  float4 *q_sorted = nullptr;
+  KnnUnit *units = nullptr;
+  int units_cap = 0;
+  int32_t *knn_idx = nullptr;
+  float *knn_d2 = nullptr;
+  uint8_t *knn_ok = nullptr;
+  DevConsts *d_consts = nullptr;
+  double *d_P = nullptr;
+  PointRow *rows = nullptr;
+  Partial *parts = nullptr;
+  int nparts = 296;
+  LinsysOut *d_out = nullptr;
+  // pinned host mirrors
+  struct HostIn {
+    ml_scan_consts c;
+    double P[ML_MAX_HX * ML_MAX_HX];
+  } *h_in = nullptr;
+  LinsysOut *h_out = nullptr;
+  bool rows_valid = false;
+  int rows_k = 0;
+  // timing
+  cudaEvent_t ev[10];
+  bool timing = true;
+  float last_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
+#define CK(call)                                                                                                       \
+  do {                                                                                                                 \
+    cudaError_t e__ = (call);                                                                                          \
+    if (e__ != cudaSuccess) {                                                                                          \
+      char buf__[512];                                                                                                 \
+      snprintf(buf__, sizeof buf__, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__);      \
+      if (h)                                                                                                           \
+        h->err = buf__;                                                                                                \
+      else                                                                                                             \
+        g_global_error = buf__;                                                                                        \
+      return ML_ERR_CUDA;                                                                                              \
+    }                                                                                                                  \
+  } while (0)
+
+#define LAUNCH(kern, grid, block, ...)                                                                                 \
+  do {                                                                                                                 \
+    kern<<<(grid), (block), 0, h->stream>>>(__VA_ARGS__);                                                              \
+    h->launches++;                                                                                                     \
+  } while (0)
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline int *st_field(ml_handle *h, size_t off) { return (int *)((char *)h->d_st + off); }
+#define ST(f) st_field(h, offsetof(ScanState, f))
+
+static int fail(ml_handle *h, int code, const char *msg) {
+  if (h)
+    h->err = msg;
+  else
+    g_global_error = msg;
+  return code;
+}
+
+static int check_launch(ml_handle *h) {
+  CK(cudaGetLastError());
+  return ML_OK;
+}
+
+// exclusive scan of `in` (n on device) into out[0..n]; total optionally to d_total. n_ub = host upper bound.
+static void excl_scan(ml_handle *h, const uint32_t *in, const int *d_n, int n_ub, uint32_t *out, int *d_total) {
+  int tiles = std::max(1, cdiv(n_ub, SCAN_TILE));
+  LAUNCH(k_scan_reduce, tiles, SCAN_BLOCK, in, d_n, h->tile_sums);
+  LAUNCH(k_scan_apply, tiles, SCAN_BLOCK, in, d_n, h->tile_sums, out, d_total);
+}
+
+// stable sort of (keys, vals) by key; result ends in sort_keys[0]/sort_vals[0]. bits = number of key bits to sort.
+static void radix_sort(ml_handle *h, const int *d_n, int n_ub, int bits) {
+  int tiles = std::max(1, cdiv(n_ub, RS_TILE));
+  int passes = std::max(1, (bits + 7) / 8);
+  if (passes & 1)
+    passes++; // even number of passes so the result lands in buffer 0
+  int src = 0;
+  for (int p = 0; p < passes; p++) {
+    LAUNCH(k_radix_hist, tiles, RS_BLOCK, h->sort_keys[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap);
+    LAUNCH(k_radix_scan, 1, 1024, h->radix_table, d_n, h->radix_tiles_cap);
+    LAUNCH(k_radix_scatter, tiles, RS_BLOCK, h->sort_keys[src], h->sort_vals[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap,
+           h->sort_keys[1 - src], h->sort_vals[1 - src]);
+    src = 1 - src;
+  }
+}
+
+// (re)build the dense kNN grid over map_pts[cur] (n = *d_map_n, host copy h->map_n)
+static int rebuild_grid(ml_handle *h) {
+  const int n = h->map_n;
+  LAUNCH(k_bbox_init, 1, 32, h->d_bbox);
+  if (n > 0)
+    LAUNCH(k_bbox, std::min(148 * 8, cdiv(n, 256)), 256, h->map_pts[h->cur], h->d_map_n, h->d_bbox);
+  LAUNCH(k_grid_setup, 1, 32, h->d_bbox, h->d_map_n, h->grid_cell, h->cap_cells, h->d_grid);
+  CK(cudaMemcpyAsync(&h->grid_host, h->d_grid, sizeof(GridDesc), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->map_init = n > 0;
+  if (n <= 0)
+    return ML_OK;
+  const int nc = h->grid_host.ncells;
+  LAUNCH(k_zero_cells, std::min(148 * 8, cdiv(nc + 1, 256)), 256, h->cell_cnt, h->d_grid);
+  LAUNCH(k_cell_count, cdiv(n, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_cnt, h->pt_cell, h->pt_rank);
+  excl_scan(h, h->cell_cnt, &h->d_grid->ncells, nc, h->cell_start, nullptr);
+  LAUNCH(k_cell_scatter, cdiv(n, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_start, h->pt_cell, h->pt_rank, h->cell_pts);
+  return check_launch(h);
+}
+
+static int sync_map_n(ml_handle *h) {
+  CK(cudaMemcpyAsync(&h->map_n, h->d_map_n, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return ML_OK;
+}
+
+extern "C" {
+
+const char *ml_global_error(void) { return g_global_error.c_str(); }
+const char *ml_last_error(const ml_handle *h) { return h ? h->err.c_str() : g_global_error.c_str(); }
+long long ml_launch_count(const ml_handle *h) { return h ? h->launches : 0; }
+
+int ml_create(const ml_config *cfg, ml_handle **out) {
+  ml_handle *h = nullptr;
+  if (!cfg || !out || cfg->max_scan_points <= 0 || cfg->max_map_points <= 0)
+    return fail(nullptr, ML_ERR_ARG, "ml_create: bad config");
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev)
+    return fail(nullptr, ML_ERR_CUDA, "ml_create: no usable CUDA device (this library has no CPU path)");
+  CK(cudaSetDevice(cfg->device));
+  h = new ml_handle();
+  h->cfg = *cfg;
+  h->cap_scan = cfg->max_scan_points;
+  h->cap_map = cfg->max_map_points;
+  h->cap_cells = cfg->max_grid_cells > 0 ? cfg->max_grid_cells : (1 << 24);
+  h->cap_all = h->cap_map + h->cap_scan;
+  h->grid_cell = cfg->grid_cell > 0 ? (double)cfg->grid_cell : 0.5;
+  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  for (auto &e : h->ev)
+    CK(cudaEventCreate(&e));
+  const size_t cs = (size_t)h->cap_scan, cm = (size_t)h->cap_map, ca = (size_t)h->cap_all;
+  CK(cudaMalloc(&h->map_pts[0], sizeof(float4) * ca));
+  CK(cudaMalloc(&h->map_pts[1], sizeof(float4) * ca));
+  CK(cudaMalloc(&h->d_map_n, sizeof(int)));
+  CK(cudaMemset(h->d_map_n, 0, sizeof(int)));
+  CK(cudaMalloc(&h->d_grid, sizeof(GridDesc)));
+  CK(cudaMemset(h->d_grid, 0, sizeof(GridDesc)));
+  CK(cudaMalloc(&h->d_bbox, sizeof(uint32_t) * 8));
+  CK(cudaMalloc(&h->cell_cnt, sizeof(uint32_t) * ((size_t)h->cap_cells + 2)));
+  CK(cudaMalloc(&h->cell_start, sizeof(uint32_t) * ((size_t)h->cap_cells + 2)));
+  CK(cudaMalloc(&h->cell_pts, sizeof(float4) * ca));
+  CK(cudaMalloc(&h->pt_cell, sizeof(uint32_t) * ca));
+  CK(cudaMalloc(&h->pt_rank, sizeof(uint32_t) * ca));
+  const size_t max_scan_len = std::max((size_t)h->cap_cells + 2, ca + 2);
+  CK(cudaMalloc(&h->tile_sums, sizeof(uint32_t) * (max_scan_len / SCAN_TILE + 2)));
+  h->vox_slots = 1;
+  while ((size_t)h->vox_slots < 2 * cs)
+    h->vox_slots <<= 1;
+  CK(cudaMalloc(&h->vox_tab, sizeof(VoxSlot) * (size_t)h->vox_slots));
+  CK(cudaMalloc(&h->add_slot, sizeof(uint32_t) * cs));
+  CK(cudaMalloc(&h->contender, sizeof(uint32_t) * ca));
+  CK(cudaMalloc(&h->keep, sizeof(uint32_t) * (ca + 2)));
+  CK(cudaMalloc(&h->pos, sizeof(uint32_t) * (ca + 2)));
+  CK(cudaMalloc(&h->d_ints, sizeof(int) * 16));
+  CK(cudaMemset(h->d_ints, 0, sizeof(int) * 16));
+  CK(cudaMalloc(&h->add_pts, sizeof(float4) * cs));
+  CK(cudaMalloc(&h->d_raw, sizeof(float) * 4 * cs));
+  CK(cudaMallocHost(&h->h_raw, sizeof(float) * 4 * cs));
+  CK(cudaMalloc(&h->scan_pts, sizeof(float4) * cs));
+  CK(cudaMalloc(&h->scan_orig, sizeof(float4) * cs));
+  CK(cudaMalloc(&h->scan_map, sizeof(float4) * cs));
+  CK(cudaMalloc(&h->scan_tmp, sizeof(float4) * ca));
+  CK(cudaMalloc(&h->d_st, sizeof(ScanState)));
+  CK(cudaMemset(h->d_st, 0, sizeof(ScanState)));
+  for (int b = 0; b < 2; b++) {
+    CK(cudaMalloc(&h->sort_keys[b], sizeof(uint32_t) * ca));
+    CK(cudaMalloc(&h->sort_vals[b], sizeof(uint32_t) * ca));
+  }
+  h->radix_tiles_cap = cdiv((long long)ca, RS_TILE) + 1;
+  CK(cudaMalloc(&h->radix_table, sizeof(uint32_t) * 256 * (size_t)h->radix_tiles_cap));
+  CK(cudaMalloc(&h->d_vg, sizeof(VoxGridDesc)));
+  h->q_slots = 1;
+  while ((size_t)h->q_slots < 2 * cs)
+    h->q_slots <<= 1;
+  CK(cudaMalloc(&h->qtab, sizeof(QSlot) * (size_t)h->q_slots));
+  CK(cudaMalloc(&h->q_slot, sizeof(uint32_t) * cs));
+  CK(cudaMalloc(&h->q_rank, sizeof(uint32_t) * cs));
+  CK(cudaMalloc(&h->q_sorted, sizeof(float4) * cs));
+  h->units_cap = (int)(cs + cs / 32 + 64);
+  CK(cudaMalloc(&h->units, sizeof(KnnUnit) * (size_t)h->units_cap));
+  CK(cudaMalloc(&h->knn_idx, sizeof(int32_t) * cs * ML_MAX_K));
+  CK(cudaMalloc(&h->knn_d2, sizeof(float) * cs * ML_MAX_K));
+  CK(cudaMalloc(&h->knn_ok, cs));
+  CK(cudaMalloc(&h->d_consts, sizeof(DevConsts)));
+  CK(cudaMalloc(&h->d_P, sizeof(double) * ML_MAX_HX * ML_MAX_HX));
+  CK(cudaMalloc(&h->rows, sizeof(PointRow) * cs));
+  CK(cudaMalloc(&h->parts, sizeof(Partial) * ML_NPART_MAX));
+  CK(cudaMalloc(&h->d_out, sizeof(LinsysOut)));
+  CK(cudaMallocHost(&h->h_in, sizeof(*h->h_in)));
+  CK(cudaMallocHost(&h->h_out, sizeof(LinsysOut)));
+  memset(&h->grid_host, 0, sizeof(GridDesc));
+  *out = h;
+  return ML_OK;
+}
+
+void ml_destroy(ml_handle *h) {
+  if (!h)
+    return;
+  cudaStreamSynchronize(h->stream);
+  void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
+                 h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
+                 h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
+                 h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->d_out};
+  for (void *p : dev)
+    if (p)
+      cudaFree(p);
+  if (h->h_raw)
+    cudaFreeHost(h->h_raw);
+  if (h->h_in)
+    cudaFreeHost(h->h_in);
+  if (h->h_out)
+    cudaFreeHost(h->h_out);
+  for (auto &e : h->ev)
+    cudaEventDestroy(e);
+  cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+// ---------------------------------------------------------------------------------------------- map
+int ml_map_reset(ml_handle *h) {
+  if (!h)
+    return ML_ERR_ARG;
+  h->map_n = 0;
+  h->map_init = false;
+  CK(cudaMemsetAsync(h->d_map_n, 0, sizeof(int), h->stream));
+  CK(cudaMemsetAsync(h->d_grid, 0, sizeof(GridDesc), h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return ML_OK;
+}
+int ml_map_initialized(const ml_handle *h) { return h && h->map_init ? 1 : 0; }
+
+int ml_map_build(ml_handle *h, const float *xyzi, int n) {
+  if (!h || n < 0 || (n > 0 && !xyzi))
+    return fail(h, ML_ERR_ARG, "ml_map_build: bad argument");
+  if (n > h->cap_map)
+    return fail(h, ML_ERR_CAPACITY, "ml_map_build: more points than max_map_points");
+  h->cur = 0;
+  if (n > 0)
+    CK(cudaMemcpyAsync(h->map_pts[0], xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+  LAUNCH(k_set_int, 1, 1, h->d_map_n, n);
+  h->map_n = n;
+  return rebuild_grid(h);
+}
+
+int ml_map_build_from_scan(ml_handle *h) {
+  if (!h)
+    return ML_ERR_ARG;
+  ScanState st;
+  CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (st.n_scan > h->cap_map)
+    return fail(h, ML_ERR_CAPACITY, "ml_map_build_from_scan: scan larger than max_map_points");
+  h->cur = 0;
+  if (st.n_scan > 0)
+    CK(cudaMemcpyAsync(h->map_pts[0], h->scan_pts, sizeof(float4) * (size_t)st.n_scan, cudaMemcpyDeviceToDevice, h->stream));
+  LAUNCH(k_set_int, 1, 1, h->d_map_n, st.n_scan);
+  h->map_n = st.n_scan;
+  return rebuild_grid(h);
+}
+
+// shared tail of ml_map_add / ml_map_add_scan: add_pts[0..*d_ints[0]) (host upper bound n_ub) into the map
+static int map_add_device(ml_handle *h, int n_ub, int downsample, float ds, int *n_live) {
+  if (n_ub <= 0) {
+    if (n_live)
+      *n_live = h->map_n;
+    return ML_OK;
+  }
+  if (downsample && !(ds > 0.f))
+    return fail(h, ML_ERR_ARG, "ml_map_add: downsample size must be positive");
+  const int M = h->map_n;
+  int *d_nadd = h->d_ints + 0, *d_total = h->d_ints + 1, *d_ovf = h->d_ints + 2;
+  const uint32_t mask = (uint32_t)h->vox_slots - 1u;
+  LAUNCH(k_set_int, 1, 1, d_ovf, 0);
+  if (downsample) {
+    LAUNCH(k_vox_clear, std::min(148 * 8, cdiv(h->vox_slots, 256)), 256, h->vox_tab, h->vox_slots);
+    LAUNCH(k_vox_insert_new, cdiv(n_ub, 256), 256, h->add_pts, d_nadd, h->d_map_n, ds, h->vox_tab, mask, h->add_slot);
+    if (M > 0)
+      LAUNCH(k_vox_compete_old, cdiv(M, 256), 256, h->map_pts[h->cur], h->d_map_n, ds, h->vox_tab, mask, h->contender);
+  }
+  LAUNCH(k_vox_flags, cdiv(M + n_ub, 256), 256, h->d_map_n, d_nadd, h->vox_tab, h->contender, h->add_slot, downsample, h->keep, d_total);
+  excl_scan(h, h->keep, d_total, M + n_ub, h->pos, h->d_ints + 3);
+  LAUNCH(k_compact2, cdiv(M + n_ub, 256), 256, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, h->keep, h->pos, h->map_pts[1 - h->cur],
+         h->cap_map, d_ovf);
+  LAUNCH(k_copy_int, 1, 1, h->d_map_n, h->d_ints + 3);
+  int host_ints[4];
+  CK(cudaMemcpyAsync(host_ints, h->d_ints, sizeof(host_ints), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (host_ints[2] || host_ints[3] > h->cap_map)
+    return fail(h, ML_ERR_CAPACITY, "ml_map_add: map capacity (max_map_points) exceeded");
+  h->cur = 1 - h->cur;
+  h->map_n = host_ints[3];
+  int rc = rebuild_grid(h);
+  if (n_live)
+    *n_live = h->map_n;
+  return rc;
+}
+
+int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds, int *n_live) {
+  if (!h || n < 0 || (n > 0 && !xyzi))
+    return fail(h, ML_ERR_ARG, "ml_map_add: bad argument");
+  if (n > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_map_add: more points than max_scan_points in one call");
+  if (n > 0)
+    CK(cudaMemcpyAsync(h->add_pts, xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+  LAUNCH(k_set_int, 1, 1, h->d_ints + 0, n);
+  return map_add_device(h, n, downsample, ds, n_live);
+}
+
+int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
+  if (!h)
+    return ML_ERR_ARG;
+  if (!h->have_T)
+    return fail(h, ML_ERR_ARG, "ml_map_add_scan: ml_scan_transform has not been called for this scan");
+  if (h->n_raw > 0)
+    LAUNCH(k_transform, cdiv(h->n_raw, 256), 256, h->scan_orig, ST(n_orig), h->T_LtoM, h->add_pts);
+  LAUNCH(k_copy_int, 1, 1, h->d_ints + 0, ST(n_orig));
+  return map_add_device(h, h->n_raw, downsample, ds, n_live);
+}
+
+// voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated. n_ub host bound. tmp buffers: sort_*, keep, pos.
+static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf) {
+  if (n_ub <= 0)
+    return ML_OK;
+  int *d_pass = h->d_ints + 4;
+  LAUNCH(k_bbox_init, 1, 32, h->d_bbox);
+  LAUNCH(k_bbox, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox);
+  LAUNCH(k_voxgrid_setup, 1, 32, h->d_bbox, d_n, leaf, h->d_vg);
+  LAUNCH(k_vox_index, cdiv(n_ub, 256), 256, src, d_n, h->d_vg, h->sort_keys[0], h->sort_vals[0]);
+  radix_sort(h, d_n, n_ub, 32);
+  LAUNCH(k_seg_heads, cdiv(n_ub, 256), 256, h->sort_keys[0], d_n, h->keep);
+  excl_scan(h, h->keep, d_n, n_ub, h->pos, nullptr);
+  LAUNCH(k_vox_centroid, cdiv(n_ub, 256), 256, src, h->sort_keys[0], h->sort_vals[0], h->keep, h->pos, d_n, dst);
+  // PCL refuses leaf sizes that overflow its int32 voxel index and returns the input unchanged
+  LAUNCH(k_copy_int, 1, 1, d_pass, &h->d_vg->passthrough);
+  LAUNCH(k_copy_if_flag, cdiv(n_ub, 256), 256, src, dst, d_n, d_pass, 1);
+  LAUNCH(k_vox_finish, 1, 32, h->d_vg, h->pos, d_n, d_pass);
+  return check_launch(h);
+}
+
+int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, double decay_time, double decay_dist, int do_downsample,
+                    float ds, int *n_live) {
+  if (!h || !T)
+    return fail(h, ML_ERR_ARG, "ml_map_reanchor: bad argument");
+  if (!h->map_init)
+    return fail(h, ML_SOFT_NO_MAP, "ml_map_reanchor: map not initialised");
+  const int M = h->map_n;
+  const float4 *src = h->map_pts[h->cur];
+  int *d_n = h->d_ints + 5;
+  LAUNCH(k_copy_int, 1, 1, d_n, h->d_map_n);
+  if (do_downsample) {
+    int rc = voxel_filter(h, src, h->scan_tmp, d_n, M, ds);
+    if (rc)
+      return rc;
+    src = h->scan_tmp;
+  }
+  ReanchorArgs a;
+  memcpy(a.T, T, sizeof(a.T));
+  a.now_minus_FT = now_minus_FT, a.decay_time = decay_time, a.decay_dist = decay_dist;
+  // transformed copy into cell_pts (free scratch: the grid is rebuilt below), keep flags, stable compaction
+  LAUNCH(k_reanchor, cdiv(M, 256), 256, src, d_n, a, h->cell_pts, h->keep);
+  excl_scan(h, h->keep, d_n, M, h->pos, h->d_ints + 3);
+  LAUNCH(k_set_int, 1, 1, h->d_ints + 2, 0);
+  LAUNCH(k_compact2, cdiv(M, 256), 256, h->cell_pts, d_n, (const float4 *)nullptr, (const int *)nullptr, h->keep, h->pos,
+         h->map_pts[1 - h->cur], h->cap_map, h->d_ints + 2);
+  LAUNCH(k_copy_int, 1, 1, h->d_map_n, h->d_ints + 3);
+  h->cur = 1 - h->cur;
+  int rc = sync_map_n(h);
+  if (rc)
+    return rc;
+  rc = rebuild_grid(h);
+  if (n_live)
+    *n_live = h->map_n;
+  return rc;
+}
+
+int ml_map_flatten(ml_handle *h, float *xyzi_out, int cap, int *n) {
+  if (!h)
+    return ML_ERR_ARG;
+  int m = std::min(cap, h->map_n);
+  if (m > 0 && xyzi_out) {
+    CK(cudaMemcpyAsync(xyzi_out, h->map_pts[h->cur], sizeof(float4) * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  if (n)
+    *n = h->map_n;
+  return ML_OK;
+}
+int ml_map_size(ml_handle *h, int *n) {
+  if (!h || !n)
+    return ML_ERR_ARG;
+  *n = h->map_n;
+  return ML_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- scan
+static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax) {
+  if (n < 0 || (n > 0 && !xyz) || (stride != 3 && stride != 4))
+    return fail(h, ML_ERR_ARG, "ml_scan_upload: bad argument (stride must be 3 or 4)");
+  if (n > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_scan_upload: more points than max_scan_points");
+  h->n_raw = n;
+  h->have_T = false;
+  h->rows_valid = false;
+  ScanState st;
+  memset(&st, 0, sizeof(st));
+  st.n_raw = n;
+  // ScanState travels in front of the points through the same pinned staging buffer? keep it simple: two copies
+  if (n > 0) {
+    const size_t bytes = sizeof(float) * (size_t)stride * (size_t)n;
+    cudaPointerAttributes at;
+    bool pinned = (cudaPointerGetAttributes(&at, xyz) == cudaSuccess) && (at.type == cudaMemoryTypeHost);
+    cudaGetLastError();
+    const float *src = xyz;
+    if (!pinned) {
+      memcpy(h->h_raw, xyz, bytes);
+      src = h->h_raw;
+    }
+    CK(cudaMemcpyAsync(h->d_raw, src, bytes, cudaMemcpyHostToDevice, h->stream));
+  }
+  CK(cudaMemcpyAsync(h->d_st, &st, sizeof(st), cudaMemcpyHostToDevice, h->stream)); // pageable 32 B: staged by the driver
+  if (n > 0) {
+    LAUNCH(k_range_flags, cdiv(n, 256), 256, h->d_raw, stride, h->d_st, (double)rmin, (double)rmax, h->keep);
+    excl_scan(h, h->keep, ST(n_raw), n, h->pos, nullptr);
+    LAUNCH(k_range_scatter, cdiv(n, 256), 256, h->d_raw, stride, h->d_st, t_rel, h->keep, h->pos, h->scan_pts, h->scan_orig);
+  }
+  return check_launch(h);
+}
+
+int ml_scan_upload(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, int *n_kept) {
+  if (!h)
+    return ML_ERR_ARG;
+  int rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax);
+  if (rc)
+    return rc;
+  if (n_kept) {
+    ScanState st;
+    CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *n_kept = st.n_orig;
+  }
+  return ML_OK;
+}
+
+int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
+  if (!h || n < 0 || (n > 0 && !xyzi))
+    return fail(h, ML_ERR_ARG, "ml_scan_set: bad argument");
+  if (n > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_scan_set: more points than max_scan_points");
+  h->n_raw = n;
+  h->have_T = false;
+  h->rows_valid = false;
+  ScanState st;
+  memset(&st, 0, sizeof(st));
+  st.n_raw = st.n_orig = st.n_scan = n;
+  if (n > 0) {
+    CK(cudaMemcpyAsync(h->scan_pts, xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->scan_orig, h->scan_pts, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToDevice, h->stream));
+  }
+  CK(cudaMemcpyAsync(h->d_st, &st, sizeof(st), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return ML_OK;
+}
+
+int ml_scan_deskew(ml_handle *h, const float *T_LitoL_knots, int n_knots, int total_points) {
+  if (!h || !T_LitoL_knots || n_knots < 2 || total_points < 1)
+    return fail(h, ML_ERR_ARG, "ml_scan_deskew: bad argument");
+  const size_t need = (size_t)n_knots * 12;
+  if (need > h->knots_cap) {
+    if (h->d_knots)
+      cudaFree(h->d_knots);
+    CK(cudaMalloc(&h->d_knots, sizeof(float) * need));
+    h->knots_cap = need;
+  }
+  CK(cudaMemcpyAsync(h->d_knots, T_LitoL_knots, sizeof(float) * need, cudaMemcpyHostToDevice, h->stream));
+  if (h->n_raw > 0)
+    LAUNCH(k_deskew, cdiv(h->n_raw, 256), 256, h->scan_pts, ST(n_scan), h->d_knots, n_knots, total_points);
+  CK(cudaStreamSynchronize(h->stream));
+  return check_launch(h);
+}
+
+static int scan_downsample_async(ml_handle *h, float leaf) {
+  if (!(leaf > 0.f))
+    return fail(h, ML_ERR_ARG, "ml_scan_downsample: leaf must be positive");
+  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf);
+  if (rc)
+    return rc;
+  std::swap(h->scan_pts, h->scan_tmp);
+  return ML_OK;
+}
+
+int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds) {
+  if (!h)
+    return ML_ERR_ARG;
+  int rc = scan_downsample_async(h, leaf);
+  if (rc)
+    return rc;
+  if (n_ds) {
+    ScanState st;
+    CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *n_ds = st.n_scan;
+  }
+  return ML_OK;
+}
+
+static int scan_transform_async(ml_handle *h, const float T[16]) {
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 4; c++)
+      h->T_LtoM.m[4 * r + c] = T[4 * r + c];
+  h->have_T = true;
+  h->rows_valid = false;
+  if (h->n_raw > 0)
+    LAUNCH(k_transform, cdiv(h->n_raw, 256), 256, h->scan_pts, ST(n_scan), h->T_LtoM, h->scan_map);
+  return check_launch(h);
+}
+
+int ml_scan_transform(ml_handle *h, const float T_LtoM[16]) {
+  if (!h || !T_LtoM)
+    return fail(h, ML_ERR_ARG, "ml_scan_transform: bad argument");
+  return scan_transform_async(h, T_LtoM);
+}
+
+int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n) {
+  if (!h || which < 0 || which > 2)
+    return fail(h, ML_ERR_ARG, "ml_scan_download: bad argument");
+  ScanState st;
+  CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  int cnt = which == 2 ? st.n_orig : st.n_scan;
+  const float4 *src = which == 0 ? h->scan_pts : (which == 1 ? h->scan_map : h->scan_orig);
+  int m = std::min(cap, cnt);
+  if (m > 0 && xyzi_out) {
+    CK(cudaMemcpyAsync(xyzi_out, src, sizeof(float4) * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  if (n)
+    *n = cnt;
+  return ML_OK;
+}
+
+// -------------------------------------------------------------------------------------------- update
+} // extern "C"
+
+template <int K> static void launch_knn(ml_handle *h, float max_d2) {
+  const int blocks = 148 * 8;
+  LAUNCH(k_knn<K>, blocks, KNN_WARPS * 32, h->units, h->d_st, h->q_sorted, h->d_grid, h->cell_start, h->cell_pts, max_d2, h->knn_idx,
+         h->knn_d2, h->knn_ok);
+}
+template <int K> static void launch_rows(ml_handle *h) {
+  LAUNCH(k_rows<K>, cdiv(h->n_raw, ROWS_BLOCK), ROWS_BLOCK, h->d_st, h->scan_pts, h->map_pts[h->cur], h->knn_idx, h->knn_ok, h->d_consts,
+         h->rows);
+}
+
+static int knn_async(ml_handle *h, int k, float max_d2) {
+  if (k < 1 || k > ML_MAX_K)
+    return fail(h, ML_ERR_ARG, "knn: k out of range [1, ML_MAX_K]");
+  if (!h->map_init)
+    return fail(h, ML_SOFT_NO_MAP, "knn: map not initialised");
+  if (!h->have_T)
+    return fail(h, ML_ERR_ARG, "knn: ml_scan_transform has not been called for this scan");
+  const int n = h->n_raw;
+  if (n <= 0)
+    return ML_OK;
+  const uint32_t mask = (uint32_t)h->q_slots - 1u;
+  if (h->timing)
+    cudaEventRecord(h->ev[3], h->stream);
+  LAUNCH(k_qslot_clear, std::min(148 * 8, cdiv(h->q_slots, 256)), 256, h->qtab, h->q_slots, h->d_st);
+  LAUNCH(k_query_bin, cdiv(n, 256), 256, h->scan_map, h->d_st, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+  LAUNCH(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, h->units, h->units_cap);
+  LAUNCH(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
+  if (h->timing)
+    cudaEventRecord(h->ev[4], h->stream);
+  switch (k) {
+  case 1: launch_knn<1>(h, max_d2); break;
+  case 2: launch_knn<2>(h, max_d2); break;
+  case 3: launch_knn<3>(h, max_d2); break;
+  case 4: launch_knn<4>(h, max_d2); break;
+  case 5: launch_knn<5>(h, max_d2); break;
+  case 6: launch_knn<6>(h, max_d2); break;
+  case 7: launch_knn<7>(h, max_d2); break;
+  case 8: launch_knn<8>(h, max_d2); break;
+  case 9: launch_knn<9>(h, max_d2); break;
+  default: launch_knn<10>(h, max_d2); break;
+  }
+  if (h->timing)
+    cudaEventRecord(h->ev[5], h->stream);
+  return check_launch(h);
+}
+
+extern "C" {
+
+int ml_knn(ml_handle *h, int k, float max_d2, int32_t *idx, float *d2, uint8_t *ok, int *n) {
+  if (!h)
+    return ML_ERR_ARG;
+  int rc = knn_async(h, k, max_d2);
+  if (rc)
+    return rc;
+  ScanState st;
+  CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  const size_t m = (size_t)st.n_scan;
+  if (idx && m)
+    CK(cudaMemcpyAsync(idx, h->knn_idx, sizeof(int32_t) * m * k, cudaMemcpyDeviceToHost, h->stream));
+  if (d2 && m)
+    CK(cudaMemcpyAsync(d2, h->knn_d2, sizeof(float) * m * k, cudaMemcpyDeviceToHost, h->stream));
+  if (ok && m)
+    CK(cudaMemcpyAsync(ok, h->knn_ok, m, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (n)
+    *n = st.n_scan;
+  return ML_OK;
+}
+
+static int check_consts(ml_handle *h, const ml_scan_consts *c) {
+  if (!c)
+    return fail(h, ML_ERR_ARG, "linsys: null constants");
+  if (c->total_hx < 1 || c->total_hx > ML_MAX_HX)
+    return fail(h, ML_ERR_ARG, "linsys: total_hx out of range");
+  if (c->map_ngbr_num < 3 || c->map_ngbr_num > ML_MAX_K)
+    return fail(h, ML_ERR_ARG, "linsys: map_ngbr_num must be in [3, ML_MAX_K]");
+  if (c->nI < 0 || c->nI > ML_MAX_BLOCKS || c->nA < 0 || c->nA > ML_MAX_BLOCKS)
+    return fail(h, ML_ERR_ARG, "linsys: too many Jacobian blocks");
+  for (int b = 0; b < c->nI + c->nA; b++) {
+    const ml_jac_block &B = b < c->nI ? c->dTdxI[b] : c->dTdxA[b - c->nI];
+    if (B.width < 1 || B.width > 6 || B.col < 0 || B.col + B.width > c->total_hx)
+      return fail(h, ML_ERR_ARG, "linsys: Jacobian block outside [0, total_hx)");
+  }
+  if (c->calib_col >= 0 && c->calib_col + 6 > c->total_hx)
+    return fail(h, ML_ERR_ARG, "linsys: calibration block outside [0, total_hx)");
+  return ML_OK;
+}
+
+// everything after the transform; one synchronisation at the end
+static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
+  const int hx = c->total_hx, k = c->map_ngbr_num;
+  h->h_in->c = *c;
+  memcpy(h->h_in->P, P, sizeof(double) * (size_t)hx * hx);
+  CK(cudaMemcpyAsync(&h->d_consts->c, &h->h_in->c, sizeof(ml_scan_consts), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->d_P, h->h_in->P, sizeof(double) * (size_t)hx * hx, cudaMemcpyHostToDevice, h->stream));
+  LAUNCH(k_prep_consts, 1, 256, h->d_consts, h->d_P);
+  int rc = knn_async(h, k, (float)c->map_ngbr_max_d);
+  if (rc)
+    return rc;
+  const int n = h->n_raw;
+  if (n > 0) {
+    switch (k) {
+    case 3: launch_rows<3>(h); break;
+    case 4: launch_rows<4>(h); break;
+    case 5: launch_rows<5>(h); break;
+    case 6: launch_rows<6>(h); break;
+    case 7: launch_rows<7>(h); break;
+    case 8: launch_rows<8>(h); break;
+    case 9: launch_rows<9>(h); break;
+    default: launch_rows<10>(h); break;
+    }
+  }
+  if (h->timing)
+    cudaEventRecord(h->ev[6], h->stream);
+  h->nparts = std::max(1, std::min(296, cdiv(std::max(n, 1), 128)));
+  LAUNCH(k_reduce, h->nparts, RED_BLOCK, h->d_st, h->rows, h->nparts, h->parts);
+  LAUNCH(k_finalize, 1, 256, h->d_st, h->parts, h->nparts, h->d_consts, h->d_out);
+  if (h->timing)
+    cudaEventRecord(h->ev[7], h->stream);
+  const size_t out_bytes = sizeof(LinsysOut);
+  CK(cudaMemcpyAsync(h->h_out, h->d_out, out_bytes, cudaMemcpyDeviceToHost, h->stream));
+  if (h->timing)
+    cudaEventRecord(h->ev[8], h->stream);
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaGetLastError());
+  h->rows_valid = true;
+  h->rows_k = k;
+  if (HtH)
+    memcpy(HtH, h->h_out->HtH, sizeof(double) * (size_t)hx * hx);
+  if (Htr)
+    memcpy(Htr, h->h_out->Htr, sizeof(double) * (size_t)hx);
+  if (cnt)
+    *cnt = h->h_out->cnt;
+  if (h->timing) {
+    auto el = [&](int a, int b) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
+        cudaGetLastError();
+        return 0.f;
+      }
+      return ms;
+    };
+    h->last_ms[3] = el(3, 4);
+    h->last_ms[4] = el(4, 5);
+    h->last_ms[5] = el(5, 6);
+    h->last_ms[6] = el(6, 7);
+  }
+  return h->h_out->cnt.n_acc > 0 ? ML_OK : ML_SOFT_NO_ROWS;
+}
+
+int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
+  if (!h || !P)
+    return fail(h, ML_ERR_ARG, "ml_linsys: bad argument");
+  int rc = check_consts(h, c);
+  if (rc)
+    return rc;
+  if (h->timing)
+    cudaEventRecord(h->ev[0], h->stream);
+  rc = linsys_async_and_wait(h, c, P, HtH, Htr, cnt);
+  if (h->timing && rc >= 0) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[8]) == cudaSuccess)
+      h->last_ms[7] = ms;
+    else
+      cudaGetLastError();
+    h->last_ms[0] = h->last_ms[1] = h->last_ms[2] = 0.f;
+  }
+  return rc;
+}
+
+int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, float leaf,
+                   const float T_LtoM[16], const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
+  if (!h || !P || !T_LtoM)
+    return fail(h, ML_ERR_ARG, "ml_scan_update: bad argument");
+  int rc = check_consts(h, c);
+  if (rc)
+    return rc;
+  if (!h->map_init)
+    return fail(h, ML_SOFT_NO_MAP, "ml_scan_update: map not initialised");
+  if (h->timing)
+    cudaEventRecord(h->ev[0], h->stream);
+  rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax);
+  if (rc)
+    return rc;
+  if (h->timing)
+    cudaEventRecord(h->ev[1], h->stream);
+  if (leaf > 0.f) {
+    rc = scan_downsample_async(h, leaf);
+    if (rc)
+      return rc;
+  }
+  if (h->timing)
+    cudaEventRecord(h->ev[2], h->stream);
+  rc = scan_transform_async(h, T_LtoM);
+  if (rc)
+    return rc;
+  if (h->timing)
+    cudaEventRecord(h->ev[9], h->stream);
+  rc = linsys_async_and_wait(h, c, P, HtH, Htr, cnt);
+  if (h->timing && rc >= 0) {
+    auto el = [&](int a, int b) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
+        cudaGetLastError();
+        return 0.f;
+      }
+      return ms;
+    };
+    h->last_ms[0] = el(0, 1);
+    h->last_ms[1] = el(1, 2);
+    h->last_ms[2] = el(2, 9);
+    h->last_ms[7] = el(0, 8);
+  }
+  return rc;
+}
+
+int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int *n) {
+  if (!h)
+    return ML_ERR_ARG;
+  if (!h->rows_valid)
+    return fail(h, ML_ERR_ARG, "ml_point_rows: no ml_linsys result for the current scan");
+  const int cnt = h->h_out->st.n_scan;
+  const int hx = h->h_in->c.total_hx;
+  const int m = std::min(cap, cnt);
+  if (n)
+    *n = cnt;
+  if (m <= 0)
+    return ML_OK;
+  if (rows) {
+    std::vector<PointRow> tmp((size_t)m);
+    CK(cudaMemcpyAsync(tmp.data(), h->rows, sizeof(PointRow) * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < m; i++) {
+      ml_point_row &o = rows[i];
+      const PointRow &r = tmp[i];
+      o.status = r.status;
+      o.pad = 0;
+      memcpy(o.plane, r.plane, sizeof(o.plane));
+      o.res = r.res, o.chi2 = r.chi2, o.w = r.w, o.vr = r.vr, o.raw_n = r.raw_n;
+    }
+  }
+  if (h_rows) {
+    double *d_h = nullptr;
+    CK(cudaMalloc(&d_h, sizeof(double) * (size_t)cnt * hx));
+    LAUNCH(k_expand_h, std::min(148 * 8, cdiv((long long)cnt * hx, 256)), 256, h->d_st, h->rows, h->d_consts, d_h);
+    cudaError_t e = cudaMemcpyAsync(h_rows, d_h, sizeof(double) * (size_t)m * hx, cudaMemcpyDeviceToHost, h->stream);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(d_h);
+    CK(e);
+  }
+  return ML_OK;
+}
+
+void ml_abi_sizes(int out[4]) {
+  out[0] = (int)sizeof(ml_scan_consts);
+  out[1] = (int)sizeof(ml_point_row);
+  out[2] = (int)sizeof(ml_counters);
+  out[3] = (int)sizeof(ml_config);
+}
+
+int ml_set_timing(ml_handle *h, int on) {
+  if (!h)
+    return ML_ERR_ARG;
+  h->timing = on != 0;
+  return ML_OK;
+}
+
+int ml_last_timing(ml_handle *h, float ms[8]) {
+  if (!h || !ms)
+    return ML_ERR_ARG;
+  memcpy(ms, h->last_ms, sizeof(h->last_ms));
+  return ML_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Host tail: information form -> square-root form by Cholesky with diagonal pivoting (rank revealing), the
+// stand-in for StateHelper::measurement_compress_inplace (StateHelper.cpp:631-643): Rc^T Rc = HtH, Rc^T rc = Htr.
+// ---------------------------------------------------------------------------------------------------
+int ml_info_to_sqrt(const double *HtH, const double *Htr, int n, double *Rc, double *rc) {
+  if (!HtH || !Htr || !Rc || !rc || n < 1 || n > ML_MAX_HX)
+    return ML_ERR_ARG;
+  std::vector<double> A(HtH, HtH + (size_t)n * n), L((size_t)n * n, 0.0);
+  std::vector<int> perm(n);
+  for (int i = 0; i < n; i++)
+    perm[i] = i;
+  double maxd = 0;
+  for (int i = 0; i < n; i++)
+    maxd = std::max(maxd, A[(size_t)i * n + i]);
+  const double tol = maxd * (double)n * 2.220446049250313e-16 * 16.0;
+  int rank = 0;
+  for (int k = 0; k < n; k++) {
+    int p = k;
+    double best = -1;
+    for (int i = k; i < n; i++) {
+      double d = A[(size_t)perm[i] * n + perm[i]];
+      for (int j = 0; j < k; j++)
+        d -= L[(size_t)perm[i] * n + j] * L[(size_t)perm[i] * n + j];
+      if (d > best)
+        best = d, p = i;
+    }
+    if (!(best > tol))
+      break;
+    std::swap(perm[k], perm[p]);
+    const int pk = perm[k];
+    const double lkk = std::sqrt(best);
+    L[(size_t)pk * n + k] = lkk;
+    for (int i = k + 1; i < n; i++) {
+      const int pi = perm[i];
+      double s = A[(size_t)pi * n + pk];
+      for (int j = 0; j < k; j++)
+        s -= L[(size_t)pi * n + j] * L[(size_t)pk * n + j];
+      L[(size_t)pi * n + k] = s / lkk;
+    }
+    rank++;
+  }
+  // Rc (rank x n): Rc[k][col] = L[col][k];  rc: forward solve L[perm[0..rank)][0..rank) rc = Htr[perm]
+  for (int k = 0; k < n; k++)
+    for (int c = 0; c < n; c++)
+      Rc[(size_t)k * n + c] = k < rank ? L[(size_t)c * n + k] : 0.0;
+  for (int k = 0; k < n; k++)
+    rc[k] = 0.0;
+  for (int k = 0; k < rank; k++) {
+    double s = Htr[perm[k]];
+    for (int j = 0; j < k; j++)
+      s -= L[(size_t)perm[k] * n + j] * rc[j];
+    rc[k] = s / L[(size_t)perm[k] * n + k];
+  }
+  return rank;
+}
+
+} // extern "C"

@@ -1,0 +1,96 @@
+// Shared device/host declarations of the B200 LiDAR-update library (sm_100a only).
+// Reference citations are relative to /root/reference.
+#pragma once
+#include "../../include/mins_lidar.h"
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ml {
+
+// ------------------------------------------------------------------------------------------------
+// fp32 arithmetic that must round like the reference's baseline x86-64 build (no FMA contraction,
+// mins/CMakeLists.txt:15): explicit _rn intrinsics are never fused by nvcc.
+// ------------------------------------------------------------------------------------------------
+// KD_TREE::calc_dist, ikd_Tree.cpp:1406-1410: (dx*dx + dy*dy) + dz*dz
+__device__ __forceinline__ float dist2_ref(float ax, float ay, float az, float bx, float by, float bz) {
+  float dx = __fsub_rn(ax, bx), dy = __fsub_rn(ay, by), dz = __fsub_rn(az, bz);
+  return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+// Eigen Vector3f::norm() as evaluated for a fixed-size 3-vector: sqrt(x*x + (y*y + z*z))
+__device__ __forceinline__ float norm3_ref(float x, float y, float z) {
+  return __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z))));
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dense kNN grid over the map's bounding box. Cell id = (z*dimy + y)*dimx + x (x fastest, so the cells
+// of one x-run are one contiguous range of cell_pts).
+// ------------------------------------------------------------------------------------------------
+struct GridDesc {
+  double ox, oy, oz; // origin (lower corner of cell 0,0,0)
+  double cell, inv_cell;
+  int dimx, dimy, dimz;
+  int ncells;
+  int n_pts; // map points binned
+  int valid;
+};
+
+__device__ __forceinline__ int cell_coord(double x, double o, double inv) { return (int)floor((x - o) * inv); }
+
+// Device-resident state of the current scan (counts produced on the device, read by later kernels).
+struct ScanState {
+  int n_raw;     // points uploaded
+  int n_orig;    // after the range filter  (pointcloud_original)
+  int n_scan;    // after down-sampling      (pointcloud / pointcloud_in_map)
+  int n_units;   // warp work units of the kNN kernel
+  int n_qsorted; // queries placed in cell order
+  int vox_n;     // occupied voxels of the last voxel-grid filter
+  int vox_passthrough;
+  int pad;
+};
+
+// One warp work unit of the kNN kernel: up to 32 queries that fall into the same grid cell.
+struct KnnUnit {
+  int qbase, cnt;
+  int cx, cy, cz;
+};
+
+// Derived per-scan constants living in device memory (built by k_prep_consts from ml_scan_consts + P).
+#define ML_G 18 // [n*dpfinM_dI (6) | n*dpfinM_dA (6) | n*dpfinM_dcalib (6)]
+struct DevConsts {
+  ml_scan_consts c;
+  double T[ML_G * ML_MAX_HX]; // h = g^T T   (rows: the 18 pose-space directions, cols: state columns)
+  double Q[ML_G * ML_G];      // Q = T P T^T  =>  h^T P h = g^T Q g
+};
+
+// Per-point result of k_rows, consumed by the fixed-order reduction.
+struct PointRow {
+  double g[ML_G]; // whitened: g / raw_noise
+  double w;       // ||v||^2
+  double vr;      // v^T r'
+  double chi2;
+  double res;     // whitened scan-point residual
+  double raw_n;
+  double rss;     // ||r'||^2
+  double plane[4];
+  int status;
+  int pad;
+};
+
+#define ML_NPART_MAX 1024
+#define ML_GSYM (ML_G * (ML_G + 1) / 2) // 171
+struct Partial {
+  double G[ML_GSYM];
+  double b[ML_G];
+  double sum_chi, sum_chi2, sum_res, sum_res2;
+  int n_knn_fail, n_plane_fail, n_badmatch, n_chi_rej, n_acc, pad;
+};
+
+// result block copied back to the host in one D2H
+struct LinsysOut {
+  double HtH[ML_MAX_HX * ML_MAX_HX];
+  double Htr[ML_MAX_HX];
+  ml_counters cnt;
+  ScanState st;
+};
+
+} // namespace ml

@@ -1,0 +1,183 @@
+// Scan pre-processing kernels: LiDARData construction (range filter), deskew, PCL-VoxelGrid down-sampling,
+// rigid transform into the map frame. Reference citations relative to /root/reference/mins/src/update/lidar/.
+#pragma once
+#include "prims.cuh"
+
+namespace ml {
+
+// ---- LiDARData::LiDARData, LidarTypes.cpp:36-55 ------------------------------------------------------
+// pass 1: keep flag per raw point (norm in fp32 compared in double like `n > max_range || n < min_range`).
+__global__ void __launch_bounds__(256) k_range_flags(const float *__restrict__ raw, int stride, const ScanState *__restrict__ st,
+                                                    double rmin, double rmax, uint32_t *__restrict__ keep) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= st->n_raw)
+    return;
+  const float *p = raw + (size_t)i * stride;
+  float n = norm3_ref(p[0], p[1], p[2]);
+  keep[i] = ((double)n > rmax || (double)n < rmin) ? 0u : 1u;
+}
+// pass 2 (after the exclusive scan): stable compaction into pointcloud and pointcloud_original, intensity = t_rel
+__global__ void __launch_bounds__(256) k_range_scatter(const float *__restrict__ raw, int stride, ScanState *__restrict__ st, float t_rel,
+                                                      const uint32_t *__restrict__ keep, const uint32_t *__restrict__ pos,
+                                                      float4 *__restrict__ cloud, float4 *__restrict__ orig) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = st->n_raw;
+  if (i == 0) {
+    int kept = (int)pos[n];
+    st->n_orig = kept;
+    st->n_scan = kept;
+  }
+  if (i >= n)
+    return;
+  if (keep[i]) {
+    const float *p = raw + (size_t)i * stride;
+    float4 q = make_float4(p[0], p[1], p[2], t_rel);
+    cloud[pos[i]] = q;
+    orig[pos[i]] = q;
+  }
+}
+
+// ---- pcl::transformPointCloud(cloud, cloud_in_map, Matrix4f), LidarHelper.cpp:192,203 -----------------
+// PCL 1.10 SSE path: m0*x + (m1*y + (m2*z + m3)) per row, fp32, no FMA.
+struct Tf32 {
+  float m[12];
+};
+__device__ __forceinline__ float4 tf_apply(const Tf32 &T, float4 p) {
+  float4 q;
+  q.x = __fadd_rn(__fmul_rn(T.m[0], p.x), __fadd_rn(__fmul_rn(T.m[1], p.y), __fadd_rn(__fmul_rn(T.m[2], p.z), T.m[3])));
+  q.y = __fadd_rn(__fmul_rn(T.m[4], p.x), __fadd_rn(__fmul_rn(T.m[5], p.y), __fadd_rn(__fmul_rn(T.m[6], p.z), T.m[7])));
+  q.z = __fadd_rn(__fmul_rn(T.m[8], p.x), __fadd_rn(__fmul_rn(T.m[9], p.y), __fadd_rn(__fmul_rn(T.m[10], p.z), T.m[11])));
+  q.w = p.w;
+  return q;
+}
+__global__ void __launch_bounds__(256) k_transform(const float4 *__restrict__ in, const int *__restrict__ d_n, Tf32 T,
+                                                  float4 *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *d_n)
+    return;
+  out[i] = tf_apply(T, in[i]);
+}
+
+// ---- LidarHelper::remove_motion_blur loop body, LidarHelper.cpp:71-85 ---------------------------------
+// transformPoint(p, Affine3f): ((r0*x + r1*y) + r2*z) + t. Knots: n_knots 3x4 transforms; point i sits at sweep
+// fraction 1 - (total - i)/total; with n_knots == total every point has its own transform (the reference's case),
+// otherwise the two bracketing knots are blended linearly (documented approximation).
+__global__ void __launch_bounds__(256) k_deskew(float4 *__restrict__ cloud, const int *__restrict__ d_n, const float *__restrict__ knots,
+                                               int n_knots, int total) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *d_n)
+    return;
+  float T[12];
+  if (n_knots == total) {
+#pragma unroll
+    for (int k = 0; k < 12; k++)
+      T[k] = knots[(size_t)i * 12 + k];
+  } else {
+    float u = (float)i / (float)(total > 1 ? total - 1 : 1) * (float)(n_knots - 1);
+    int k0 = min((int)u, n_knots - 2);
+    float a = u - (float)k0;
+#pragma unroll
+    for (int k = 0; k < 12; k++)
+      T[k] = (1.f - a) * knots[(size_t)k0 * 12 + k] + a * knots[(size_t)(k0 + 1) * 12 + k];
+  }
+  float4 p = cloud[i];
+  float4 q;
+  q.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[0], p.x), __fmul_rn(T[1], p.y)), __fmul_rn(T[2], p.z)), T[3]);
+  q.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[4], p.x), __fmul_rn(T[5], p.y)), __fmul_rn(T[6], p.z)), T[7]);
+  q.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[8], p.x), __fmul_rn(T[9], p.y)), __fmul_rn(T[10], p.z)), T[11]);
+  q.w = p.w;
+  cloud[i] = q;
+}
+
+// ---- pcl::VoxelGrid<PointXYZI>, LidarHelper.cpp:89-101,214 -------------------------------------------
+// PCL 1.10 filters/impl/voxel_grid.hpp: bounds -> min_b/div_b -> linear voxel index -> sort -> centroids in
+// ascending index. Here: bbox reduce, k_vox_index, stable radix sort by index (ties in input order), segment
+// heads, one thread per voxel sums its points sequentially in fp32 and divides by the count.
+struct VoxGridDesc {
+  int minb[3];
+  int divb[3];
+  int passthrough; // PCL: "Leaf size is too small" -> output = input
+  float inv_leaf;
+};
+__global__ void k_voxgrid_setup(const uint32_t *__restrict__ bbox, const int *__restrict__ d_n, float leaf, VoxGridDesc *__restrict__ vg) {
+  if (threadIdx.x != 0 || blockIdx.x != 0)
+    return;
+  const float inv = __fdiv_rn(1.0f, leaf);
+  vg->inv_leaf = inv;
+  if (*d_n <= 0) {
+    vg->passthrough = 0;
+    for (int a = 0; a < 3; a++)
+      vg->minb[a] = 0, vg->divb[a] = 1;
+    return;
+  }
+  long long d[3];
+  for (int a = 0; a < 3; a++) {
+    float mn = __uint_as_float(0), mx = 0;
+    uint32_t u0 = bbox[a], u1 = bbox[3 + a];
+    mn = __uint_as_float((u0 & 0x80000000u) ? (u0 & 0x7fffffffu) : ~u0);
+    mx = __uint_as_float((u1 & 0x80000000u) ? (u1 & 0x7fffffffu) : ~u1);
+    d[a] = (long long)(__fmul_rn(__fsub_rn(mx, mn), inv)) + 1;
+    vg->minb[a] = (int)floorf(__fmul_rn(mn, inv));
+    int maxb = (int)floorf(__fmul_rn(mx, inv));
+    vg->divb[a] = maxb - vg->minb[a] + 1;
+  }
+  vg->passthrough = (d[0] * d[1] * d[2] > 2147483647ll) ? 1 : 0;
+}
+__global__ void __launch_bounds__(256) k_vox_index(const float4 *__restrict__ cloud, const int *__restrict__ d_n,
+                                                  const VoxGridDesc *__restrict__ vgd, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *d_n)
+    return;
+  const VoxGridDesc vg = *vgd;
+  float4 p = cloud[i];
+  int i0 = (int)floorf(__fmul_rn(p.x, vg.inv_leaf)) - vg.minb[0];
+  int i1 = (int)floorf(__fmul_rn(p.y, vg.inv_leaf)) - vg.minb[1];
+  int i2 = (int)floorf(__fmul_rn(p.z, vg.inv_leaf)) - vg.minb[2];
+  keys[i] = (uint32_t)(i0 + i1 * vg.divb[0] + i2 * vg.divb[0] * vg.divb[1]);
+  vals[i] = (uint32_t)i;
+}
+// head flag of each run of equal keys in the sorted order
+__global__ void __launch_bounds__(256) k_seg_heads(const uint32_t *__restrict__ keys, const int *__restrict__ d_n, uint32_t *__restrict__ head) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *d_n)
+    return;
+  head[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+}
+// one thread per sorted element that is a head: sum the run sequentially (fp32, input order inside the voxel)
+__global__ void __launch_bounds__(256) k_vox_centroid(const float4 *__restrict__ cloud, const uint32_t *__restrict__ keys,
+                                                     const uint32_t *__restrict__ vals, const uint32_t *__restrict__ head,
+                                                     const uint32_t *__restrict__ pos, const int *__restrict__ d_n,
+                                                     float4 *__restrict__ out) {
+  const int n = *d_n;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !head[i])
+    return;
+  const uint32_t key = keys[i];
+  float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f;
+  int j = i;
+  for (; j < n && keys[j] == key; j++) {
+    float4 p = cloud[vals[j]];
+    sx = __fadd_rn(sx, p.x), sy = __fadd_rn(sy, p.y), sz = __fadd_rn(sz, p.z), sw = __fadd_rn(sw, p.w);
+  }
+  float c = (float)(j - i);
+  out[pos[i]] = make_float4(__fdiv_rn(sx, c), __fdiv_rn(sy, c), __fdiv_rn(sz, c), __fdiv_rn(sw, c));
+}
+// publish the down-sampled count (or copy through when PCL would refuse the leaf size)
+__global__ void k_vox_finish(const VoxGridDesc *__restrict__ vg, const uint32_t *__restrict__ pos, int *__restrict__ d_n_inout,
+                             int *__restrict__ d_passthrough) {
+  if (threadIdx.x != 0 || blockIdx.x != 0)
+    return;
+  *d_passthrough = vg->passthrough;
+  if (!vg->passthrough)
+    *d_n_inout = (int)pos[*d_n_inout];
+}
+__global__ void __launch_bounds__(256) k_copy_if_flag(const float4 *__restrict__ src, float4 *__restrict__ dst, const int *__restrict__ d_n,
+                                                     const int *__restrict__ d_flag, int want) {
+  if ((*d_flag != 0) != (want != 0))
+    return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < *d_n)
+    dst[i] = src[i];
+}
+
+} // namespace ml

@@ -1,0 +1,259 @@
+// The per-scan measurement-update kernels: query binning, exact grid kNN, per-point plane/residual/Jacobian/
+// chi2 rows, fixed-order reduction to the information form. Reference: mins/src/update/lidar/UpdaterLidar.cpp:266-397,
+// LidarHelper.cpp:268-328, mins/src/state/StateHelper.cpp:645-680, mins/src/update/UpdaterStatistics.cpp:94-117.
+#pragma once
+#include "prims.cuh"
+#include "map.cuh"
+
+namespace ml {
+
+// ------------------------------------------------------------------------------------------------
+// Query binning: queries are grouped by grid cell with a hash table (O(N), no pass over the grid).
+// ------------------------------------------------------------------------------------------------
+struct QSlot {
+  unsigned long long key; // 0 = empty
+  uint32_t cnt;
+  uint32_t qbase;
+};
+__device__ __forceinline__ unsigned long long cell_key(int cx, int cy, int cz) {
+  const long long B = 1ll << 20;
+  return ((((unsigned long long)(cx + B)) & 0x1fffffull) << 42) | ((((unsigned long long)(cy + B)) & 0x1fffffull) << 21) |
+         (((unsigned long long)(cz + B)) & 0x1fffffull) | (1ull << 63);
+}
+__device__ __forceinline__ void cell_unkey(unsigned long long k, int *cx, int *cy, int *cz) {
+  const int B = 1 << 20;
+  *cx = (int)((k >> 42) & 0x1fffffull) - B;
+  *cy = (int)((k >> 21) & 0x1fffffull) - B;
+  *cz = (int)(k & 0x1fffffull) - B;
+}
+
+__global__ void __launch_bounds__(256) k_qslot_clear(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    st->n_units = 0;
+    st->n_qsorted = 0;
+  }
+  for (int s = i; s < nslots; s += gridDim.x * blockDim.x) {
+    tab[s].key = 0ull;
+    tab[s].cnt = 0u;
+    tab[s].qbase = 0u;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
+                                                  const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
+                                                  uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= st->n_scan)
+    return;
+  const double ox = gd->ox, oy = gd->oy, oz = gd->oz, inv = gd->inv_cell;
+  float4 q = q_in_map[i];
+  // clamp far-away queries to a band around the grid so the key packing cannot overflow; such queries have no
+  // candidate within reach anyway
+  const int lim = 1 << 19;
+  int cx = max(-lim, min(lim, cell_coord((double)q.x, ox, inv)));
+  int cy = max(-lim, min(lim, cell_coord((double)q.y, oy, inv)));
+  int cz = max(-lim, min(lim, cell_coord((double)q.z, oz, inv)));
+  unsigned long long key = cell_key(cx, cy, cz);
+  uint32_t s = hash64(key) & mask;
+  for (;;) {
+    unsigned long long prev = atomicCAS(&tab[s].key, 0ull, key);
+    if (prev == 0ull || prev == key)
+      break;
+    s = (s + 1) & mask;
+  }
+  q_slot[i] = s;
+  q_rank[i] = atomicAdd(&tab[s].cnt, 1u);
+}
+
+// every occupied slot gets a contiguous range of the sorted query array and ceil(cnt/32) warp units;
+// one atomic pair per block (block-level aggregation)
+__global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st,
+                                                   KnnUnit *__restrict__ units, int units_cap) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t cnt = (s < nslots) ? tab[s].cnt : 0u;
+  uint32_t nu = (cnt + 31u) >> 5;
+  uint32_t tq, tu;
+  uint32_t eq = block_excl_scan<256>(cnt, &tq);
+  uint32_t eu = block_excl_scan<256>(nu, &tu);
+  __shared__ uint32_t bq, bu;
+  if (threadIdx.x == 0) {
+    bq = tq ? (uint32_t)atomicAdd(&st->n_qsorted, (int)tq) : 0u;
+    bu = tu ? (uint32_t)atomicAdd(&st->n_units, (int)tu) : 0u;
+  }
+  __syncthreads();
+  if (cnt) {
+    uint32_t qb = bq + eq, ub = bu + eu;
+    tab[s].qbase = qb;
+    int cx, cy, cz;
+    cell_unkey(tab[s].key, &cx, &cy, &cz);
+    for (uint32_t j = 0; j < nu; j++) {
+      if ((int)(ub + j) < units_cap) {
+        KnnUnit u;
+        u.qbase = (int)(qb + 32u * j);
+        u.cnt = (int)min(32u, cnt - 32u * j);
+        u.cx = cx, u.cy = cy, u.cz = cz;
+        units[ub + j] = u;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_query_scatter(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
+                                                      const QSlot *__restrict__ tab, const uint32_t *__restrict__ q_slot,
+                                                      const uint32_t *__restrict__ q_rank, float4 *__restrict__ q_sorted) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= st->n_scan)
+    return;
+  float4 q = q_in_map[i];
+  q.w = __int_as_float(i);
+  q_sorted[tab[q_slot[i]].qbase + q_rank[i]] = q;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Exact k-NN — replaces KD_TREE::Nearest_Search (ikd_Tree.cpp:358-389, :890-1032) as called by
+// LidarHelper::get_neighbors (LidarHelper.cpp:268-289).
+// One warp per unit (<= 32 queries of one grid cell). The warp walks cubes of cells of growing half-width
+// s = 1..R around the unit's cell; every candidate is loaded once per warp from a warp-uniform address
+// (one broadcast wavefront) and tested by all lanes. After level s every map point NOT yet visited is at
+// least g_s = (fmin + s) * cell away from the lane's query (fmin = distance of the query to the nearest face of
+// its own cell, in cells), so a lane whose k-th best satisfies d2_k < g_s^2 (1 - 1e-6) is exact and complete;
+// the warp stops when all its lanes are. R covers sqrt(max_d2): queries still incomplete after level R have
+// d2_k > max_d2 and are rejected by get_neighbors anyway (LidarHelper.cpp:284).
+// Order: (d2, map index) ascending — total, so results do not depend on the visiting order.
+// ------------------------------------------------------------------------------------------------
+template <int K> struct TopK {
+  float d[K];
+  int i[K];
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+      d[j] = INFINITY;
+      i[j] = 0x7fffffff;
+    }
+  }
+  __device__ __forceinline__ void offer(float d2, int idx) {
+    if (d2 < d[K - 1] || (d2 == d[K - 1] && idx < i[K - 1])) {
+      d[K - 1] = d2;
+      i[K - 1] = idx;
+#pragma unroll
+      for (int s = K - 1; s > 0; --s) {
+        bool sw = d[s] < d[s - 1] || (d[s] == d[s - 1] && i[s] < i[s - 1]);
+        float td = sw ? d[s - 1] : d[s];
+        int ti = sw ? i[s - 1] : i[s];
+        d[s - 1] = sw ? d[s] : d[s - 1];
+        i[s - 1] = sw ? i[s] : i[s - 1];
+        d[s] = td;
+        i[s] = ti;
+      }
+    }
+  }
+};
+
+constexpr int KNN_WARPS = 4;
+
+template <int K>
+__global__ void __launch_bounds__(KNN_WARPS * 32)
+    k_knn(const KnnUnit *__restrict__ units, const ScanState *__restrict__ st, const float4 *__restrict__ q_sorted,
+          const GridDesc *__restrict__ gd, const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
+          int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int n_units = st->n_units;
+  const GridDesc g = *gd;
+  const int R = max(1, (int)ceil(sqrt((double)max_d2) * (1.0 + 1e-5) * g.inv_cell));
+
+  for (int u = warp; u < n_units; u += nwarps) {
+    const KnnUnit un = units[u];
+    const bool active = lane < un.cnt;
+    const float4 q = q_sorted[un.qbase + (active ? lane : 0)];
+    // distance (in cells) from the query to the nearest face of its own cell
+    double fx = ((double)q.x - g.ox) * g.inv_cell - (double)un.cx;
+    double fy = ((double)q.y - g.oy) * g.inv_cell - (double)un.cy;
+    double fz = ((double)q.z - g.oz) * g.inv_cell - (double)un.cz;
+    double fmn = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
+    fmn = fmax(0.0, fmn);
+    TopK<K> best;
+    best.init();
+
+    for (int s = 1; s <= R; s++) {
+      const int w = 2 * s + 1;
+      const int nrows = w * w;
+      for (int rb = 0; rb < nrows; rb += 32) {
+        // lane-parallel row set-up: row t -> (dy, dz); segment A and (for inner rows of levels >= 2) segment B
+        const int t = rb + lane;
+        uint32_t begA = 0, endA = 0, begB = 0, endB = 0;
+        if (t < nrows) {
+          const int dy = t / w - s, dz = t - (t / w) * w - s;
+          const int y = un.cy + dy, z = un.cz + dz;
+          if (y >= 0 && y < g.dimy && z >= 0 && z < g.dimz) {
+            const int rowbase = (z * g.dimy + y) * g.dimx;
+            const bool outer = (s == 1) || (abs(dy) == s) || (abs(dz) == s);
+            if (outer) {
+              int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
+              if (x0 <= x1) {
+                begA = cell_start[rowbase + x0];
+                endA = cell_start[rowbase + x1 + 1];
+              }
+            } else {
+              int xa = un.cx - s, xb = un.cx + s;
+              if (xa >= 0 && xa < g.dimx) {
+                begA = cell_start[rowbase + xa];
+                endA = cell_start[rowbase + xa + 1];
+              }
+              if (xb >= 0 && xb < g.dimx) {
+                begB = cell_start[rowbase + xb];
+                endB = cell_start[rowbase + xb + 1];
+              }
+            }
+          }
+        }
+        // which lanes hold non-empty segments
+        unsigned mA = __ballot_sync(0xffffffffu, endA > begA);
+        unsigned mB = __ballot_sync(0xffffffffu, endB > begB);
+        for (int pass = 0; pass < 2; pass++) {
+          unsigned m = pass ? mB : mA;
+          while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const uint32_t beg = __shfl_sync(0xffffffffu, pass ? begB : begA, src);
+            const uint32_t end = __shfl_sync(0xffffffffu, pass ? endB : endA, src);
+            uint32_t j = beg;
+            for (; j + 4 <= end; j += 4) {
+              const float4 c0 = __ldg(&cell_pts[j]), c1 = __ldg(&cell_pts[j + 1]), c2 = __ldg(&cell_pts[j + 2]),
+                           c3 = __ldg(&cell_pts[j + 3]);
+              best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+              best.offer(dist2_ref(c1.x, c1.y, c1.z, q.x, q.y, q.z), __float_as_int(c1.w));
+              best.offer(dist2_ref(c2.x, c2.y, c2.z, q.x, q.y, q.z), __float_as_int(c2.w));
+              best.offer(dist2_ref(c3.x, c3.y, c3.z, q.x, q.y, q.z), __float_as_int(c3.w));
+            }
+            for (; j < end; j++) {
+              const float4 c0 = __ldg(&cell_pts[j]);
+              best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+            }
+          }
+        }
+      }
+      // completeness test for this level
+      const double gs = (fmn + (double)s) * g.cell;
+      const bool done = !active || ((double)best.d[K - 1] < gs * gs * (1.0 - 1e-6));
+      if (__all_sync(0xffffffffu, done))
+        break;
+    }
+    if (active) {
+      const int qi = __float_as_int(q.w);
+      const bool found = best.i[K - 1] != 0x7fffffff;
+      if (knn_idx) {
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+          knn_idx[(size_t)qi * K + j] = best.i[j] == 0x7fffffff ? -1 : best.i[j];
+          knn_d2[(size_t)qi * K + j] = best.d[j];
+        }
+      }
+      knn_ok[qi] = (found && !((double)best.d[K - 1] > (double)max_d2)) ? 1 : 0;
+    }
+  }
+}
+
+} // namespace ml
