@@ -476,24 +476,31 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   ScanState st;
   memset(&st, 0, sizeof(st));
   st.n_raw = n;
-  // ScanState travels in front of the points through the same pinned staging buffer? keep it simple: two copies
+  const float *raw_src = h->d_raw;
   if (n > 0) {
     const size_t bytes = sizeof(float) * (size_t)stride * (size_t)n;
     cudaPointerAttributes at;
-    bool pinned = (cudaPointerGetAttributes(&at, xyz) == cudaSuccess) && (at.type == cudaMemoryTypeHost);
+    const bool known = cudaPointerGetAttributes(&at, xyz) == cudaSuccess;
     cudaGetLastError();
-    const float *src = xyz;
-    if (!pinned) {
-      memcpy(h->h_raw, xyz, bytes);
-      src = h->h_raw;
+    const bool pinned = known && at.type == cudaMemoryTypeHost;
+    const bool on_device = known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+    if (on_device) {
+      // scan already resident in HBM (e.g. produced by a device-side driver): used in place, no copy
+      raw_src = xyz;
+    } else {
+      const float *src = xyz;
+      if (!pinned) { // pageable host memory: stage through the handle's pinned buffer
+        memcpy(h->h_raw, xyz, bytes);
+        src = h->h_raw;
+      }
+      CK(cudaMemcpyAsync(h->d_raw, src, bytes, cudaMemcpyHostToDevice, h->stream));
     }
-    CK(cudaMemcpyAsync(h->d_raw, src, bytes, cudaMemcpyHostToDevice, h->stream));
   }
   CK(cudaMemcpyAsync(h->d_st, &st, sizeof(st), cudaMemcpyHostToDevice, h->stream)); // pageable 32 B: staged by the driver
   if (n > 0) {
-    LAUNCH(k_range_flags, cdiv(n, 256), 256, h->d_raw, stride, h->d_st, (double)rmin, (double)rmax, h->keep);
+    LAUNCH(k_range_flags, cdiv(n, 256), 256, raw_src, stride, h->d_st, (double)rmin, (double)rmax, h->keep);
     excl_scan(h, h->keep, ST(n_raw), n, h->pos, nullptr);
-    LAUNCH(k_range_scatter, cdiv(n, 256), 256, h->d_raw, stride, h->d_st, t_rel, h->keep, h->pos, h->scan_pts, h->scan_orig);
+    LAUNCH(k_range_scatter, cdiv(n, 256), 256, raw_src, stride, h->d_st, t_rel, h->keep, h->pos, h->scan_pts, h->scan_orig);
   }
   return check_launch(h);
 }
@@ -728,9 +735,9 @@ static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, const do
   }
   if (h->timing)
     cudaEventRecord(h->ev[6], h->stream);
-  h->nparts = std::max(1, std::min(296, cdiv(std::max(n, 1), 128)));
+  h->nparts = std::max(1, std::min(148, cdiv(std::max(n, 1), 128)));
   LAUNCH(k_reduce, h->nparts, RED_BLOCK, h->d_st, h->rows, h->nparts, h->parts);
-  LAUNCH(k_finalize, 1, 256, h->d_st, h->parts, h->nparts, h->d_consts, h->d_out);
+  LAUNCH(k_finalize, 1, 1024, h->d_st, h->parts, h->nparts, h->d_consts, h->d_out);
   if (h->timing)
     cudaEventRecord(h->ev[7], h->stream);
   const size_t out_bytes = sizeof(LinsysOut);

@@ -472,29 +472,30 @@ __global__ void __launch_bounds__(RED_BLOCK) k_reduce(const ScanState *__restric
   }
 }
 
-// Sum the partials in order, expand to the state columns: HtH = T^T G T, Htr = T^T b. One block.
-__global__ void __launch_bounds__(256) k_finalize(const ScanState *__restrict__ st, const Partial *__restrict__ parts, int nparts,
-                                                 const DevConsts *__restrict__ dc, LinsysOut *__restrict__ out) {
+// Sum the partials in a fixed order, expand to the state columns: HtH = T^T G T, Htr = T^T b. One block of 1024:
+// thread (e, q) sums entry e over the partials p = q, q+4, ... with 8 loads in flight; the 4 groups are combined in order.
+__global__ void __launch_bounds__(1024) k_finalize(const ScanState *__restrict__ st, const Partial *__restrict__ parts, int nparts,
+                                                  const DevConsts *__restrict__ dc, LinsysOut *__restrict__ out) {
   __shared__ double G[ML_G][ML_G];
   __shared__ double bv[ML_G];
   __shared__ double GT[ML_G][ML_MAX_HX];
+  __shared__ double grp[4][ML_GSYM + ML_G];
   const int hx = dc->c.total_hx;
-  const int e = threadIdx.x;
+  const int e = threadIdx.x & 255, q = threadIdx.x >> 8;
   if (e < ML_GSYM + ML_G) {
-    double s = 0.0;
-    for (int p = 0; p < nparts; p++)
-      s += (e < ML_GSYM) ? parts[p].G[e] : parts[p].b[e - ML_GSYM];
-    if (e < ML_GSYM) {
-      int r = 0, rem = e;
-      while (rem >= ML_G - r) {
-        rem -= ML_G - r;
-        r++;
-      }
-      G[r][r + rem] = s;
-      G[r + rem][r] = s;
-    } else
-      bv[e - ML_GSYM] = s;
-  } else if (e == 200) {
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const double *base = (e < ML_GSYM) ? &parts[0].G[e] : &parts[0].b[e - ML_GSYM];
+    const size_t stride = sizeof(Partial) / sizeof(double);
+    int p = q;
+    for (; p + 28 < nparts; p += 32) {
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+        acc[u] += base[(size_t)(p + 4 * u) * stride];
+    }
+    for (int u = 0; p < nparts; p += 4, u++)
+      acc[u] += base[(size_t)p * stride];
+    grp[q][e] = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
+  } else if (threadIdx.x == 200) {
     ml_counters cn;
     cn.n_points = st->n_scan;
     cn.n_knn_fail = cn.n_plane_fail = cn.n_badmatch = cn.n_chi_rej = cn.n_acc = 0;
@@ -508,7 +509,21 @@ __global__ void __launch_bounds__(256) k_finalize(const ScanState *__restrict__ 
     out->st = *st;
   }
   __syncthreads();
-  for (int idx = e; idx < ML_G * hx; idx += blockDim.x) {
+  if (q == 0 && e < ML_GSYM + ML_G) {
+    const double s = (grp[0][e] + grp[1][e]) + (grp[2][e] + grp[3][e]);
+    if (e < ML_GSYM) {
+      int r = 0, rem = e;
+      while (rem >= ML_G - r) {
+        rem -= ML_G - r;
+        r++;
+      }
+      G[r][r + rem] = s;
+      G[r + rem][r] = s;
+    } else
+      bv[e - ML_GSYM] = s;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < ML_G * hx; idx += blockDim.x) {
     const int r = idx / hx, j = idx - r * hx;
     double s = 0.0;
 #pragma unroll
@@ -517,7 +532,7 @@ __global__ void __launch_bounds__(256) k_finalize(const ScanState *__restrict__ 
     GT[r][j] = s;
   }
   __syncthreads();
-  for (int idx = e; idx < hx * hx; idx += blockDim.x) {
+  for (int idx = threadIdx.x; idx < hx * hx; idx += blockDim.x) {
     const int a = idx / hx, b2 = idx - a * hx;
     double s = 0.0;
 #pragma unroll
@@ -525,7 +540,7 @@ __global__ void __launch_bounds__(256) k_finalize(const ScanState *__restrict__ 
       s += dc->T[l * ML_MAX_HX + a] * GT[l][b2];
     out->HtH[idx] = s;
   }
-  for (int a = e; a < hx; a += blockDim.x) {
+  for (int a = threadIdx.x; a < hx; a += blockDim.x) {
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)

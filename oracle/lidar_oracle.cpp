@@ -597,8 +597,9 @@ int orc_point(const ml_scan_consts *c, const double *P, const float *pfinL_f, co
 //   optionally Hc/rc = the Givens-compressed system of :397 (Hc: total_hx x total_hx, rc: total_hx; n_c rows valid).
 // Threading = the reference's static chunks (:269-277).
 // ---------------------------------------------------------------------------------------------------------
-int orc_scan_linsys(const ml_scan_consts *c, const double *P, const float *map_xyzi, int M, const float *scan_L,
-                    const float *scan_M, int N, const int32_t *knn_idx_in, double *HtH, double *Htr, ml_counters *cnt,
+static int scan_linsys_core(const ml_scan_consts *c, const double *P, const float *map_xyzi, int M, const float *scan_L,
+                    const float *scan_M, int N, const int32_t *knn_idx_in, const float *nb_in, const uint8_t *nb_ok_in,
+                    double *HtH, double *Htr, ml_counters *cnt,
                     ml_point_row *rows_out, double *h_rows_out, double *Hc, double *rc, int *n_c, int threads) {
   const int k = c->map_ngbr_num, hx = c->total_hx;
   std::vector<int32_t> idx((size_t)N * k);
@@ -606,7 +607,10 @@ int orc_scan_linsys(const ml_scan_consts *c, const double *P, const float *map_x
   std::vector<float> d2((size_t)N * k);
   if (threads < 1)
     threads = 1;
-  if (knn_idx_in) {
+  if (nb_in) {
+    for (int i = 0; i < N; i++)
+      ok[i] = nb_ok_in[i];
+  } else if (knn_idx_in) {
     memcpy(idx.data(), knn_idx_in, sizeof(int32_t) * (size_t)N * k);
     for (int i = 0; i < N; i++) {
       bool good = true;
@@ -634,7 +638,7 @@ int orc_scan_linsys(const ml_scan_consts *c, const double *P, const float *map_x
       if (!ok[i])
         continue;
       for (int j = 0; j < k; j++)
-        memcpy(&nb[4 * j], map_xyzi + 4 * (size_t)idx[(size_t)i * k + j], 4 * sizeof(float));
+        memcpy(&nb[4 * j], nb_in ? nb_in + 4 * ((size_t)i * k + j) : map_xyzi + 4 * (size_t)idx[(size_t)i * k + j], 4 * sizeof(float));
       status[i] = orc_point(c, P, scan_L + 4 * (size_t)i, nb.data(), &Hall[(size_t)i * pr * hx], &rall[(size_t)i * pr],
                             &rows[i], &hrows[(size_t)i * hx]);
     }
@@ -725,6 +729,20 @@ int orc_scan_linsys(const ml_scan_consts *c, const double *P, const float *map_x
     }
   }
   return total_res;
+}
+
+int orc_scan_linsys(const ml_scan_consts *c, const double *P, const float *map_xyzi, int M, const float *scan_L,
+                    const float *scan_M, int N, const int32_t *knn_idx_in, double *HtH, double *Htr, ml_counters *cnt,
+                    ml_point_row *rows_out, double *h_rows_out, double *Hc, double *rc, int *n_c, int threads) {
+  return scan_linsys_core(c, P, map_xyzi, M, scan_L, scan_M, N, knn_idx_in, nullptr, nullptr, HtH, Htr, cnt, rows_out, h_rows_out, Hc,
+                          rc, n_c, threads);
+}
+// same, with the neighbours given by coordinates (what KD_TREE::Nearest_Search returns): nb = N x k x float[4],
+// nb_ok[i] = LidarHelper::get_neighbors' verdict. Used to time the reference tree + restated rows as one CPU path.
+int orc_scan_linsys_nb(const ml_scan_consts *c, const double *P, const float *scan_L, int N, const float *nb, const uint8_t *nb_ok,
+                       double *HtH, double *Htr, ml_counters *cnt, double *Hc, double *rc, int *n_c, int threads) {
+  return scan_linsys_core(c, P, nullptr, 0, scan_L, nullptr, N, nullptr, nb, nb_ok, HtH, Htr, cnt, nullptr, nullptr, Hc, rc, n_c,
+                          threads);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -902,10 +920,11 @@ int orc_voxel_downsample(const float *in_xyzi, int n, float leaf, float *out_xyz
 // point the box is [floor(x/ds)*ds, +ds) per axis in fp32 (:411-416), its centre min + (max-min)/2.0 (:417-419,
 // evaluated in double then stored to float), candidates = live points inside the half-open box (Search_by_range,
 // :1050-1053); the winner is the one closest to the centre, an existing point winning only if strictly closer
-// (:422-430); if more than one candidate existed or the new point won, the box is emptied and the winner
-// (re)inserted at the END of the list (:432-436). Without down-sampling points are appended.
-// Output: the new live list (existing survivors in their old order, then winners in the order they were inserted,
-// with later re-insertions replacing earlier ones). Returns the live count. cap = capacity of `out`.
+// (:422-430); if more than one candidate existed or the new point won, every other candidate of the box dies
+// (:432-436): a winning new point is appended to the list, a winning existing point keeps its place (the tree has no
+// list order; this is the flat-list convention that defines map indices). Without down-sampling points are appended.
+// Output: the live list = surviving existing points in their old order, then surviving new points in input order.
+// Returns the live count. cap = capacity of `out`.
 // Ties among pre-existing points: the reference keeps whichever its tree traversal meets first (not a function of
 // the point set); here the LAST in list order wins so the rule is uniform ("later wins").
 // ---------------------------------------------------------------------------------------------------------
@@ -976,16 +995,16 @@ int orc_map_insert(const float *map_xyzi, int M, const float *add_xyzi, int n, i
         }
       }
       if (storage.size() > 1 || win < 0) { // :432
-        Pt w;
-        if (win < 0)
-          memcpy(w.v, np, 16);
-        else
-          w = pts[win];
         for (int id : storage)
-          pts[id].live = false; // Delete_by_range
-        w.live = true;
-        pts.push_back(w); // Add_by_point
-        bk->push_back((int)pts.size() - 1);
+          if (id != win)
+            pts[id].live = false; // Delete_by_range (a surviving existing point keeps its place in the list)
+        if (win < 0) {
+          Pt w;
+          memcpy(w.v, np, 16);
+          w.live = true;
+          pts.push_back(w); // Add_by_point
+          bk->push_back((int)pts.size() - 1);
+        }
       }
     }
   }

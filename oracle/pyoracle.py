@@ -80,6 +80,8 @@ def ref():
         L.ref_ikd_flatten.argtypes = [vp, vp, C.c_int]
         L.ref_ikd_knn.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp, vp, C.c_int]
         L.ref_ikd_knn.restype = None
+        L.ref_lidar_update.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_double, C.c_double, vp,
+                                       C.POINTER(capi.ml_scan_consts), vp, vp, vp, vp, C.POINTER(capi.ml_counters), C.c_int, vp, vp]
         _ref = L
     return _ref
 
@@ -226,3 +228,17 @@ class RefIkd:
         found = np.zeros(len(q), np.int32)
         self.L.ref_ikd_knn(self.h, q.ctypes.data, len(q), k, nb.ctypes.data, d2.ctypes.data, found.ctypes.data, threads)
         return nb, d2, found
+
+    def lidar_update(self, raw, t_rel, op, T_LtoM, consts, P, threads=8):
+        """The reference CPU path for one scan: LiDARData ctor -> transform -> reference ikd-Tree kNN in
+        the static-chunk thread loop -> restated rows -> stacking -> Givens compression. Returns (Hc, rc, counters, HtH, Htr)."""
+        a = f32(raw)
+        hx = consts.total_hx
+        T, P = f32(T_LtoM).reshape(4, 4), f64(P)
+        Hc, rc, nc = np.zeros((hx, hx)), np.zeros(hx), C.c_int(0)
+        HtH, Htr = np.zeros((hx, hx)), np.zeros(hx)
+        cnt = capi.ml_counters()
+        self.L.ref_lidar_update(self.h, a.ctypes.data, a.shape[1], len(a), t_rel, op.max_range, op.min_range, T.ctypes.data,
+                                C.byref(consts), P.ctypes.data, Hc.ctypes.data, rc.ctypes.data, C.byref(nc), C.byref(cnt), threads,
+                                HtH.ctypes.data, Htr.ctypes.data)
+        return Hc[:nc.value], rc[:nc.value], cnt, HtH, Htr

@@ -88,3 +88,30 @@ void ref_ikd_knn(void *h, const float *q, int nq, int k, float *nb_xyzi, float *
     x.join();
 }
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Whole CPU LiDAR update of one scan, as SURVEY.md §8(d) defines the timed CPU path: the reference's own
+// KD_TREE::Nearest_Search inside the static-chunk thread loop of UpdaterLidar.cpp:269-277, followed by the restated
+// rows / stacking / Givens compression (oracle/lidar_oracle.cpp). Declared here, resolved from liboracle.so.
+// ---------------------------------------------------------------------------------------------------------
+#include "../include/mins_lidar.h"
+extern "C" int orc_range_filter(const float *xyz, int stride, int n, float t_rel, double max_range, double min_range, float *out_xyzi);
+extern "C" void orc_transform_f32(const float *in_xyzi, int n, const float *T, float *out_xyzi);
+extern "C" int orc_scan_linsys_nb(const ml_scan_consts *c, const double *P, const float *scan_L, int N, const float *nb, const uint8_t *nb_ok,
+                                  double *HtH, double *Htr, ml_counters *cnt, double *Hc, double *rc, int *n_c, int threads);
+
+extern "C" int ref_lidar_update(void *tree, const float *raw, int stride, int n, float t_rel, double rmax, double rmin, const float *T_LtoM,
+                                const ml_scan_consts *c, const double *P, double *Hc, double *rc, int *n_c, ml_counters *cnt, int threads,
+                                double *HtH, double *Htr) {
+  std::vector<float> sc(4 * (size_t)std::max(n, 1)), sm(4 * (size_t)std::max(n, 1));
+  int m = orc_range_filter(raw, stride, n, t_rel, rmax, rmin, sc.data());   // LiDARData ctor
+  orc_transform_f32(sc.data(), m, T_LtoM, sm.data());                       // transform_to_map tail
+  const int k = c->map_ngbr_num;
+  std::vector<float> nb((size_t)std::max(m, 1) * k * 4), d2((size_t)std::max(m, 1) * k);
+  std::vector<int> found(std::max(m, 1));
+  ref_ikd_knn(tree, sm.data(), m, k, nb.data(), d2.data(), found.data(), threads); // get_neighbors -> Nearest_Search
+  std::vector<uint8_t> ok(std::max(m, 1));
+  for (int i = 0; i < m; i++)
+    ok[i] = (found[i] >= k && !((double)d2[(size_t)i * k + k - 1] > c->map_ngbr_max_d)) ? 1 : 0; // LidarHelper.cpp:280-285
+  return orc_scan_linsys_nb(c, P, sc.data(), m, nb.data(), ok.data(), HtH, Htr, cnt, Hc, rc, n_c, threads);
+}
