@@ -199,7 +199,7 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   for (auto &e : h->ev)
     CK(cudaEventCreate(&e));
-  const size_t cs = (size_t)h->cap_scan, cm = (size_t)h->cap_map, ca = (size_t)h->cap_all;
+  const size_t cs = (size_t)h->cap_scan, ca = (size_t)h->cap_all;
   CK(cudaMalloc(&h->map_pts[0], sizeof(float4) * ca));
   CK(cudaMalloc(&h->map_pts[1], sizeof(float4) * ca));
   CK(cudaMalloc(&h->d_map_n, sizeof(int)));
@@ -357,8 +357,10 @@ static int map_add_device(ml_handle *h, int n_ub, int downsample, float ds, int 
   int host_ints[4];
   CK(cudaMemcpyAsync(host_ints, h->d_ints, sizeof(host_ints), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  if (host_ints[2] || host_ints[3] > h->cap_map)
+  if (host_ints[2] || host_ints[3] > h->cap_map) {
+    LAUNCH(k_set_int, 1, 1, h->d_map_n, h->map_n); // the map itself is untouched (double-buffered): restore its count
     return fail(h, ML_ERR_CAPACITY, "ml_map_add: map capacity (max_map_points) exceeded");
+  }
   h->cur = 1 - h->cur;
   h->map_n = host_ints[3];
   int rc = rebuild_grid(h);

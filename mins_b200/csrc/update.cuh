@@ -177,19 +177,28 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
     TopK<K> best;
     best.init();
 
-    for (int s = 1; s <= R; s++) {
-      const int w = 2 * s + 1;
-      const int nrows = w * w;
+    // levels below s_lo cannot touch the grid (Chebyshev distance from the unit's cell to the grid box); at s_hi the
+    // cube covers the whole grid, so every map point has been visited and the search is exact whatever max_d2 is
+    const int ox_ = max(max(-un.cx, un.cx - (g.dimx - 1)), 0), oy_ = max(max(-un.cy, un.cy - (g.dimy - 1)), 0),
+              oz_ = max(max(-un.cz, un.cz - (g.dimz - 1)), 0);
+    const int s_lo = max(1, max(ox_, max(oy_, oz_)));
+    const int s_hi = min(R, max(max(max(un.cx, g.dimx - 1 - un.cx), max(un.cy, g.dimy - 1 - un.cy)), max(un.cz, g.dimz - 1 - un.cz)));
+    for (int s = s_lo; s <= s_hi; s++) {
+      // rows (y, z) of the cube clipped to the grid
+      const int y0 = max(un.cy - s, 0), y1 = min(un.cy + s, g.dimy - 1);
+      const int z0 = max(un.cz - s, 0), z1 = min(un.cz + s, g.dimz - 1);
+      const int nz = z1 - z0 + 1;
+      const int nrows = (y1 >= y0 && nz > 0) ? (y1 - y0 + 1) * nz : 0;
       for (int rb = 0; rb < nrows; rb += 32) {
-        // lane-parallel row set-up: row t -> (dy, dz); segment A and (for inner rows of levels >= 2) segment B
+        // lane-parallel row set-up: row t -> (y, z); segment A and (for inner rows of levels > s_lo) segment B
         const int t = rb + lane;
         uint32_t begA = 0, endA = 0, begB = 0, endB = 0;
         if (t < nrows) {
-          const int dy = t / w - s, dz = t - (t / w) * w - s;
-          const int y = un.cy + dy, z = un.cz + dz;
-          if (y >= 0 && y < g.dimy && z >= 0 && z < g.dimz) {
+          const int y = y0 + t / nz, z = z0 + (t - (t / nz) * nz);
+          const int dy = y - un.cy, dz = z - un.cz;
+          {
             const int rowbase = (z * g.dimy + y) * g.dimx;
-            const bool outer = (s == 1) || (abs(dy) == s) || (abs(dz) == s);
+            const bool outer = (s == s_lo) || (abs(dy) == s) || (abs(dz) == s);
             if (outer) {
               int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
               if (x0 <= x1) {
@@ -247,8 +256,10 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
       if (knn_idx) {
 #pragma unroll
         for (int j = 0; j < K; j++) {
-          knn_idx[(size_t)qi * K + j] = best.i[j] == 0x7fffffff ? -1 : best.i[j];
-          knn_d2[(size_t)qi * K + j] = best.d[j];
+          // candidates beyond the search radius are not reported (same convention as the brute-force oracle)
+          const bool in = best.i[j] != 0x7fffffff && best.d[j] <= max_d2;
+          knn_idx[(size_t)qi * K + j] = in ? best.i[j] : -1;
+          knn_d2[(size_t)qi * K + j] = in ? best.d[j] : INFINITY;
         }
       }
       knn_ok[qi] = (found && !((double)best.d[K - 1] > (double)max_d2)) ? 1 : 0;
