@@ -44,39 +44,55 @@ def workload_desc(w, extra=None):
 
 
 class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons sampled in-process through NVML every ~2 ms (a timed region of a few ms is too short
+    for `nvidia-smi -lms`); only samples taken while `active` (the timed regions) are reported."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.stop_flag, self.proc = index, [], False, None
+        self.index, self.samples, self.stop_flag, self.active, self.err = index, [], False, False, None
+        self.sm_max = None
 
     def run(self):
-        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index),
-                                          "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            for line in self.proc.stdout:
-                self.samples.append([x.strip() for x in line.split(",")])
-                if self.stop_flag:
-                    break
-        except Exception:
-            pass
+            import pynvml as nv
+            nv.nvmlInit()
+            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES; map it back to the NVML index when the variable is set
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.index
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.index])
+                except Exception:
+                    pass
+            hdl = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(nv.nvmlDeviceGetMaxClockInfo(hdl, nv.NVML_CLOCK_SM))
+            while not self.stop_flag:
+                if self.active:
+                    clk = nv.nvmlDeviceGetClockInfo(hdl, nv.NVML_CLOCK_SM)
+                    try:
+                        rs = nv.nvmlDeviceGetCurrentClocksEventReasons(hdl)
+                    except Exception:
+                        rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(hdl)
+                    self.samples.append((float(clk), int(rs)))
+                time.sleep(0.002)
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
 
     def finish(self):
         self.stop_flag = True
-        if self.proc:
-            self.proc.terminate()
-        sm, mx, reasons = [], 0, set()
-        for s in self.samples:
-            try:
-                sm.append(float(s[0]))
-                mx = max(mx, float(s[1]))
-                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], s[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            except Exception:
-                pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self.join(timeout=2.0)
+        sm = [c for c, _ in self.samples]
+        reasons = set()
+        for _, r in self.samples:
+            for bit, name in self.REASONS.items():
+                if r & bit:
+                    reasons.add(name)
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.sm_max, "reasons": sorted(reasons),
+               "samples": len(sm), "how": "NVML in-process, ~2 ms period, timed regions only"}
+        if self.err:
+            out["error"] = self.err
+        return out
 
 
 def cpu_reference_run(w, steps, warmup, threads):
@@ -189,6 +205,7 @@ def main():
     sampler.start()
     # ---- timed region 1: device-resident input, device time (events on the handle's stream) --------------------------
     barrier()
+    sampler.active = True
     l0 = m.launch_count()
     t_wall0 = time.perf_counter()
     dev_ms, stage = 0.0, {}
@@ -213,6 +230,7 @@ def main():
         step(host_ptr)
         e2e_s += time.perf_counter() - t0
     barrier()
+    sampler.active = False
     clocks = sampler.finish()
     m.set_timing(1)
 

@@ -532,13 +532,17 @@ __global__ void __launch_bounds__(1024) k_finalize(const ScanState *__restrict__
     GT[r][j] = s;
   }
   __syncthreads();
+  // upper triangle computed once and mirrored: HtH is exactly symmetric
   for (int idx = threadIdx.x; idx < hx * hx; idx += blockDim.x) {
     const int a = idx / hx, b2 = idx - a * hx;
+    if (a > b2)
+      continue;
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
       s += dc->T[l * ML_MAX_HX + a] * GT[l][b2];
     out->HtH[idx] = s;
+    out->HtH[b2 * hx + a] = s;
   }
   for (int a = threadIdx.x; a < hx; a += blockDim.x) {
     double s = 0.0;
