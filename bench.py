@@ -251,9 +251,9 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        kern = {"knn": "k_knn<5>", "rows": "k_rows<5>", "reduce": "k_reduce+k_finalize", "bin": "query binning (4 kernels)",
-                "upload_filter": "range filter (3 kernels)"}
-        cand = {k_: stage.get(k_, 0.0) / args.steps for k_ in ("knn", "rows", "reduce", "bin", "upload_filter")}
+        kern = {"knn": "k_knn<5>", "rows_reduce": "k_rows_reduce<5> (plane fit + residual/Jacobian + chi2 + reduction + finalize)",
+                "bin": "query binning (3 kernels)", "upload_filter": "range filter + transform (2 kernels)"}
+        cand = {k_: stage.get(k_, 0.0) / args.steps for k_ in kern}
         dom = max(cand, key=cand.get)
         ach = ALG_BYTES_PER_POINT * n / (cand[dom] * 1e-3) / 1e9
         traffic = None

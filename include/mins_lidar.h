@@ -188,7 +188,8 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
 int ml_info_to_sqrt(const double *HtH, const double *Htr, int total_hx, double *Rc, double *rc);
 
 /* device-time (ms, CUDA events on the handle's stream) of the stages of the last ml_linsys / ml_scan_update:
- * [0] upload+filter, [1] downsample, [2] transform, [3] query binning, [4] knn, [5] rows, [6] reduce, [7] total */
+ * [0] upload+range filter (+ transform when not down-sampling), [1] downsample, [2] transform, [3] query binning, [4] knn,
+ * [5] rows + reduction + finalize (one fused kernel), [6] D2H of the result block, [7] total */
 int ml_last_timing(ml_handle *h, float ms[8]);
 /* switch the per-stage CUDA-event timers on/off (default on) */
 int ml_set_timing(ml_handle *h, int on);

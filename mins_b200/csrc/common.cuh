@@ -38,14 +38,15 @@ __device__ __forceinline__ int cell_coord(double x, double o, double inv) { retu
 
 // Device-resident state of the current scan (counts produced on the device, read by later kernels).
 struct ScanState {
-  int n_raw;     // points uploaded
-  int n_orig;    // after the range filter  (pointcloud_original)
-  int n_scan;    // after down-sampling      (pointcloud / pointcloud_in_map)
-  int n_units;   // warp work units of the kNN kernel
-  int n_qsorted; // queries placed in cell order
-  int vox_n;     // occupied voxels of the last voxel-grid filter
+  int n_raw;  // points uploaded
+  int n_orig; // after the range filter  (pointcloud_original)
+  int n_scan; // after down-sampling      (pointcloud / pointcloud_in_map)
+  int vox_n;  // occupied voxels of the last voxel-grid filter
   int vox_passthrough;
   int pad;
+  // kNN work-list counters, double-buffered by the parity of the kNN call: call c fills [c & 1] and clears [(c + 1) & 1]
+  int n_units[2];   // warp work units
+  int n_qsorted[2]; // queries placed in cell order
 };
 
 // One warp work unit of the kNN kernel: up to 32 queries that fall into the same grid cell.
@@ -76,14 +77,8 @@ struct PointRow {
   int pad;
 };
 
-#define ML_NPART_MAX 1024
+#define ML_NPART_MAX 256 // >= number of CTAs of the fused rows+reduce kernel (one per SM)
 #define ML_GSYM (ML_G * (ML_G + 1) / 2) // 171
-struct Partial {
-  double G[ML_GSYM];
-  double b[ML_G];
-  double sum_chi, sum_chi2, sum_res, sum_res2;
-  int n_knn_fail, n_plane_fail, n_badmatch, n_chi_rej, n_acc, pad;
-};
 
 // result block copied back to the host in one D2H
 struct LinsysOut {

@@ -56,18 +56,20 @@ __device__ __forceinline__ void sym3_eig_minmax(double a00, double a01, double a
   *lmin = q + 2.0 * p * cos(phi + 2.0943951023931953);
 }
 
-// T (18 x hx) and Q = T P T^T from the scan constants. One block.
-__global__ void __launch_bounds__(256) k_prep_consts(DevConsts *__restrict__ dc, const double *__restrict__ P) {
-  __shared__ double TP[ML_G * ML_MAX_HX];
+// T (18 x hx) and Q = T P T^T from the scan constants. One block of 1024; T and T P staged in shared memory, P read
+// coalesced (thread index runs along P's rows).
+__global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc, const double *__restrict__ P) {
+  __shared__ double sT[ML_G * ML_MAX_HX];
+  __shared__ double sTP[ML_G * ML_MAX_HX];
   const ml_scan_consts &c = dc->c;
   const int hx = c.total_hx;
   for (int e = threadIdx.x; e < ML_G * ML_MAX_HX; e += blockDim.x)
-    dc->T[e] = 0.0;
+    sT[e] = 0.0;
   __syncthreads();
-  // one thread per (block, row, col) would race on overlapping columns (I and A clones may coincide): serialise per row
+  // columns of different blocks may coincide (I and A clones overlap): one thread per row adds its blocks in order
   if (threadIdx.x < ML_G) {
     const int r = threadIdx.x;
-    double *Tr = dc->T + r * ML_MAX_HX;
+    double *Tr = sT + r * ML_MAX_HX;
     if (r < 6) {
       for (int b = 0; b < c.nI; b++)
         for (int cc = 0; cc < c.dTdxI[b].width; cc++)
@@ -81,56 +83,45 @@ __global__ void __launch_bounds__(256) k_prep_consts(DevConsts *__restrict__ dc,
     }
   }
   __syncthreads();
+  for (int e = threadIdx.x; e < ML_G * ML_MAX_HX; e += blockDim.x)
+    dc->T[e] = sT[e];
   for (int e = threadIdx.x; e < ML_G * hx; e += blockDim.x) {
     const int r = e / hx, j = e - r * hx;
-    double s = 0;
-    for (int l = 0; l < hx; l++)
-      s += dc->T[r * ML_MAX_HX + l] * P[(size_t)l * hx + j];
-    TP[r * ML_MAX_HX + j] = s;
+    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+    int l = 0;
+    for (; l + 4 <= hx; l += 4) {
+      s0 += sT[r * ML_MAX_HX + l] * __ldg(&P[(size_t)l * hx + j]);
+      s1 += sT[r * ML_MAX_HX + l + 1] * __ldg(&P[(size_t)(l + 1) * hx + j]);
+      s2 += sT[r * ML_MAX_HX + l + 2] * __ldg(&P[(size_t)(l + 2) * hx + j]);
+      s3 += sT[r * ML_MAX_HX + l + 3] * __ldg(&P[(size_t)(l + 3) * hx + j]);
+    }
+    for (; l < hx; l++)
+      s0 += sT[r * ML_MAX_HX + l] * __ldg(&P[(size_t)l * hx + j]);
+    sTP[r * ML_MAX_HX + j] = (s0 + s1) + (s2 + s3);
   }
   __syncthreads();
   for (int e = threadIdx.x; e < ML_G * ML_G; e += blockDim.x) {
     const int r = e / ML_G, q = e - r * ML_G;
-    double s = 0;
-    for (int l = 0; l < hx; l++)
-      s += TP[r * ML_MAX_HX + l] * dc->T[q * ML_MAX_HX + l];
-    dc->Q[e] = s;
+    double s0 = 0, s1 = 0;
+    int l = 0;
+    for (; l + 2 <= hx; l += 2) {
+      s0 += sTP[r * ML_MAX_HX + l] * sT[q * ML_MAX_HX + l];
+      s1 += sTP[r * ML_MAX_HX + l + 1] * sT[q * ML_MAX_HX + l + 1];
+    }
+    for (; l < hx; l++)
+      s0 += sTP[r * ML_MAX_HX + l] * sT[q * ML_MAX_HX + l];
+    dc->Q[e] = s0 + s1;
   }
 }
 
-constexpr int ROWS_BLOCK = 128;
-
+// One scan point: neighbours -> plane -> gates -> g, w, vr, chi2 (see the header of this file). `c` and `sQ` live in
+// shared memory; `out` arrives zeroed with status 1. out.status: 0 accepted, 1 kNN fail, 2 plane fail, 3 bad match,
+// 4 chi2 reject.
 template <int K>
-__global__ void __launch_bounds__(ROWS_BLOCK)
-    k_rows(const ScanState *__restrict__ st, const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
-           const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, const DevConsts *__restrict__ dc,
-           PointRow *__restrict__ rows) {
-  __shared__ double sQ[ML_G * ML_G];
-  __shared__ ml_scan_consts sc_s;
-  {
-    const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
-    const int *src = reinterpret_cast<const int *>(&dc->c);
-    int *dst = reinterpret_cast<int *>(&sc_s);
-    for (int e = threadIdx.x; e < nw; e += blockDim.x)
-      dst[e] = src[e];
-    for (int e = threadIdx.x; e < ML_G * ML_G; e += blockDim.x)
-      sQ[e] = dc->Q[e];
-  }
-  __syncthreads();
-  const ml_scan_consts &c = sc_s;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= st->n_scan)
-    return;
-  PointRow out;
-#pragma unroll
-  for (int a = 0; a < ML_G; a++)
-    out.g[a] = 0.0;
-  out.w = out.vr = out.chi2 = out.res = out.raw_n = out.rss = 0.0;
-  out.plane[0] = out.plane[1] = out.plane[2] = out.plane[3] = 0.0;
-  out.pad = 0;
-  out.status = 1;
+__device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, const double *__restrict__ sQ,
+                                          const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
+                                          const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, PointRow &out) {
   if (!knn_ok[i]) {
-    rows[i] = out;
     return;
   }
   // ---- neighbours, A = k x 3, d = mean range (LidarHelper.cpp:293-302) ----
@@ -157,7 +148,6 @@ __global__ void __launch_bounds__(ROWS_BLOCK)
     // would... NaN compares false in the reference, but a rank-deficient 5x3 A never passes the later gates)
     if (!(lmin > 0.0) || lmax > c.plane_max_condi * c.plane_max_condi * lmin) {
       out.status = 2;
-      rows[i] = out;
       return;
     }
   }
@@ -227,7 +217,6 @@ __global__ void __launch_bounds__(ROWS_BLOCK)
       bad = bad || (fabs(pl0 * PN[j][0] + pl1 * PN[j][1] + pl2 * PN[j][2] + pl3) > c.plane_max_p2pd);
     if (bad || !(nn == nn)) {
       out.status = 2;
-      rows[i] = out;
       return;
     }
   }
@@ -247,7 +236,6 @@ __global__ void __launch_bounds__(ROWS_BLOCK)
   const double res5 = -(n[0] * pfinM_est[0] + n[1] * pfinM_est[1] + n[2] * pfinM_est[2]) - dmean;
   if (res5 > c.plane_max_p2pd * 3.0) {
     out.status = 3;
-    rows[i] = out;
     return;
   }
   // ---- g = n * [dpfinM_dI | dpfinM_dA | dpfinM_dcalib] (UpdaterLidar.cpp:320-329) ----
@@ -372,27 +360,67 @@ __global__ void __launch_bounds__(ROWS_BLOCK)
   out.raw_n = raw_n;
   out.rss = rss;
   out.status = (chi2 < c.chi2_thr) ? 0 : 4; // NaN -> reject (UpdaterStatistics.cpp:117)
-  rows[i] = out;
 }
 
 // ------------------------------------------------------------------------------------------------
-// Reduction: partial[b] = sum over a contiguous chunk of points, in index order (bit-reproducible).
-// thread e < 171: G entry (i<=j); 171 <= e < 189: b entry; warp 6 (threads 192..223): counters.
+// Fused rows + reduction + finalize (one launch per scan).
+//  * grid = nblocks <= #SMs CTAs of RR_BLOCK threads; CTA b owns the contiguous chunk [b*chunk, (b+1)*chunk) of scan
+//    points and walks it in tiles of RR_BLOCK points.
+//  * phase 1 (all threads): thread t computes point_row of its point and leaves g (18), w, v^T r, chi2, ||r'||^2 in
+//    shared memory (never in HBM unless the parity export `rows_out` is requested).
+//  * phase 2: thread (e, half), e < 189, half < 2, accumulates entry e of G = sum w g g^T (171 upper-triangle entries)
+//    or b = sum g (v^T r) (18) over its half of the tile in point order; warp 12 sums the chi2 statistics.
+//  * the CTA's partial sums go to parts[e][b] (entry-major so the final pass reads coalesced); the last CTA to finish
+//    (ticket) adds the partials in CTA order, expands HtH = T^T G T, Htr = T^T b and writes the result block.
+//  Every sum has a fixed order for a given scan size: results are bit-reproducible run to run.
 // ------------------------------------------------------------------------------------------------
-constexpr int RED_BLOCK = 224;
-constexpr int RED_TILE = 64;
+constexpr int RR_BLOCK = 512;
+constexpr int RR_NE = ML_GSYM + ML_G; // 189
+constexpr int RR_ROW = ML_G + 1;      // padded row of g in shared memory
+#define ML_NRED (RR_NE + 3)           // + sum_chi, sum_chi2, sum_res2
+struct RRParts {
+  double v[ML_NRED][ML_NPART_MAX];
+  int c[5][ML_NPART_MAX];
+};
+constexpr size_t RR_SMEM =
+    sizeof(double) * ((size_t)RR_BLOCK * RR_ROW + 4 * (size_t)RR_BLOCK + ML_G * ML_G) + sizeof(ml_scan_consts) + 64;
 
-__global__ void __launch_bounds__(RED_BLOCK) k_reduce(const ScanState *__restrict__ st, const PointRow *__restrict__ rows, int nparts,
-                                                     Partial *__restrict__ parts) {
-  __shared__ double sg[RED_TILE][ML_G + 1];
-  __shared__ double swg[RED_TILE][ML_G + 1];
-  __shared__ double svr[RED_TILE];
-  __shared__ double schi[RED_TILE], srss[RED_TILE];
-  __shared__ int sstat[RED_TILE];
+template <int K>
+__global__ void __launch_bounds__(RR_BLOCK, 1)
+    k_rows_reduce(const ScanState *__restrict__ st, const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
+                  const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, const DevConsts *__restrict__ dc,
+                  PointRow *__restrict__ rows_out, RRParts *__restrict__ parts, unsigned int *__restrict__ ticket,
+                  LinsysOut *__restrict__ out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double *sg = reinterpret_cast<double *>(smem_raw); // [RR_BLOCK][RR_ROW]
+  double *sw = sg + (size_t)RR_BLOCK * RR_ROW;        // [RR_BLOCK]
+  double *svr = sw + RR_BLOCK;
+  double *schi = svr + RR_BLOCK;
+  double *srss = schi + RR_BLOCK;
+  double *sQ = srss + RR_BLOCK; // [18*18]
+  ml_scan_consts *scp = reinterpret_cast<ml_scan_consts *>(sQ + ML_G * ML_G);
+  __shared__ int scnt[5];
+  __shared__ unsigned int s_last;
+  {
+    const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
+    const int *src = reinterpret_cast<const int *>(&dc->c);
+    int *dst = reinterpret_cast<int *>(scp);
+    for (int e = threadIdx.x; e < nw; e += blockDim.x)
+      dst[e] = src[e];
+    for (int e = threadIdx.x; e < ML_G * ML_G; e += blockDim.x)
+      sQ[e] = dc->Q[e];
+    if (threadIdx.x < 5)
+      scnt[threadIdx.x] = 0;
+  }
+  __syncthreads();
+  const ml_scan_consts &c = *scp;
   const int n = st->n_scan;
-  const int chunk = (n + nparts - 1) / nparts;
-  const int p0 = blockIdx.x * chunk, p1 = min(n, p0 + chunk);
-  const int e = threadIdx.x;
+  const int nb = gridDim.x;
+  const int chunk = (n + nb - 1) / nb;
+  const int p0 = min(n, (int)blockIdx.x * chunk), p1 = min(n, p0 + chunk);
+  // phase-2 role of this thread
+  const int t = threadIdx.x;
+  const int e = t % RR_NE, half = t / RR_NE; // halves 0/1 accumulate; warp 12 (t in [384,416)) does the statistics
   int gi = 0, gj = 0;
   if (e < ML_GSYM) {
     int r = 0, rem = e;
@@ -402,153 +430,176 @@ __global__ void __launch_bounds__(RED_BLOCK) k_reduce(const ScanState *__restric
     }
     gi = r;
     gj = r + rem;
+  } else {
+    gi = e - ML_GSYM;
   }
   double acc = 0.0;
-  // counters (warp 6)
-  int c_knn = 0, c_plane = 0, c_bad = 0, c_chi = 0, c_acc = 0;
-  double s_chi = 0, s_chi2 = 0, s_res = 0, s_res2 = 0;
-  for (int base = p0; base < p1; base += RED_TILE) {
-    const int cnt = min(RED_TILE, p1 - base);
-    for (int idx = threadIdx.x; idx < RED_TILE * (ML_G + 1); idx += RED_BLOCK) {
-      const int p = idx / (ML_G + 1), a = idx - p * (ML_G + 1);
-      if (p < cnt) {
-        const PointRow *r = &rows[base + p];
-        if (a < ML_G) {
-          const double gv = r->g[a];
-          const bool ok = r->status == 0;
-          sg[p][a] = ok ? gv : 0.0;
-          swg[p][a] = ok ? gv * r->w : 0.0;
-        } else {
-          svr[p] = r->status == 0 ? r->vr : 0.0;
-          schi[p] = r->chi2;
-          srss[p] = r->rss;
-          sstat[p] = r->status;
-        }
-      }
-    }
-    __syncthreads();
-    if (e < ML_GSYM) {
-      for (int p = 0; p < cnt; p++)
-        acc += swg[p][gi] * sg[p][gj];
-    } else if (e < ML_GSYM + ML_G) {
-      const int a = e - ML_GSYM;
-      for (int p = 0; p < cnt; p++)
-        acc += sg[p][a] * svr[p];
-    } else if (e >= 192) {
-      const int lane = e - 192;
-      for (int h = 0; h < RED_TILE; h += 32) {
-        const int p = h + lane;
-        const int stt = p < cnt ? sstat[p] : -1;
-        const bool tested = (stt == 0 || stt == 4) && (schi[p < cnt ? p : 0] == schi[p < cnt ? p : 0]);
-        double vchi = tested ? schi[p] : 0.0, vrss = tested ? srss[p] : 0.0;
-        double vchi2 = vchi * vchi;
-        // sum of r' over a point is not an invariant of the projection basis; sum_res carries sum ||r'||_1-free
-        // moment 0 instead: we accumulate ||r'||^2 only (sum_res2) and leave sum_res = 0.
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          vchi += __shfl_xor_sync(0xffffffffu, vchi, o);
-          vchi2 += __shfl_xor_sync(0xffffffffu, vchi2, o);
-          vrss += __shfl_xor_sync(0xffffffffu, vrss, o);
-        }
-        s_chi += vchi, s_chi2 += vchi2, s_res2 += vrss;
-        c_knn += __popc(__ballot_sync(0xffffffffu, stt == 1));
-        c_plane += __popc(__ballot_sync(0xffffffffu, stt == 2));
-        c_bad += __popc(__ballot_sync(0xffffffffu, stt == 3));
-        c_chi += __popc(__ballot_sync(0xffffffffu, stt == 4));
-        c_acc += __popc(__ballot_sync(0xffffffffu, stt == 0));
-      }
-    }
-    __syncthreads();
-  }
-  Partial *out = &parts[blockIdx.x];
-  if (e < ML_GSYM)
-    out->G[e] = acc;
-  else if (e < ML_GSYM + ML_G)
-    out->b[e - ML_GSYM] = acc;
-  else if (e == 192) {
-    out->sum_chi = s_chi, out->sum_chi2 = s_chi2, out->sum_res = s_res, out->sum_res2 = s_res2;
-    out->n_knn_fail = c_knn, out->n_plane_fail = c_plane, out->n_badmatch = c_bad, out->n_chi_rej = c_chi, out->n_acc = c_acc;
-    out->pad = 0;
-  }
-}
+  double s_chi = 0.0, s_chi2 = 0.0, s_rss = 0.0;
 
-// Sum the partials in a fixed order, expand to the state columns: HtH = T^T G T, Htr = T^T b. One block of 1024:
-// thread (e, q) sums entry e over the partials p = q, q+4, ... with 8 loads in flight; the 4 groups are combined in order.
-__global__ void __launch_bounds__(1024) k_finalize(const ScanState *__restrict__ st, const Partial *__restrict__ parts, int nparts,
-                                                  const DevConsts *__restrict__ dc, LinsysOut *__restrict__ out) {
-  __shared__ double G[ML_G][ML_G];
-  __shared__ double bv[ML_G];
-  __shared__ double GT[ML_G][ML_MAX_HX];
-  __shared__ double grp[4][ML_GSYM + ML_G];
-  const int hx = dc->c.total_hx;
-  const int e = threadIdx.x & 255, q = threadIdx.x >> 8;
-  if (e < ML_GSYM + ML_G) {
-    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    const double *base = (e < ML_GSYM) ? &parts[0].G[e] : &parts[0].b[e - ML_GSYM];
-    const size_t stride = sizeof(Partial) / sizeof(double);
-    int p = q;
-    for (; p + 28 < nparts; p += 32) {
+  for (int base = p0; base < p1; base += RR_BLOCK) {
+    const int cnt = min(RR_BLOCK, p1 - base);
+    // ---- phase 1 ----
+    if (t < cnt) {
+      PointRow pr;
 #pragma unroll
-      for (int u = 0; u < 8; u++)
-        acc[u] += base[(size_t)(p + 4 * u) * stride];
+      for (int a = 0; a < ML_G; a++)
+        pr.g[a] = 0.0;
+      pr.w = pr.vr = pr.chi2 = pr.res = pr.raw_n = pr.rss = 0.0;
+      pr.plane[0] = pr.plane[1] = pr.plane[2] = pr.plane[3] = 0.0;
+      pr.pad = 0;
+      pr.status = 1;
+      point_row<K>(base + t, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
+      const bool okp = pr.status == 0;
+#pragma unroll
+      for (int a = 0; a < ML_G; a++)
+        sg[t * RR_ROW + a] = okp ? pr.g[a] : 0.0;
+      sw[t] = okp ? pr.w : 0.0;
+      svr[t] = okp ? pr.vr : 0.0;
+      const bool tested = (pr.status == 0 || pr.status == 4) && (pr.chi2 == pr.chi2);
+      schi[t] = tested ? pr.chi2 : 0.0;
+      srss[t] = tested ? pr.rss : 0.0;
+      atomicAdd(&scnt[pr.status], 1);
+      if (rows_out)
+        rows_out[base + t] = pr;
     }
-    for (int u = 0; p < nparts; p += 4, u++)
-      acc[u] += base[(size_t)p * stride];
-    grp[q][e] = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
-  } else if (threadIdx.x == 200) {
+    __syncthreads();
+    // ---- phase 2 ----
+    if (half < 2) {
+      const int h0 = half ? (cnt + 1) / 2 : 0, h1 = half ? cnt : (cnt + 1) / 2;
+      double a0 = 0.0, a1 = 0.0;
+      int p = h0;
+      if (e < ML_GSYM) {
+        for (; p + 2 <= h1; p += 2) {
+          a0 += (sw[p] * sg[p * RR_ROW + gi]) * sg[p * RR_ROW + gj];
+          a1 += (sw[p + 1] * sg[(p + 1) * RR_ROW + gi]) * sg[(p + 1) * RR_ROW + gj];
+        }
+        if (p < h1)
+          a0 += (sw[p] * sg[p * RR_ROW + gi]) * sg[p * RR_ROW + gj];
+      } else {
+        for (; p + 2 <= h1; p += 2) {
+          a0 += sg[p * RR_ROW + gi] * svr[p];
+          a1 += sg[(p + 1) * RR_ROW + gi] * svr[p + 1];
+        }
+        if (p < h1)
+          a0 += sg[p * RR_ROW + gi] * svr[p];
+      }
+      acc += a0 + a1;
+    } else if (t >= 384 && t < 416) { // warp 12: chi2 statistics, lane-strided then a fixed shuffle tree
+      const int lane = t - 384;
+      double vchi = 0.0, vchi2 = 0.0, vrss = 0.0;
+      for (int p = lane; p < cnt; p += 32) {
+        const double x = schi[p];
+        vchi += x;
+        vchi2 += x * x;
+        vrss += srss[p];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        vchi += __shfl_xor_sync(0xffffffffu, vchi, o);
+        vchi2 += __shfl_xor_sync(0xffffffffu, vchi2, o);
+        vrss += __shfl_xor_sync(0xffffffffu, vrss, o);
+      }
+      s_chi += vchi, s_chi2 += vchi2, s_rss += vrss;
+    }
+    __syncthreads();
+  }
+  // ---- CTA partial: combine the two halves in a fixed order ----
+  if (half == 1)
+    sw[e] = acc; // sw is free after the last tile's barrier
+  __syncthreads();
+  if (half == 0)
+    parts->v[e][blockIdx.x] = acc + sw[e];
+  if (t == 384) {
+    parts->v[RR_NE + 0][blockIdx.x] = s_chi;
+    parts->v[RR_NE + 1][blockIdx.x] = s_chi2;
+    parts->v[RR_NE + 2][blockIdx.x] = s_rss;
+  }
+  if (t < 5)
+    parts->c[t][blockIdx.x] = scnt[t];
+  // ---- last CTA finalizes ----
+  __threadfence();
+  __syncthreads();
+  if (t == 0) {
+    const unsigned int prev = atomicAdd(ticket, 1u);
+    s_last = (prev == (unsigned int)nb - 1u) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last)
+    return;
+  __threadfence();
+  // shared-memory carve-up for the tail (the phase buffers are dead now)
+  double *fsum = sg;                  // [ML_NRED]
+  double *G = fsum + 256;             // [18][18]
+  double *bv = G + ML_G * ML_G;       // [18]
+  double *sT = bv + 32;               // [18][ML_MAX_HX]
+  double *GT = sT + ML_G * ML_MAX_HX; // [18][ML_MAX_HX]
+  const int hx = c.total_hx;
+  const int lane = t & 31, wid = t >> 5;
+  const volatile RRParts *vp = parts; // written by other CTAs: do not serve from L1
+  for (int q = wid; q < ML_NRED; q += RR_BLOCK / 32) {
+    double v = 0.0;
+    for (int bq = lane; bq < nb; bq += 32)
+      v += vp->v[q][bq];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0)
+      fsum[q] = v;
+  }
+  if (wid < 5) { // integer counters
+    int v = 0;
+    for (int bq = lane; bq < nb; bq += 32)
+      v += vp->c[wid][bq];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0)
+      scnt[wid] = v;
+  }
+  for (int q = t; q < ML_G * ML_MAX_HX; q += RR_BLOCK)
+    sT[q] = dc->T[q];
+  __syncthreads();
+  if (t < ML_GSYM) {
+    G[gi * ML_G + gj] = fsum[t];
+    G[gj * ML_G + gi] = fsum[t];
+  } else if (t < RR_NE) {
+    bv[t - ML_GSYM] = fsum[t];
+  } else if (t == RR_NE) {
     ml_counters cn;
-    cn.n_points = st->n_scan;
-    cn.n_knn_fail = cn.n_plane_fail = cn.n_badmatch = cn.n_chi_rej = cn.n_acc = 0;
-    cn.sum_chi = cn.sum_chi2 = cn.sum_res = cn.sum_res2 = 0.0;
-    for (int p = 0; p < nparts; p++) {
-      cn.n_knn_fail += parts[p].n_knn_fail, cn.n_plane_fail += parts[p].n_plane_fail, cn.n_badmatch += parts[p].n_badmatch;
-      cn.n_chi_rej += parts[p].n_chi_rej, cn.n_acc += parts[p].n_acc;
-      cn.sum_chi += parts[p].sum_chi, cn.sum_chi2 += parts[p].sum_chi2, cn.sum_res += parts[p].sum_res, cn.sum_res2 += parts[p].sum_res2;
-    }
+    cn.n_points = n;
+    cn.n_acc = scnt[0], cn.n_knn_fail = scnt[1], cn.n_plane_fail = scnt[2], cn.n_badmatch = scnt[3], cn.n_chi_rej = scnt[4];
+    cn.sum_chi = fsum[RR_NE + 0], cn.sum_chi2 = fsum[RR_NE + 1], cn.sum_res = 0.0, cn.sum_res2 = fsum[RR_NE + 2];
     out->cnt = cn;
     out->st = *st;
+    *ticket = 0u; // ready for the next scan
   }
   __syncthreads();
-  if (q == 0 && e < ML_GSYM + ML_G) {
-    const double s = (grp[0][e] + grp[1][e]) + (grp[2][e] + grp[3][e]);
-    if (e < ML_GSYM) {
-      int r = 0, rem = e;
-      while (rem >= ML_G - r) {
-        rem -= ML_G - r;
-        r++;
-      }
-      G[r][r + rem] = s;
-      G[r + rem][r] = s;
-    } else
-      bv[e - ML_GSYM] = s;
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < ML_G * hx; idx += blockDim.x) {
+  for (int idx = t; idx < ML_G * hx; idx += RR_BLOCK) {
     const int r = idx / hx, j = idx - r * hx;
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
-      s += G[r][l] * dc->T[l * ML_MAX_HX + j];
-    GT[r][j] = s;
+      s += G[r * ML_G + l] * sT[l * ML_MAX_HX + j];
+    GT[r * ML_MAX_HX + j] = s;
   }
   __syncthreads();
   // upper triangle computed once and mirrored: HtH is exactly symmetric
-  for (int idx = threadIdx.x; idx < hx * hx; idx += blockDim.x) {
+  for (int idx = t; idx < hx * hx; idx += RR_BLOCK) {
     const int a = idx / hx, b2 = idx - a * hx;
     if (a > b2)
       continue;
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
-      s += dc->T[l * ML_MAX_HX + a] * GT[l][b2];
+      s += sT[l * ML_MAX_HX + a] * GT[l * ML_MAX_HX + b2];
     out->HtH[idx] = s;
     out->HtH[b2 * hx + a] = s;
   }
-  for (int a = threadIdx.x; a < hx; a += blockDim.x) {
+  for (int a = t; a < hx; a += RR_BLOCK) {
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
-      s += dc->T[l * ML_MAX_HX + a] * bv[l];
+      s += sT[l * ML_MAX_HX + a] * bv[l];
     out->Htr[a] = s;
   }
 }

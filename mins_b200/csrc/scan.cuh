@@ -5,38 +5,6 @@
 
 namespace ml {
 
-// ---- LiDARData::LiDARData, LidarTypes.cpp:36-55 ------------------------------------------------------
-// pass 1: keep flag per raw point (norm in fp32 compared in double like `n > max_range || n < min_range`).
-__global__ void __launch_bounds__(256) k_range_flags(const float *__restrict__ raw, int stride, const ScanState *__restrict__ st,
-                                                    double rmin, double rmax, uint32_t *__restrict__ keep) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= st->n_raw)
-    return;
-  const float *p = raw + (size_t)i * stride;
-  float n = norm3_ref(p[0], p[1], p[2]);
-  keep[i] = ((double)n > rmax || (double)n < rmin) ? 0u : 1u;
-}
-// pass 2 (after the exclusive scan): stable compaction into pointcloud and pointcloud_original, intensity = t_rel
-__global__ void __launch_bounds__(256) k_range_scatter(const float *__restrict__ raw, int stride, ScanState *__restrict__ st, float t_rel,
-                                                      const uint32_t *__restrict__ keep, const uint32_t *__restrict__ pos,
-                                                      float4 *__restrict__ cloud, float4 *__restrict__ orig) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int n = st->n_raw;
-  if (i == 0) {
-    int kept = (int)pos[n];
-    st->n_orig = kept;
-    st->n_scan = kept;
-  }
-  if (i >= n)
-    return;
-  if (keep[i]) {
-    const float *p = raw + (size_t)i * stride;
-    float4 q = make_float4(p[0], p[1], p[2], t_rel);
-    cloud[pos[i]] = q;
-    orig[pos[i]] = q;
-  }
-}
-
 // ---- pcl::transformPointCloud(cloud, cloud_in_map, Matrix4f), LidarHelper.cpp:192,203 -----------------
 // PCL 1.10 SSE path: m0*x + (m1*y + (m2*z + m3)) per row, fp32, no FMA.
 struct Tf32 {
@@ -50,6 +18,120 @@ __device__ __forceinline__ float4 tf_apply(const Tf32 &T, float4 p) {
   q.w = p.w;
   return q;
 }
+// ---- LiDARData::LiDARData, LidarTypes.cpp:36-55 ------------------------------------------------------
+// Stable compaction of the in-range points in two launches (no intermediate flag/prefix arrays in HBM):
+//   k_range_count   : per-tile (2048 points) count of kept points; CTA 0 initialises the scan state
+//   k_range_compact : every CTA sums the counts of the tiles before it (<= 128 values), ranks its own points with warp
+//                     ballots and writes pointcloud, pointcloud_original and - when the map transform is already known -
+//                     pointcloud_in_map (LidarHelper.cpp:192) in the same pass.
+// Keep rule: norm in fp32 compared in double like `n > max_range || n < min_range` (LidarTypes.cpp:39).
+constexpr int RF_BLOCK = 256;
+constexpr int RF_TILE = 2048; // 8 warps x 8 rounds x 32 lanes
+
+template <bool VEC4> __device__ __forceinline__ float4 load_raw(const float *__restrict__ raw, int stride, int i) {
+  if (VEC4)
+    return __ldg(reinterpret_cast<const float4 *>(raw) + i);
+  const float *p = raw + (size_t)i * stride;
+  return make_float4(p[0], p[1], p[2], 0.f);
+}
+__device__ __forceinline__ bool range_keep(const float4 p, double rmin, double rmax) {
+  const float nrm = norm3_ref(p.x, p.y, p.z);
+  return !((double)nrm > rmax || (double)nrm < rmin);
+}
+
+template <bool VEC4>
+__global__ void __launch_bounds__(RF_BLOCK) k_range_count(const float *__restrict__ raw, int stride, int n, double rmin, double rmax,
+                                                          ScanState *__restrict__ st, uint32_t *__restrict__ tile_sums) {
+  __shared__ uint32_t wsum[RF_BLOCK / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int wbase = blockIdx.x * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
+  uint32_t cnt = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int i = wbase + r * 32 + lane;
+    const bool k = i < n && range_keep(load_raw<VEC4>(raw, stride, i), rmin, rmax);
+    cnt += __popc(__ballot_sync(0xffffffffu, k));
+  }
+  if (lane == 0)
+    wsum[wid] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < RF_BLOCK / 32; w++)
+      s += wsum[w];
+    tile_sums[blockIdx.x] = s;
+    if (blockIdx.x == 0) {
+      st->n_raw = n;
+      st->vox_n = 0;
+      st->vox_passthrough = 0;
+    }
+  }
+}
+
+template <bool VEC4>
+__global__ void __launch_bounds__(RF_BLOCK)
+    k_range_compact(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax,
+                    const uint32_t *__restrict__ tile_sums, ScanState *__restrict__ st, float4 *__restrict__ cloud,
+                    float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map /* nullptr: transform later */) {
+  __shared__ uint32_t wsum[RF_BLOCK / 32];
+  __shared__ uint32_t tile_prefix;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid == 0) { // counts of the tiles before this one, fixed order
+    uint32_t s = 0;
+    for (int b = lane; b < (int)blockIdx.x; b += 32)
+      s += tile_sums[b];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0)
+      tile_prefix = s;
+  }
+  const int wbase = blockIdx.x * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
+  float4 pt[8];
+  uint32_t bal[8];
+  uint32_t cnt = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int i = wbase + r * 32 + lane;
+    pt[r] = i < n ? load_raw<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool k = i < n && range_keep(pt[r], rmin, rmax);
+    bal[r] = __ballot_sync(0xffffffffu, k);
+    cnt += __popc(bal[r]);
+  }
+  if (lane == 0)
+    wsum[wid] = cnt;
+  __syncthreads();
+  uint32_t pos = tile_prefix;
+  for (int w = 0; w < wid; w++)
+    pos += wsum[w];
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    uint32_t tot = tile_prefix;
+#pragma unroll
+    for (int w = 0; w < RF_BLOCK / 32; w++)
+      tot += wsum[w];
+    st->n_orig = (int)tot;
+    st->n_scan = (int)tot;
+  }
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    if ((bal[r] >> lane) & 1u) {
+      const uint32_t o = pos + __popc(bal[r] & lt);
+      const float4 q = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
+      cloud[o] = q;
+      orig[o] = q;
+      if (in_map)
+        in_map[o] = tf_apply(T, q);
+    }
+    pos += __popc(bal[r]);
+  }
+}
+__global__ void k_scanstate_zero(ScanState *__restrict__ st) {
+  st->n_raw = st->n_orig = st->n_scan = 0;
+  st->vox_n = st->vox_passthrough = 0;
+}
+
 __global__ void __launch_bounds__(256) k_transform(const float4 *__restrict__ in, const int *__restrict__ d_n, Tf32 T,
                                                   float4 *__restrict__ out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -27,19 +27,6 @@ __device__ __forceinline__ void cell_unkey(unsigned long long k, int *cx, int *c
   *cz = (int)(k & 0x1fffffull) - B;
 }
 
-__global__ void __launch_bounds__(256) k_qslot_clear(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) {
-    st->n_units = 0;
-    st->n_qsorted = 0;
-  }
-  for (int s = i; s < nslots; s += gridDim.x * blockDim.x) {
-    tab[s].key = 0ull;
-    tab[s].cnt = 0u;
-    tab[s].qbase = 0u;
-  }
-}
-
 __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
                                                   const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
                                                   uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
@@ -68,7 +55,7 @@ __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_
 
 // every occupied slot gets a contiguous range of the sorted query array and ceil(cnt/32) warp units;
 // one atomic pair per block (block-level aggregation)
-__global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st,
+__global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st, int ph,
                                                    KnnUnit *__restrict__ units, int units_cap) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t cnt = (s < nslots) ? tab[s].cnt : 0u;
@@ -78,8 +65,8 @@ __global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int
   uint32_t eu = block_excl_scan<256>(nu, &tu);
   __shared__ uint32_t bq, bu;
   if (threadIdx.x == 0) {
-    bq = tq ? (uint32_t)atomicAdd(&st->n_qsorted, (int)tq) : 0u;
-    bu = tu ? (uint32_t)atomicAdd(&st->n_units, (int)tu) : 0u;
+    bq = tq ? (uint32_t)atomicAdd(&st->n_qsorted[ph], (int)tq) : 0u;
+    bu = tu ? (uint32_t)atomicAdd(&st->n_units[ph], (int)tu) : 0u;
   }
   __syncthreads();
   if (cnt) {
@@ -154,13 +141,24 @@ constexpr int KNN_WARPS = 4;
 
 template <int K>
 __global__ void __launch_bounds__(KNN_WARPS * 32)
-    k_knn(const KnnUnit *__restrict__ units, const ScanState *__restrict__ st, const float4 *__restrict__ q_sorted,
+    k_knn(const KnnUnit *__restrict__ units, ScanState *__restrict__ st, int ph, const float4 *__restrict__ q_sorted,
           const GridDesc *__restrict__ gd, const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
-          int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok) {
+          int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok, QSlot *__restrict__ qtab, int q_slots) {
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  const int n_units = st->n_units;
+  const int n_units = st->n_units[ph];
+  // housekeeping for the next kNN call: the query hash table is dead once the queries are in cell order (nobody reads it
+  // in this kernel), and the other parity's work-list counters are idle
+  for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < q_slots; s += gridDim.x * blockDim.x) {
+    qtab[s].key = 0ull;
+    qtab[s].cnt = 0u;
+    qtab[s].qbase = 0u;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    st->n_units[ph ^ 1] = 0;
+    st->n_qsorted[ph ^ 1] = 0;
+  }
   const GridDesc g = *gd;
   const int R = max(1, (int)ceil(sqrt((double)max_d2) * (1.0 + 1e-5) * g.inv_cell));
 

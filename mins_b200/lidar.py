@@ -277,7 +277,7 @@ class LidarMap:
     def timing(self):
         ms = (C.c_float * 8)()
         self.lib.ml_last_timing(self.h, ms)
-        return dict(zip(["upload_filter", "downsample", "transform", "bin", "knn", "rows", "reduce", "total"], list(ms)))
+        return dict(zip(["upload_filter", "downsample", "transform", "bin", "knn", "rows_reduce", "d2h", "total"], list(ms)))
 
     def set_timing(self, on):
         self.lib.ml_set_timing(self.h, int(on))
