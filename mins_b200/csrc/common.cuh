@@ -61,6 +61,7 @@ struct DevConsts {
   ml_scan_consts c;
   double T[ML_G * ML_MAX_HX]; // h = g^T T   (rows: the 18 pose-space directions, cols: state columns)
   double Q[ML_G * ML_G];      // Q = T P T^T  =>  h^T P h = g^T Q g
+  double Qu[ML_G * (ML_G + 1) / 2]; // packed upper triangle of Q by rows, off-diagonal entries doubled
 };
 
 // Per-point result of k_rows, consumed by the fixed-order reduction.

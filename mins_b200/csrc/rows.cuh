@@ -112,6 +112,18 @@ __global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc
       s0 += sTP[r * ML_MAX_HX + l] * sT[q * ML_MAX_HX + l];
     dc->Q[e] = s0 + s1;
   }
+  __syncthreads();
+  __threadfence_block();
+  // packed upper triangle, off-diagonals doubled, for the per-point quadratic form g^T Q g
+  for (int e = threadIdx.x; e < ML_GSYM; e += blockDim.x) {
+    int r = 0, rem = e;
+    while (rem >= ML_G - r) {
+      rem -= ML_G - r;
+      r++;
+    }
+    const int q = r + rem;
+    dc->Qu[e] = (q == r) ? dc->Q[r * ML_G + r] : dc->Q[r * ML_G + q] + dc->Q[q * ML_G + r];
+  }
 }
 
 // One scan point: neighbours -> plane -> gates -> g, w, vr, chi2 (see the header of this file). `c` and `sQ` live in
@@ -340,14 +352,18 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
 #pragma unroll
   for (int a = 0; a < ML_G; a++)
     g[a] *= ir;
+  // sQ = packed upper triangle of Q by rows, off-diagonal entries doubled (Q is symmetric): 171 terms instead of 324
   double s = 0.0;
+  {
+    int q = 0;
 #pragma unroll
-  for (int a = 0; a < ML_G; a++) {
-    double acc = 0.0;
+    for (int a = 0; a < ML_G; a++) {
+      double acc = 0.0;
 #pragma unroll
-    for (int bq = 0; bq < ML_G; bq++)
-      acc += sQ[a * ML_G + bq] * g[bq];
-    s += g[a] * acc;
+      for (int bq = a; bq < ML_G; bq++)
+        acc += sQ[q++] * g[bq];
+      s += g[a] * acc;
+    }
   }
   const double chi2 = rss - s * vr * vr / (1.0 + s * wv);
 #pragma unroll
@@ -363,27 +379,34 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Fused rows + reduction + finalize (one launch per scan).
-//  * grid = nblocks <= #SMs CTAs of RR_BLOCK threads; CTA b owns the contiguous chunk [b*chunk, (b+1)*chunk) of scan
-//    points and walks it in tiles of RR_BLOCK points.
-//  * phase 1 (all threads): thread t computes point_row of its point and leaves g (18), w, v^T r, chi2, ||r'||^2 in
-//    shared memory (never in HBM unless the parity export `rows_out` is requested).
-//  * phase 2: thread (e, half), e < 189, half < 2, accumulates entry e of G = sum w g g^T (171 upper-triangle entries)
-//    or b = sum g (v^T r) (18) over its half of the tile in point order; warp 12 sums the chi2 statistics.
-//  * the CTA's partial sums go to parts[e][b] (entry-major so the final pass reads coalesced); the last CTA to finish
-//    (ticket) adds the partials in CTA order, expands HtH = T^T G T, Htr = T^T b and writes the result block.
-//  Every sum has a fixed order for a given scan size: results are bit-reproducible run to run.
+// Fused rows + reduction + finalize (one launch per scan). Warp-autonomous: no CTA-wide barrier in the main loop.
+//  * the scan is cut into tiles of 32 points; tile j belongs to global warp j mod NW, with global warp id
+//    gw = warp_in_cta * gridDim + cta (so a partial last round spreads over all SMs). A warp walks its tiles in order.
+//  * phase 1 (32 lanes): lane computes point_row of its point and leaves g (18), w, v^T r in the warp's shared-memory
+//    slab (never in HBM unless the parity export `rows_out` is requested); chi2 statistics by a fixed shuffle tree.
+//  * phase 2 (21 lanes): G = sum w g g^T is cut into 3x3 blocks; lane r < 21 owns upper-triangle block (bi, bj) and adds
+//    the 32 points in order (7 shared loads for 9 to 12 FMAs); diagonal blocks also carry b = sum g (v^T r).
+//    The running sums live in the warp's slab.
+//  * end: one barrier, CTA partial = sum over its warps in warp order -> parts[e][cta] (entry-major so the final pass reads
+//    coalesced); the last CTA to finish (ticket) adds the partials in CTA order, expands HtH = T^T G T, Htr = T^T b and
+//    writes the result block. Every sum has a fixed order for a given scan size and SM count: bit-reproducible.
 // ------------------------------------------------------------------------------------------------
 constexpr int RR_BLOCK = 512;
+constexpr int RR_WARPS = RR_BLOCK / 32;
 constexpr int RR_NE = ML_GSYM + ML_G; // 189
 constexpr int RR_ROW = ML_G + 1;      // padded row of g in shared memory
+constexpr int RR_ROLES = 21;          // upper-triangle 3x3 blocks of the 18x18 matrix
+constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diagonal blocks)
 #define ML_NRED (RR_NE + 3)           // + sum_chi, sum_chi2, sum_res2
 struct RRParts {
   double v[ML_NRED][ML_NPART_MAX];
   int c[5][ML_NPART_MAX];
 };
-constexpr size_t RR_SMEM =
-    sizeof(double) * ((size_t)RR_BLOCK * RR_ROW + 4 * (size_t)RR_BLOCK + ML_G * ML_G) + sizeof(ml_scan_consts) + 64;
+// per-warp slab: g rows | w | vr | running sums | 4 statistics
+constexpr int RR_SLAB = 32 * RR_ROW + 32 + 32 + RR_ROLES * RR_RACC + 4;
+constexpr size_t RR_SMEM = sizeof(double) * ((size_t)RR_WARPS * RR_SLAB + ML_GSYM + 1) + sizeof(ml_scan_consts) + 64;
+
+__device__ __forceinline__ int rr_role_of(int bi, int bj) { return bi * 6 - (bi * (bi - 1)) / 2 + (bj - bi); }
 
 template <int K>
 __global__ void __launch_bounds__(RR_BLOCK, 1)
@@ -392,130 +415,159 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
                   PointRow *__restrict__ rows_out, RRParts *__restrict__ parts, unsigned int *__restrict__ ticket,
                   LinsysOut *__restrict__ out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double *sg = reinterpret_cast<double *>(smem_raw); // [RR_BLOCK][RR_ROW]
-  double *sw = sg + (size_t)RR_BLOCK * RR_ROW;        // [RR_BLOCK]
-  double *svr = sw + RR_BLOCK;
-  double *schi = svr + RR_BLOCK;
-  double *srss = schi + RR_BLOCK;
-  double *sQ = srss + RR_BLOCK; // [18*18]
-  ml_scan_consts *scp = reinterpret_cast<ml_scan_consts *>(sQ + ML_G * ML_G);
+  double *slabs = reinterpret_cast<double *>(smem_raw);
+  double *sQ = slabs + (size_t)RR_WARPS * RR_SLAB; // packed Qu (171)
+  ml_scan_consts *scp = reinterpret_cast<ml_scan_consts *>(sQ + ML_GSYM + 1);
   __shared__ int scnt[5];
   __shared__ unsigned int s_last;
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
   {
     const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
     const int *src = reinterpret_cast<const int *>(&dc->c);
     int *dst = reinterpret_cast<int *>(scp);
-    for (int e = threadIdx.x; e < nw; e += blockDim.x)
+    for (int e = t; e < nw; e += RR_BLOCK)
       dst[e] = src[e];
-    for (int e = threadIdx.x; e < ML_G * ML_G; e += blockDim.x)
-      sQ[e] = dc->Q[e];
-    if (threadIdx.x < 5)
-      scnt[threadIdx.x] = 0;
+    for (int e = t; e < ML_GSYM; e += RR_BLOCK)
+      sQ[e] = dc->Qu[e];
+    if (t < 5)
+      scnt[t] = 0;
   }
+  double *sg = slabs + (size_t)wid * RR_SLAB; // [32][RR_ROW]
+  double *sw = sg + 32 * RR_ROW;               // [32]
+  double *svr = sw + 32;                       // [32]
+  double *sacc = svr + 32;                     // [RR_ROLES][RR_RACC]
+  double *sstat = sacc + RR_ROLES * RR_RACC;   // chi, chi^2, rss
+  for (int e = lane; e < RR_ROLES * RR_RACC + 4; e += 32)
+    sacc[e] = 0.0;
   __syncthreads();
   const ml_scan_consts &c = *scp;
   const int n = st->n_scan;
   const int nb = gridDim.x;
-  const int chunk = (n + nb - 1) / nb;
-  const int p0 = min(n, (int)blockIdx.x * chunk), p1 = min(n, p0 + chunk);
-  // phase-2 role of this thread
-  const int t = threadIdx.x;
-  const int e = t % RR_NE, half = t / RR_NE; // halves 0/1 accumulate; warp 12 (t in [384,416)) does the statistics
-  int gi = 0, gj = 0;
-  if (e < ML_GSYM) {
-    int r = 0, rem = e;
-    while (rem >= ML_G - r) {
-      rem -= ML_G - r;
+  const int NW = nb * RR_WARPS;
+  const int gw = wid * nb + (int)blockIdx.x;
+  const int ntiles = (n + 31) >> 5;
+  // phase-2 role of this lane: block (bi, bj), bi <= bj
+  int bi = 0, bj = 0;
+  if (lane < RR_ROLES) {
+    int r = 0, rem = lane;
+    while (rem >= 6 - r) {
+      rem -= 6 - r;
       r++;
     }
-    gi = r;
-    gj = r + rem;
-  } else {
-    gi = e - ML_GSYM;
+    bi = r;
+    bj = r + rem;
   }
-  double acc = 0.0;
-  double s_chi = 0.0, s_chi2 = 0.0, s_rss = 0.0;
+  int c_st[5] = {0, 0, 0, 0, 0};
 
-  for (int base = p0; base < p1; base += RR_BLOCK) {
-    const int cnt = min(RR_BLOCK, p1 - base);
+  for (int tile = gw; tile < ntiles; tile += NW) {
+    const int i = (tile << 5) + lane;
     // ---- phase 1 ----
-    if (t < cnt) {
-      PointRow pr;
+    PointRow pr;
 #pragma unroll
-      for (int a = 0; a < ML_G; a++)
-        pr.g[a] = 0.0;
-      pr.w = pr.vr = pr.chi2 = pr.res = pr.raw_n = pr.rss = 0.0;
-      pr.plane[0] = pr.plane[1] = pr.plane[2] = pr.plane[3] = 0.0;
-      pr.pad = 0;
-      pr.status = 1;
-      point_row<K>(base + t, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
-      const bool okp = pr.status == 0;
-#pragma unroll
-      for (int a = 0; a < ML_G; a++)
-        sg[t * RR_ROW + a] = okp ? pr.g[a] : 0.0;
-      sw[t] = okp ? pr.w : 0.0;
-      svr[t] = okp ? pr.vr : 0.0;
-      const bool tested = (pr.status == 0 || pr.status == 4) && (pr.chi2 == pr.chi2);
-      schi[t] = tested ? pr.chi2 : 0.0;
-      srss[t] = tested ? pr.rss : 0.0;
-      atomicAdd(&scnt[pr.status], 1);
+    for (int a = 0; a < ML_G; a++)
+      pr.g[a] = 0.0;
+    pr.w = pr.vr = pr.chi2 = pr.res = pr.raw_n = pr.rss = 0.0;
+    pr.plane[0] = pr.plane[1] = pr.plane[2] = pr.plane[3] = 0.0;
+    pr.pad = 0;
+    pr.status = 1;
+    if (i < n) {
+      point_row<K>(i, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
       if (rows_out)
-        rows_out[base + t] = pr;
+        rows_out[i] = pr;
     }
-    __syncthreads();
-    // ---- phase 2 ----
-    if (half < 2) {
-      const int h0 = half ? (cnt + 1) / 2 : 0, h1 = half ? cnt : (cnt + 1) / 2;
-      double a0 = 0.0, a1 = 0.0;
-      int p = h0;
-      if (e < ML_GSYM) {
-        for (; p + 2 <= h1; p += 2) {
-          a0 += (sw[p] * sg[p * RR_ROW + gi]) * sg[p * RR_ROW + gj];
-          a1 += (sw[p + 1] * sg[(p + 1) * RR_ROW + gi]) * sg[(p + 1) * RR_ROW + gj];
-        }
-        if (p < h1)
-          a0 += (sw[p] * sg[p * RR_ROW + gi]) * sg[p * RR_ROW + gj];
-      } else {
-        for (; p + 2 <= h1; p += 2) {
-          a0 += sg[p * RR_ROW + gi] * svr[p];
-          a1 += sg[(p + 1) * RR_ROW + gi] * svr[p + 1];
-        }
-        if (p < h1)
-          a0 += sg[p * RR_ROW + gi] * svr[p];
-      }
-      acc += a0 + a1;
-    } else if (t >= 384 && t < 416) { // warp 12: chi2 statistics, lane-strided then a fixed shuffle tree
-      const int lane = t - 384;
-      double vchi = 0.0, vchi2 = 0.0, vrss = 0.0;
-      for (int p = lane; p < cnt; p += 32) {
-        const double x = schi[p];
-        vchi += x;
-        vchi2 += x * x;
-        vrss += srss[p];
-      }
+    const bool okp = i < n && pr.status == 0;
+#pragma unroll
+    for (int a = 0; a < ML_G; a++)
+      sg[lane * RR_ROW + a] = okp ? pr.g[a] : 0.0;
+    sw[lane] = okp ? pr.w : 0.0;
+    svr[lane] = okp ? pr.vr : 0.0;
+    {
+      const bool tested = i < n && (pr.status == 0 || pr.status == 4) && (pr.chi2 == pr.chi2);
+      double vchi = tested ? pr.chi2 : 0.0, vrss = tested ? pr.rss : 0.0;
+      double vchi2 = vchi * vchi;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         vchi += __shfl_xor_sync(0xffffffffu, vchi, o);
         vchi2 += __shfl_xor_sync(0xffffffffu, vchi2, o);
         vrss += __shfl_xor_sync(0xffffffffu, vrss, o);
       }
-      s_chi += vchi, s_chi2 += vchi2, s_rss += vrss;
+      if (lane == 0) {
+        sstat[0] += vchi;
+        sstat[1] += vchi2;
+        sstat[2] += vrss;
+      }
+#pragma unroll
+      for (int q = 0; q < 5; q++)
+        c_st[q] += __popc(__ballot_sync(0xffffffffu, i < n && pr.status == q));
     }
-    __syncthreads();
+    const unsigned any_ok = __ballot_sync(0xffffffffu, okp);
+    __syncwarp();
+    // ---- phase 2 ----
+    if (any_ok && lane < RR_ROLES) {
+      double a9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      double b3[3] = {0, 0, 0};
+      const double *gI = sg + 3 * bi, *gJ = sg + 3 * bj;
+#pragma unroll 4
+      for (int p = 0; p < 32; p++) {
+        const double w = sw[p];
+        const double x0 = gI[p * RR_ROW] * w, x1 = gI[p * RR_ROW + 1] * w, x2 = gI[p * RR_ROW + 2] * w;
+        const double y0 = gJ[p * RR_ROW], y1 = gJ[p * RR_ROW + 1], y2 = gJ[p * RR_ROW + 2];
+        a9[0] += x0 * y0, a9[1] += x0 * y1, a9[2] += x0 * y2;
+        a9[3] += x1 * y0, a9[4] += x1 * y1, a9[5] += x1 * y2;
+        a9[6] += x2 * y0, a9[7] += x2 * y1, a9[8] += x2 * y2;
+        if (bi == bj) {
+          const double vr = svr[p];
+          b3[0] += y0 * vr, b3[1] += y1 * vr, b3[2] += y2 * vr;
+        }
+      }
+      double *my = sacc + lane * RR_RACC;
+#pragma unroll
+      for (int q = 0; q < 9; q++)
+        my[q] += a9[q];
+      if (bi == bj) {
+        my[9] += b3[0], my[10] += b3[1], my[11] += b3[2];
+      }
+    }
+    __syncwarp();
   }
-  // ---- CTA partial: combine the two halves in a fixed order ----
-  if (half == 1)
-    sw[e] = acc; // sw is free after the last tile's barrier
+  if (lane == 0) {
+#pragma unroll
+    for (int q = 0; q < 5; q++)
+      if (c_st[q])
+        atomicAdd(&scnt[q], c_st[q]);
+  }
   __syncthreads();
-  if (half == 0)
-    parts->v[e][blockIdx.x] = acc + sw[e];
-  if (t == 384) {
-    parts->v[RR_NE + 0][blockIdx.x] = s_chi;
-    parts->v[RR_NE + 1][blockIdx.x] = s_chi2;
-    parts->v[RR_NE + 2][blockIdx.x] = s_rss;
+  // ---- CTA partial: sum over the warps in warp order ----
+  if (t < RR_NE) {
+    int role, q;
+    if (t < ML_GSYM) {
+      int r = 0, rem = t;
+      while (rem >= ML_G - r) {
+        rem -= ML_G - r;
+        r++;
+      }
+      const int gi = r, gj = r + rem;
+      role = rr_role_of(gi / 3, gj / 3);
+      q = (gi % 3) * 3 + (gj % 3);
+    } else {
+      const int a = t - ML_GSYM;
+      role = rr_role_of(a / 3, a / 3);
+      q = 9 + a % 3;
+    }
+    double v = 0.0;
+#pragma unroll 4
+    for (int w = 0; w < RR_WARPS; w++)
+      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + role * RR_RACC + q];
+    parts->v[t][blockIdx.x] = v;
+  } else if (t < RR_NE + 3) {
+    const int q = t - RR_NE;
+    double v = 0.0;
+    for (int w = 0; w < RR_WARPS; w++)
+      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + RR_ROLES * RR_RACC + q];
+    parts->v[t][blockIdx.x] = v;
+  } else if (t >= 256 && t < 261) {
+    parts->c[t - 256][blockIdx.x] = scnt[t - 256];
   }
-  if (t < 5)
-    parts->c[t][blockIdx.x] = scnt[t];
   // ---- last CTA finalizes ----
   __threadfence();
   __syncthreads();
@@ -527,16 +579,15 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
   if (!s_last)
     return;
   __threadfence();
-  // shared-memory carve-up for the tail (the phase buffers are dead now)
-  double *fsum = sg;                  // [ML_NRED]
+  // shared-memory carve-up for the tail (the slabs are dead now)
+  double *fsum = slabs;               // [ML_NRED]
   double *G = fsum + 256;             // [18][18]
   double *bv = G + ML_G * ML_G;       // [18]
   double *sT = bv + 32;               // [18][ML_MAX_HX]
   double *GT = sT + ML_G * ML_MAX_HX; // [18][ML_MAX_HX]
   const int hx = c.total_hx;
-  const int lane = t & 31, wid = t >> 5;
   const volatile RRParts *vp = parts; // written by other CTAs: do not serve from L1
-  for (int q = wid; q < ML_NRED; q += RR_BLOCK / 32) {
+  for (int q = wid; q < ML_NRED; q += RR_WARPS) {
     double v = 0.0;
     for (int bq = lane; bq < nb; bq += 32)
       v += vp->v[q][bq];
@@ -560,8 +611,13 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     sT[q] = dc->T[q];
   __syncthreads();
   if (t < ML_GSYM) {
-    G[gi * ML_G + gj] = fsum[t];
-    G[gj * ML_G + gi] = fsum[t];
+    int r = 0, rem = t;
+    while (rem >= ML_G - r) {
+      rem -= ML_G - r;
+      r++;
+    }
+    G[r * ML_G + r + rem] = fsum[t];
+    G[(r + rem) * ML_G + r] = fsum[t];
   } else if (t < RR_NE) {
     bv[t - ML_GSYM] = fsum[t];
   } else if (t == RR_NE) {
