@@ -14,7 +14,8 @@ ML_OK, ML_SOFT_NO_ROWS, ML_SOFT_NO_MAP = 0, 1, 2
 ML_ERR_CUDA, ML_ERR_CAPACITY, ML_ERR_ARG = -1, -2, -3
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmins_lidar.so")
+# MINS_LIDAR_LIB: development override to A/B-test a differently compiled build of the same library
+LIB_PATH = os.environ.get("MINS_LIDAR_LIB") or os.path.join(_HERE, "libmins_lidar.so")
 
 
 class ml_config(C.Structure):

@@ -860,16 +860,15 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     return fail(h, ML_SOFT_NO_MAP, "ml_scan_update: map not initialised");
   if (h->timing)
     cudaEventRecord(h->ev[0], h->stream);
-  rc = consts_async(h, c, P);
-  if (rc)
-    return rc;
   const bool ds = leaf > 0.f;
   // without down-sampling the compaction pass also writes pointcloud_in_map
   rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax, ds ? nullptr : T_LtoM);
-  if (rc) {
-    cudaStreamSynchronize(h->stream2);
+  if (rc)
     return rc;
-  }
+  // the constants are enqueued after the scan so that the GPU already works while the host stages them
+  rc = consts_async(h, c, P);
+  if (rc)
+    return rc;
   if (h->timing)
     cudaEventRecord(h->ev[1], h->stream);
   if (ds) {

@@ -391,7 +391,10 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
 //    coalesced); the last CTA to finish (ticket) adds the partials in CTA order, expands HtH = T^T G T, Htr = T^T b and
 //    writes the result block. Every sum has a fixed order for a given scan size and SM count: bit-reproducible.
 // ------------------------------------------------------------------------------------------------
-constexpr int RR_BLOCK = 512;
+#ifndef ML_RR_BLOCK
+#define ML_RR_BLOCK 512
+#endif
+constexpr int RR_BLOCK = ML_RR_BLOCK;
 constexpr int RR_WARPS = RR_BLOCK / 32;
 constexpr int RR_NE = ML_GSYM + ML_G; // 189
 constexpr int RR_ROW = ML_G + 1;      // padded row of g in shared memory
@@ -565,8 +568,8 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     for (int w = 0; w < RR_WARPS; w++)
       v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + RR_ROLES * RR_RACC + q];
     parts->v[t][blockIdx.x] = v;
-  } else if (t >= 256 && t < 261) {
-    parts->c[t - 256][blockIdx.x] = scnt[t - 256];
+  } else if (t >= 192 && t < 197) {
+    parts->c[t - 192][blockIdx.x] = scnt[t - 192];
   }
   // ---- last CTA finalizes ----
   __threadfence();

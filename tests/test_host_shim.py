@@ -1,0 +1,63 @@
+"""Host side in the reference's language (C++): the UpdaterLidar/LidarHelper mirror over the C ABI
+(mins_b200/host/*.hpp). CPU only: the queueing policy of UpdaterLidar.cpp:50-160 is driven with a scripted state and a
+recording mock of the ABI; the link check proves the shim binds the real library's symbols."""
+import os
+import subprocess
+
+from conftest import ROOT
+
+HOST = os.path.join(ROOT, "mins_b200", "host")
+
+
+def run(name, *args):
+    return subprocess.run([os.path.join(HOST, name), *args], capture_output=True, text=True, check=True).stdout
+
+
+def test_shim_links_against_the_real_abi():
+    assert "ml_api bound: 16 entries" in run("shim_link_check")
+
+
+def test_queueing_policy_trace():
+    out = run("shim_policy_test")
+    lines = [l for l in out.splitlines() if not l.startswith("#")]
+    it = iter(lines)
+
+    def expect(prefix):
+        for l in it:
+            if l.startswith(prefix):
+                return l
+        raise AssertionError(f"missing trace line starting with {prefix!r}\n{out}")
+
+    expect("create h0")
+    assert "raw=1 new=0 used=0" in expect("stacks")                  # no clones: wait (UpdaterLidar.cpp:70-71)
+    # first usable scan initialises the map: ctor range filter -> downsample -> Build (UpdaterLidar.cpp:88-95)
+    assert "t_rel=0.000" in expect("h0 scan_upload") and "range=[1.00,100.0]" in lines[2]
+    expect("h0 scan_downsample leaf=0.30")
+    expect("h0 map_build_from_scan")
+    assert "raw=1 new=0 used=0" in expect("stacks")                  # 10.10 + 0.05 > newest clone: delayed (:78-82)
+    assert "raw=0 new=2 used=0" in expect("stacks")
+    # update(): exactly-at-clone scan has one pose block per time, calibration first in H_order (:181-214)
+    u1 = expect("h0 scan_update")
+    assert "hx=18 nI=1 nA=1 calib_col=0 cols=[6 | 12] at_clone=11" in u1 and "leaf=0.30" in u1 and "chi2=7.8147" in u1
+    assert "rows=18 hx=18" in expect("EKFUpdate")
+    u2 = expect("h0 scan_update")
+    assert "hx=36 nI=4 nA=1" in u2 and "cols=[6 12 18 24 | 30] at_clone=01" in u2 and "tx=0.120" in u2
+    expect("EKFUpdate")
+    # all updates first, then registrations in order with the transform each update used (:118-124, LidarHelper.cpp:196-207)
+    assert "tx=0.100" in expect("h0 scan_transform")
+    expect("h0 map_add_scan ds=1 size=0.30")
+    assert "tx=0.120" in expect("h0 scan_transform")
+    expect("h0 map_add_scan ds=1 size=0.30")
+    assert "raw=0 new=0 used=0" in expect("stacks")
+    assert "n_acp=20 n_rej=2 last_up=10.12 anchor=10.00" in expect("chi")
+    # re-anchor: old LiDAR frame -> newest clone's, decay options forwarded, last_up_time kept (LidarHelper.cpp:209-266)
+    assert "tx=-0.300 now=0.300 decay=30.0/100.0 ds=1" in expect("h0 map_reanchor")
+    assert "anchor=10.30 last_up=10.12" in expect("anchor")
+    # soft "no rows": scan stays in the new stack (UpdaterLidar.cpp:398-399, :115-117); later dropped by the window
+    expect("h0 scan_update")
+    assert "raw=0 new=1 used=0" in expect("stacks")
+    assert "raw=1 new=0 used=0" in expect("stacks")
+    # stale map (> 1 s without registration): re-initialised from the next usable scan (:91)
+    expect("h0 map_build_from_scan")
+    assert "anchor=11.50 last_up=11.50 t_hist=6" in expect("anchor")
+    assert out.count("map_reanchor") == 1
