@@ -167,7 +167,8 @@ def main():
     w = synth.make_workload(WORKLOAD, op=op, seed=64 + rank)
     n = int(w["n_rays"])
     hx = w["total_hx"]
-    m = LidarMap(max_scan_points=n, max_map_points=len(w["map"]) + 2 * n, device=local_rank)
+    m = LidarMap(max_scan_points=n, max_map_points=len(w["map"]) + 2 * n, device=local_rank,
+                 grid_cell=float(os.environ.get("MINS_GRID_CELL", "0")))  # 0 = library default (0.5 m); env = tuning experiments
     m.Build(w["map"])
     pinned = torch.empty((n, 4), dtype=torch.float32).pin_memory()
     pinned.copy_(torch.from_numpy(w["raw"]))
