@@ -1,0 +1,58 @@
+"""TEST INFRASTRUCTURE ONLY — CPU-oracle backend for the closed-loop harness (mins_b200/sim/updater.py).
+
+Same interface as mins_b200.sim.updater.GpuBackend, every step done by the CPU oracle (oracle/pyoracle.py): range filter,
+PCL-VoxelGrid restatement, fp32 transform, brute-force exact kNN, restated rows, stacking and the reference's Givens
+measurement compression (StateHelper.cpp:631-643), map insert and re-anchor. Used by tests/ to compare closed-loop
+trajectories (GPU updater vs CPU oracle updater in the same EKF). Never imported by the product package.
+"""
+import numpy as np
+
+from . import pyoracle as po
+
+
+class OracleBackend:
+    def __init__(self, threads=8):
+        self.map = np.zeros((0, 4), np.float32)
+        self.init = False
+        self.threads = threads
+
+    def close(self):
+        pass
+
+    def initialized(self):
+        return self.init
+
+    def _scan(self, scan, op, downsample):
+        sc = po.range_filter(scan["xyz"], scan["t_rel"], op.max_range, op.min_range)  # LiDARData ctor
+        if downsample and len(sc):
+            sc, _ = po.voxel_downsample(sc, op.raw_downsample_size)                   # LidarHelper::downsample
+        return sc
+
+    def build_map_from_scan(self, scan, op):
+        self.map = self._scan(scan, op, op.raw_do_downsample).copy()                  # init_map_local -> Build
+        self.init = len(self.map) > 0
+
+    def scan_update(self, scan, op, T_LtoM, consts, P):
+        from mins_b200 import capi
+        sc = self._scan(scan, op, op.raw_do_downsample)
+        if len(sc) == 0:
+            return capi.ML_SOFT_NO_ROWS, None, None, capi.ml_counters()
+        sm = po.transform_f32(sc, T_LtoM)                                             # transform_to_map
+        ref = po.scan_linsys(consts, P, self.map, sc, sm, threads=self.threads, want_compress=True)
+        if ref["cnt"].n_acc == 0:
+            return capi.ML_SOFT_NO_ROWS, None, None, ref["cnt"]
+        return 0, ref["Hc"], ref["rc"], ref["cnt"]
+
+    def register_scan(self, scan, op, T_LtoM):
+        sc = po.range_filter(scan["xyz"], scan["t_rel"], op.max_range, op.min_range)  # pointcloud_original
+        sm = po.transform_f32(sc, T_LtoM)
+        self.map = po.map_insert(self.map, sm, op.map_do_downsample, op.map_downsample_size)
+        return len(self.map)
+
+    def reanchor(self, T_old_to_new, now_minus_FT, op):
+        self.map = po.reanchor(self.map, T_old_to_new, now_minus_FT, op.map_decay_time, op.map_decay_dist, op.map_do_downsample,
+                               op.map_downsample_size)
+        return len(self.map)
+
+    def map_size(self):
+        return len(self.map)
