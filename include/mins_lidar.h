@@ -162,6 +162,26 @@ int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n);
 /* test hook: replace `pointcloud` (and `pointcloud_original`) verbatim, no filtering */
 int ml_scan_set(ml_handle *h, const float *xyzi, int n);
 
+/* ---- simulator LiDAR model: replaces Simulator::get_lidar_pointcloud ------------------- */
+/* The world of Simulator::load_plane_data (mins/src/sim/Simulator.cpp:990-1096): n_planes x 22 doubles
+ * [A B C D | top_left(3) | bottom_right(3) | V1 V2 V3 V4 (3 each)] with the plane equation and the edge directions of
+ * SimulationPlane (mins/src/sim/SimulationPlane.h:43-53,80-87). */
+int ml_sim_set_world(ml_handle *h, const double *planes, int n_planes);
+/* Ray bearings in the LiDAR frame, n_rays x 3 doubles, in the reference's emission order (for v_angle: for h_angle,
+ * Simulator.cpp:756-757,767-769). n_rays <= max_scan_points. */
+int ml_sim_set_rays(ml_handle *h, const double *dirs_L, int n_rays);
+/* Simulator::get_lidar_pointcloud (Simulator.cpp:742-815) for one sensor pose: p_LinG = p_IinG + R_GtoI^T p_LinI (:765),
+ * R_LtoG = R_GtoI^T R_ItoL^T (:769, row-major). Nearest hit over all planes (SimulationPlane.h:73-95), rays outside
+ * [min_range, max_range] dropped (:788), p = d * bearing cast to fp32 (:792-795), + noise * N(0,1) per axis in fp32
+ * (:798-803; noise <= 0: none). The reference draws from a sequential std::mt19937; here the normal deviates come from
+ * Philox-4x32-10 keyed by `seed` with the ray index as counter (order-independent). The scan stays on the device (it
+ * becomes the raw-scan buffer, see ml_sim_scan_device); xyz_out (stride 4, may be NULL) receives min(cap, n) points. */
+int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9], double min_range, double max_range, float noise,
+                   uint64_t seed, float *xyz_out, int cap, int *n_out);
+/* device pointer (stride 4) and size of the last ray-cast scan: pass them to ml_scan_upload / ml_scan_update, which use
+ * device-resident input in place. Valid until the next upload of a host scan. */
+int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n);
+
 /* ---- update: replaces the point loop + stacking + compression of UpdaterLidar::update ------------------- */
 /* LidarHelper::get_neighbors / KD_TREE::Nearest_Search (LidarHelper.cpp:268-289, ikd_Tree.cpp:358-389) for every
  * point of pointcloud_in_map. Exact k-NN on fp32 squared distance ((dx*dx + dy*dy) + dz*dz, no FMA), total order

@@ -6,6 +6,7 @@
 #include "prims.cuh"
 #include "rows.cuh"
 #include "scan.cuh"
+#include "sim.cuh"
 #include "update.cuh"
 
 #include <algorithm>
@@ -62,6 +63,11 @@ struct ml_handle {
   VoxGridDesc *d_vg = nullptr;
   float *d_knots = nullptr;
   size_t knots_cap = 0;
+  // simulator (ml_sim_*)
+  double *sim_planes = nullptr, *sim_dirs = nullptr, *sim_dist = nullptr;
+  int sim_n_planes = 0, sim_n_rays = 0;
+  int *sim_n_out = nullptr;
+  int sim_last_n = 0;
   // update
   QSlot *qtab = nullptr;
   int q_slots = 0;
@@ -287,7 +293,8 @@ void ml_destroy(ml_handle *h) {
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
-                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out};
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
+                 h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -648,6 +655,80 @@ int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n) 
   }
   if (n)
     *n = cnt;
+  return ML_OK;
+}
+
+// ---------------------------------------------------------------------------------------- simulator
+int ml_sim_set_world(ml_handle *h, const double *planes, int n_planes) {
+  if (!h || !planes || n_planes < 1)
+    return fail(h, ML_ERR_ARG, "ml_sim_set_world: bad argument");
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->sim_planes)
+    cudaFree(h->sim_planes);
+  h->sim_planes = nullptr;
+  const size_t bytes = sizeof(double) * SIM_PLANE_STRIDE * (size_t)n_planes;
+  CK(cudaMalloc(&h->sim_planes, bytes));
+  CK(cudaMemcpyAsync(h->sim_planes, planes, bytes, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->sim_n_planes = n_planes;
+  return ML_OK;
+}
+
+int ml_sim_set_rays(ml_handle *h, const double *dirs_L, int n_rays) {
+  if (!h || !dirs_L || n_rays < 1)
+    return fail(h, ML_ERR_ARG, "ml_sim_set_rays: bad argument");
+  if (n_rays > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_sim_set_rays: more rays than max_scan_points");
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->sim_dirs)
+    cudaFree(h->sim_dirs);
+  if (h->sim_dist)
+    cudaFree(h->sim_dist);
+  h->sim_dirs = h->sim_dist = nullptr;
+  CK(cudaMalloc(&h->sim_dirs, sizeof(double) * 3 * (size_t)n_rays));
+  CK(cudaMalloc(&h->sim_dist, sizeof(double) * (size_t)n_rays));
+  if (!h->sim_n_out)
+    CK(cudaMalloc(&h->sim_n_out, sizeof(int)));
+  CK(cudaMemcpyAsync(h->sim_dirs, dirs_L, sizeof(double) * 3 * (size_t)n_rays, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->sim_n_rays = n_rays;
+  return ML_OK;
+}
+
+int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9], double min_range, double max_range, float noise,
+                   uint64_t seed, float *xyz_out, int cap, int *n_out) {
+  if (!h || !p_LinG || !R_LtoG)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast: bad argument");
+  if (!h->sim_planes || !h->sim_dirs)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast: ml_sim_set_world / ml_sim_set_rays have not been called");
+  SimPose pose;
+  for (int a = 0; a < 3; a++)
+    pose.o[a] = p_LinG[a];
+  for (int a = 0; a < 9; a++)
+    pose.R[a] = R_LtoG[a];
+  const int n = h->sim_n_rays, tiles = cdiv(n, RF_TILE);
+  LAUNCH(k_ray_cast, tiles, SIM_BLOCK, h->sim_planes, h->sim_n_planes, h->sim_dirs, n, pose, min_range, max_range, h->sim_dist,
+         h->tile_sums);
+  LAUNCH(k_ray_emit, tiles, SIM_BLOCK, h->sim_dist, h->sim_dirs, n, h->tile_sums, noise, (uint32_t)(seed & 0xffffffffu),
+         (uint32_t)(seed >> 32), reinterpret_cast<float4 *>(h->d_raw), h->sim_n_out);
+  CK(cudaMemcpyAsync(&h->sim_last_n, h->sim_n_out, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaGetLastError());
+  const int m = std::min(cap, h->sim_last_n);
+  if (xyz_out && m > 0) {
+    CK(cudaMemcpyAsync(xyz_out, h->d_raw, sizeof(float) * 4 * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  if (n_out)
+    *n_out = h->sim_last_n;
+  return ML_OK;
+}
+
+int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n) {
+  if (!h || !xyz_dev || !n)
+    return fail(h, ML_ERR_ARG, "ml_sim_scan_device: bad argument");
+  *xyz_dev = h->d_raw;
+  *n = h->sim_last_n;
   return ML_OK;
 }
 

@@ -274,6 +274,31 @@ class LidarMap:
         self._ck(self.lib.ml_point_rows(self.h, rows, h.ctypes.data if want_h else None, n.value, C.byref(n)))
         return rows_to_numpy(rows, n.value), h
 
+    # ---- simulator LiDAR model (Simulator::get_lidar_pointcloud, Simulator.cpp:742-815) --------------
+    def sim_set_world(self, planes22):
+        a = _f64(planes22).reshape(-1, 22)
+        self._ck(self.lib.ml_sim_set_world(self.h, a.ctypes.data, len(a)))
+
+    def sim_set_rays(self, dirs_L):
+        a = _f64(dirs_L).reshape(-1, 3)
+        self._ck(self.lib.ml_sim_set_rays(self.h, a.ctypes.data, len(a)))
+        self._sim_rays = len(a)
+
+    def sim_raycast(self, p_LinG, R_LtoG, min_range, max_range, noise=0.0, seed=0, download=True):
+        """Returns the (n, 4) float32 scan (or just n when download=False; the scan then stays on the device only)."""
+        p, R = _f64(p_LinG).reshape(3), _f64(R_LtoG).reshape(3, 3)
+        n = C.c_int()
+        out = np.zeros((self._sim_rays, 4), np.float32) if download else None
+        self._ck(self.lib.ml_sim_raycast(self.h, p.ctypes.data, R.ctypes.data, min_range, max_range, noise, int(seed),
+                                         out.ctypes.data if download else None, self._sim_rays if download else 0, C.byref(n)))
+        return out[:n.value] if download else n.value
+
+    def sim_scan_device(self):
+        """(device pointer, n) of the last ray-cast scan, to pass as `xyz` of ml_scan_update (stride 4)."""
+        ptr, n = C.c_void_p(), C.c_int()
+        self._ck(self.lib.ml_sim_scan_device(self.h, C.byref(ptr), C.byref(n)))
+        return ptr.value, n.value
+
     def timing(self):
         ms = (C.c_float * 8)()
         self.lib.ml_last_timing(self.h, ms)

@@ -30,7 +30,7 @@ class PlaneWorld:
         self.bounds = (mnx, mxx, mny, mxy)
 
     def packed(self):
-        """(P, 24) float64 rows [A B C D | tl | br | V1 | V2 | V3 | V4]: the layout the CUDA ray-caster takes."""
+        """(P, 22) float64 rows [A B C D | tl | br | V1 | V2 | V3 | V4]: the layout the CUDA ray-caster takes."""
         return np.ascontiguousarray(np.concatenate([self.abcd, self.tl, self.br, self.V1, self.V2, self.V3, self.V4], 1))
 
     def raycast(self, origin, dirs):

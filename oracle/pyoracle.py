@@ -187,6 +187,63 @@ def deskew(xyzi, T_per_point):
     return a
 
 
+# ---- simulator LiDAR model (mins/src/sim/Simulator.cpp:742-815, SimulationPlane.h:43-95) restated in numpy -------------
+def philox4x32(counter0, key_lo, key_hi):
+    """Philox-4x32-10 (Salmon et al. 2011, the published algorithm) for counters (counter0[i], 0, 0, 0): (n, 4) uint32."""
+    c = np.zeros((len(counter0), 4), np.uint64)
+    c[:, 0] = np.asarray(counter0, np.uint64)
+    k0, k1 = np.uint64(key_lo), np.uint64(key_hi)
+    M0, M1, mask = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c[:, 0], M1 * c[:, 2]
+        hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & mask, p1 >> np.uint64(32), p1 & mask
+        c = np.stack([hi1 ^ c[:, 1] ^ k0, lo1, hi0 ^ c[:, 3] ^ k1, lo0], 1)
+        k0 = (k0 + np.uint64(0x9E3779B9)) & mask
+        k1 = (k1 + np.uint64(0xBB67AE85)) & mask
+    return c.astype(np.uint32)
+
+
+def sim_noise(ray_idx, seed):
+    """(n, 3) float32 N(0,1): Box-Muller on Philox words, u = ((x >> 8) + 1) * 2^-24 (the scheme of csrc/sim.cuh)."""
+    w = philox4x32(ray_idx, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    u = ((w >> np.uint32(8)).astype(np.float32) + np.float32(1.0)) * np.float32(5.9604644775390625e-08)
+    r0 = np.sqrt(np.float32(-2.0) * np.log(u[:, 0]))
+    r1 = np.sqrt(np.float32(-2.0) * np.log(u[:, 2]))
+    th0, th1 = np.float32(6.283185307179586) * u[:, 1], np.float32(6.283185307179586) * u[:, 3]
+    return np.stack([r0 * np.cos(th0), r0 * np.sin(th0), r1 * np.cos(th1)], 1).astype(np.float32)
+
+
+def sim_lidar_scan(corners, p_LinG, R_LtoG, dirs_L, min_range, max_range, noise=0.0, seed=0):
+    """Simulator::get_lidar_pointcloud for one pose. corners: (P, 4, 3) [top_left, top_right, bottom_left, bottom_right]
+    (Simulator.cpp:1053-1090). Literal SimulationPlane::calculate_intersection incl. the normalisations. Returns the (n, 4)
+    float32 scan, the kept ray indices and the hit distance of every ray."""
+    q = f64(corners).reshape(-1, 4, 3)
+    tl, tr, bl, br = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    N = np.cross(tr - tl, bl - tl)                      # SimulationPlane.h:46-49
+    D = -(N * tl).sum(1)                                # :53
+    unit = lambda v: v / np.linalg.norm(v, axis=-1, keepdims=True)
+    V1, V2, V3, V4 = unit(tr - tl), unit(bl - tl), unit(tr - br), unit(bl - br)
+    o = f64(p_LinG).reshape(3)
+    dl = f64(dirs_L).reshape(-1, 3)
+    dg = dl @ f64(R_LtoG).reshape(3, 3).T               # Simulator.cpp:769
+    best = np.full(len(dg), np.inf)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for s in range(0, len(dg), 4096):
+            d = dg[s:s + 4096]
+            t = -(N @ o + D)[None, :] / (d @ N.T)       # :76
+            pt = o[None, None, :] + t[:, :, None] * d[:, None, :]
+            U1, U2 = unit(pt - tl[None]), unit(pt - br[None])
+            ok = (t > 0) & ((U1 * V1[None]).sum(2) > 0) & ((U1 * V2[None]).sum(2) > 0) & ((U2 * V3[None]).sum(2) > 0) & \
+                 ((U2 * V4[None]).sum(2) > 0)           # :94
+            best[s:s + 4096] = np.where(ok, t, np.inf).min(1)
+    keep = np.where(~((best > max_range) | (best < min_range)))[0]  # Simulator.cpp:788
+    pts = np.zeros((len(keep), 4), np.float32)
+    pts[:, :3] = (best[keep, None] * dl[keep]).astype(np.float32)  # :792-795
+    if noise > 0:
+        pts[:, :3] = pts[:, :3] + np.float32(noise) * sim_noise(keep, seed)  # :798-803 (generator: see ml_sim_raycast)
+    return pts, keep, best
+
+
 class RefIkd:
     """The reference's KD_TREE<PointXYZI> (compiled unmodified)."""
 
