@@ -162,6 +162,42 @@ int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n);
 /* test hook: replace `pointcloud` (and `pointcloud_original`) verbatim, no filtering */
 int ml_scan_set(ml_handle *h, const float *xyzi, int n);
 
+/* ---- ICP pre-alignment: replaces the PointMatcher<float>::ICP block of LidarHelper::transform_to_map -------- */
+/* Parameters of the libpointmatcher chain LidarHelper.cpp:156-171 builds (ICP::setDefault, pointmatcher/ICP.cpp:100-113,
+ * with the reference filters replaced by MaxDist + SamplingSurfaceNormal). ml_icp_default_options fills the library
+ * defaults; the caller sets max_dist = map_icp_dist (OptionsLidar.h:97) and the seed. */
+typedef struct ml_icp_options {
+  double max_dist;       /* MaxDistDataPointsFilter maxDist: reference = map points with ||p|| < max_dist */
+  double read_prob;      /* RandomSamplingDataPointsFilter prob (0.75) */
+  double ref_ratio;      /* SamplingSurfaceNormalDataPointsFilter ratio (0.5) */
+  int normal_knn;        /* SamplingSurfaceNormalDataPointsFilter knn (7): support of the PCA normal */
+  double trim_ratio;     /* TrimmedDistOutlierFilter ratio (0.85) */
+  int max_iter;          /* CounterTransformationChecker maxIterationCount (40) */
+  double min_diff_rot;   /* DifferentialTransformationChecker minDiffRotErr (0.001 rad) */
+  double min_diff_trans; /* DifferentialTransformationChecker minDiffTransErr (0.001 m) */
+  int smooth_len;        /* DifferentialTransformationChecker smoothLength (3) */
+  double max_match_dist; /* bound of the 1-NN matcher [m]. The reference's KDTreeMatcher is unbounded (maxDist = inf) and
+                            leaves far matches to the trimmed filter; a bound keeps the grid walk local. Reading points
+                            without a reference point within the bound count as unmatched (weight 0). Default 2. */
+  double normal_radius;  /* neighbours for the normal are searched within this radius [m]; default 2 */
+  uint64_t seed;         /* the reference seeds its samplers from std::random_device / std::rand (non-deterministic) */
+} ml_icp_options;
+typedef struct ml_icp_result {
+  float T_LtoM[16];      /* what transform_to_map stores in lidar->T_LtoM: T_icp on success, else the initial guess */
+  float T_icp[16];       /* raw ICP output */
+  int success;           /* lidar->icp_success: !maxNumIterationsReached && ||trans(T_icp * T_init^-1)|| <= 1 (LidarHelper.cpp:177) */
+  int iterations;
+  int max_iter_reached;
+  int n_reading, n_reference; /* points after the reading / reference filters */
+  int n_matched, n_used;      /* last iteration: matches within the bound, matches with weight 1 */
+  double mean_sq_err;         /* last iteration: mean squared point-to-plane error over the used matches, before its update */
+} ml_icp_result;
+void ml_icp_default_options(ml_icp_options *o);
+/* PointMatcher<float>::ICP::compute(new_points, map_points, T_LtoM) (LidarHelper.cpp:173-184) on the current scan cloud
+ * (`pointcloud`, after ml_scan_downsample) against the current map. The caller then passes res->T_LtoM to
+ * ml_scan_transform, like LidarHelper.cpp:192. Returns ML_SOFT_NO_ROWS when either cloud is (nearly) empty. */
+int ml_scan_icp(ml_handle *h, const float T_init[16], const ml_icp_options *o, ml_icp_result *res);
+
 /* ---- simulator LiDAR model: replaces Simulator::get_lidar_pointcloud ------------------- */
 /* The world of Simulator::load_plane_data (mins/src/sim/Simulator.cpp:990-1096): n_planes x 22 doubles
  * [A B C D | top_left(3) | bottom_right(3) | V1 V2 V3 V4 (3 each)] with the plane equation and the edge directions of
@@ -211,7 +247,8 @@ int ml_info_to_sqrt(const double *HtH, const double *Htr, int total_hx, double *
  * [0] upload+range filter (+ transform when not down-sampling), [1] downsample, [2] transform, [3] query binning, [4] knn,
  * [5] rows + reduction + finalize (one fused kernel), [6] D2H of the result block, [7] total */
 int ml_last_timing(ml_handle *h, float ms[8]);
-/* switch the per-stage CUDA-event timers on/off (default on) */
+/* CUDA-event timers: 0 = off, 1 = per-stage (default; diagnostic - the event records between kernels serialise the
+ * programmatically dependent launches of the pipeline), 2 = total only ([7]; the other entries read 0) */
 int ml_set_timing(ml_handle *h, int on);
 /* sizeof of {ml_scan_consts, ml_point_row, ml_counters, ml_config} as compiled, for FFI layout checks */
 void ml_abi_sizes(int out[4]);

@@ -60,6 +60,18 @@ class ml_point_row(C.Structure):
                 ("chi2", C.c_double), ("w", C.c_double), ("vr", C.c_double), ("raw_n", C.c_double)]
 
 
+class ml_icp_options(C.Structure):
+    _fields_ = [("max_dist", C.c_double), ("read_prob", C.c_double), ("ref_ratio", C.c_double), ("normal_knn", C.c_int),
+                ("trim_ratio", C.c_double), ("max_iter", C.c_int), ("min_diff_rot", C.c_double), ("min_diff_trans", C.c_double),
+                ("smooth_len", C.c_int), ("max_match_dist", C.c_double), ("normal_radius", C.c_double), ("seed", C.c_uint64)]
+
+
+class ml_icp_result(C.Structure):
+    _fields_ = [("T_LtoM", C.c_float * 16), ("T_icp", C.c_float * 16), ("success", C.c_int), ("iterations", C.c_int),
+                ("max_iter_reached", C.c_int), ("n_reading", C.c_int), ("n_reference", C.c_int), ("n_matched", C.c_int),
+                ("n_used", C.c_int), ("mean_sq_err", C.c_double)]
+
+
 # every symbol include/mins_lidar.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
     "ml_create", "ml_destroy", "ml_last_error", "ml_global_error", "ml_map_reset", "ml_map_initialized", "ml_map_build",
@@ -67,6 +79,7 @@ SYMBOLS = [
     "ml_scan_upload", "ml_scan_deskew", "ml_scan_downsample", "ml_scan_transform", "ml_scan_download", "ml_scan_set",
     "ml_knn", "ml_linsys", "ml_scan_update", "ml_point_rows", "ml_info_to_sqrt", "ml_last_timing", "ml_set_timing",
     "ml_abi_sizes", "ml_launch_count", "ml_sim_set_world", "ml_sim_set_rays", "ml_sim_raycast", "ml_sim_scan_device",
+    "ml_icp_default_options", "ml_scan_icp",
 ]
 
 _lib = None
@@ -116,6 +129,9 @@ def load():
     lib.ml_abi_sizes.restype = None
     lib.ml_launch_count.argtypes = [vp]
     lib.ml_launch_count.restype = C.c_longlong
+    lib.ml_icp_default_options.argtypes = [C.POINTER(ml_icp_options)]
+    lib.ml_icp_default_options.restype = None
+    lib.ml_scan_icp.argtypes = [vp, vp, C.POINTER(ml_icp_options), C.POINTER(ml_icp_result)]
     lib.ml_sim_set_world.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_set_rays.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_raycast.argtypes = [vp, vp, vp, C.c_double, C.c_double, C.c_float, C.c_uint64, vp, C.c_int, ip]

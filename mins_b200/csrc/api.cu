@@ -8,13 +8,16 @@
 #include "scan.cuh"
 #include "sim.cuh"
 #include "update.cuh"
+#include "icp.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
+#include <utility>
 #include <vector>
 
 using namespace ml;
@@ -68,6 +71,14 @@ struct ml_handle {
   int sim_n_planes = 0, sim_n_rays = 0;
   int *sim_n_out = nullptr;
   int sim_last_n = 0;
+  // ICP pre-alignment (ml_scan_icp), allocated on first use
+  uint8_t *icp_keep = nullptr;
+  float4 *icp_normals = nullptr, *icp_cell_pts = nullptr, *icp_read = nullptr, *icp_q = nullptr;
+  IcpState *d_icp = nullptr;
+  ScanState *d_ist = nullptr;
+  double *icp_parts = nullptr;
+  IcpHostOut *h_icp = nullptr;
+  int icp_knn_calls = 0;
   // update
   QSlot *qtab = nullptr;
   int q_slots = 0;
@@ -95,7 +106,8 @@ struct ml_handle {
   int rows_k = 0;
   // timing
   cudaEvent_t ev[10];
-  bool timing = true;
+  int timing = 1; // 0 off, 1 per-stage events (diagnostic: event records between kernels defeat the launch overlap), 2 total only
+  bool use_pdl = true;
   float last_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
@@ -118,6 +130,24 @@ struct ml_handle {
     kern<<<(grid), (block), 0, h->stream>>>(__VA_ARGS__);                                                              \
     h->launches++;                                                                                                     \
   } while (0)
+
+// launch on the handle's stream with programmatic stream serialization (see pdl_enter in common.cuh): the kernel may be
+// scheduled while its predecessor drains; it calls griddepcontrol.wait before touching memory.
+template <typename... KArgs, typename... Args>
+static inline void launch_pdl(ml_handle *h, void (*kern)(KArgs...), int grid, int block, size_t smem, Args &&...args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid), cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = h->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = h->use_pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+  h->launches++;
+}
+#define LAUNCHP(kern, grid, block, ...) launch_pdl(h, kern, (grid), (block), 0, __VA_ARGS__)
 
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline int *st_field(ml_handle *h, size_t off) { return (int *)((char *)h->d_st + off); }
@@ -207,6 +237,8 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   h->cap_cells = cfg->max_grid_cells > 0 ? cfg->max_grid_cells : (1 << 24);
   h->cap_all = h->cap_map + h->cap_scan;
   h->grid_cell = cfg->grid_cell > 0 ? (double)cfg->grid_cell : 0.5;
+  if (const char *e = getenv("MINS_NO_PDL")) // A/B switch for profiling
+    h->use_pdl = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&h->ev_prep, cudaEventDisableTiming));
@@ -294,7 +326,8 @@ void ml_destroy(ml_handle *h) {
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
-                 h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out};
+                 h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -304,6 +337,8 @@ void ml_destroy(ml_handle *h) {
     cudaFreeHost(h->h_in);
   if (h->h_out)
     cudaFreeHost(h->h_out);
+  if (h->h_icp)
+    cudaFreeHost(h->h_icp);
   for (auto &e : h->ev)
     cudaEventDestroy(e);
   cudaEventDestroy(h->ev_prep);
@@ -535,12 +570,12 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   const int tiles = cdiv(n, RF_TILE);
   float4 *in_map = T_LtoM ? h->scan_map : nullptr;
   if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0) {
-    LAUNCH(k_range_count<true>, tiles, RF_BLOCK, raw_src, stride, n, (double)rmin, (double)rmax, h->d_st, h->tile_sums);
-    LAUNCH(k_range_compact<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->tile_sums, h->d_st,
+    LAUNCHP(k_range_count<true>, tiles, RF_BLOCK, raw_src, stride, n, (double)rmin, (double)rmax, h->d_st, h->tile_sums);
+    LAUNCHP(k_range_compact<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->tile_sums, h->d_st,
            h->scan_pts, h->scan_orig, h->T_LtoM, in_map);
   } else {
-    LAUNCH(k_range_count<false>, tiles, RF_BLOCK, raw_src, stride, n, (double)rmin, (double)rmax, h->d_st, h->tile_sums);
-    LAUNCH(k_range_compact<false>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->tile_sums, h->d_st,
+    LAUNCHP(k_range_count<false>, tiles, RF_BLOCK, raw_src, stride, n, (double)rmin, (double)rmax, h->d_st, h->tile_sums);
+    LAUNCHP(k_range_compact<false>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->tile_sums, h->d_st,
            h->scan_pts, h->scan_orig, h->T_LtoM, in_map);
   }
   return check_launch(h);
@@ -737,7 +772,7 @@ int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n) {
 
 template <int K> static void launch_knn(ml_handle *h, float max_d2, int ph) {
   const int blocks = h->n_sm * 8;
-  LAUNCH(k_knn<K>, blocks, KNN_WARPS * 32, h->units, h->d_st, ph, h->q_sorted, h->d_grid, h->cell_start, h->cell_pts, max_d2,
+  LAUNCHP(k_knn<K>, blocks, KNN_WARPS * 32, h->units, h->d_st, ph, h->q_sorted, h->d_grid, h->cell_start, h->cell_pts, max_d2,
          h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots);
 }
 // fused rows + reduction + finalize; rows_out != nullptr only for the parity export
@@ -748,9 +783,9 @@ template <int K> static int launch_rows(ml_handle *h, PointRow *rows_out) {
     attr_set = true;
   }
   const int nb = std::max(1, std::min(h->n_sm, cdiv(std::max(h->n_raw, 1), 256)));
-  k_rows_reduce<K><<<nb, RR_BLOCK, RR_SMEM, h->stream>>>(h->d_st, h->scan_pts, h->map_pts[h->cur], h->knn_idx, h->knn_ok, h->d_consts,
-                                                        rows_out, h->parts, h->ticket, h->d_out);
-  h->launches++;
+  launch_pdl(h, k_rows_reduce<K>, nb, RR_BLOCK, RR_SMEM, (const ScanState *)h->d_st, (const float4 *)h->scan_pts,
+             (const float4 *)h->map_pts[h->cur], (const int32_t *)h->knn_idx, (const uint8_t *)h->knn_ok, (const DevConsts *)h->d_consts,
+             rows_out, h->parts, h->ticket, h->h_out /* pinned host memory, written by the last CTA */);
   return ML_OK;
 }
 static int launch_rows_k(ml_handle *h, int k, PointRow *rows_out) {
@@ -779,12 +814,12 @@ static int knn_async(ml_handle *h, int k, float max_d2) {
   const uint32_t mask = (uint32_t)h->q_slots - 1u;
   const int ph = h->knn_calls & 1;
   h->knn_calls++;
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[3], h->stream);
-  LAUNCH(k_query_bin, cdiv(n, 256), 256, h->scan_map, h->d_st, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
-  LAUNCH(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, ph, h->units, h->units_cap);
-  LAUNCH(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
-  if (h->timing)
+  LAUNCHP(k_query_bin, cdiv(n, 256), 256, h->scan_map, h->d_st, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+  LAUNCHP(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, ph, h->units, h->units_cap);
+  LAUNCHP(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
+  if (h->timing == 1)
     cudaEventRecord(h->ev[4], h->stream);
   switch (k) {
   case 1: launch_knn<1>(h, max_d2, ph); break;
@@ -798,7 +833,7 @@ static int knn_async(ml_handle *h, int k, float max_d2) {
   case 9: launch_knn<9>(h, max_d2, ph); break;
   default: launch_knn<10>(h, max_d2, ph); break;
   }
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[5], h->stream);
   return check_launch(h);
 }
@@ -851,8 +886,8 @@ static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) 
   const int hx = c->total_hx;
   h->h_in->c = *c;
   memcpy(h->h_in->P, P, sizeof(double) * (size_t)hx * hx);
-  CK(cudaEventRecord(h->ev_fork, h->stream)); // the previous scan's rows kernel may still be reading d_consts
-  CK(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+  // no fork event: every entry point that launches the rows kernel (the only reader of d_consts) synchronises the main
+  // stream before it returns, so d_consts is idle here; an event record here would also split the kernel chain
   CK(cudaMemcpyAsync(&h->d_consts->c, &h->h_in->c, sizeof(ml_scan_consts), cudaMemcpyHostToDevice, h->stream2));
   CK(cudaMemcpyAsync(h->d_P, h->h_in->P, sizeof(double) * (size_t)hx * hx, cudaMemcpyHostToDevice, h->stream2));
   k_prep_consts<<<1, 1024, 0, h->stream2>>>(h->d_consts, h->d_P);
@@ -864,19 +899,21 @@ static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) 
 // everything after the transform; one synchronisation at the end. consts_async must have been issued.
 static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *HtH, double *Htr, ml_counters *cnt) {
   const int hx = c->total_hx, k = c->map_ngbr_num;
+  // join the constants' stream BEFORE the binning kernels (k_prep_consts is long done by then): bin -> alloc -> scatter ->
+  // knn -> rows then form one uninterrupted chain of programmatically dependent launches
+  CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   int rc = knn_async(h, k, (float)c->map_ngbr_max_d);
   if (rc) {
     cudaStreamSynchronize(h->stream2);
     return rc;
   }
-  CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   rc = launch_rows_k(h, k, nullptr);
   if (rc)
     return rc;
   h->rows_exported = false;
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[6], h->stream);
-  CK(cudaMemcpyAsync(h->h_out, h->d_out, sizeof(LinsysOut), cudaMemcpyDeviceToHost, h->stream));
+  // no D2H copy: the kernel's last CTA wrote the result block straight into the pinned host mirror
   if (h->timing)
     cudaEventRecord(h->ev[8], h->stream);
   CK(cudaStreamSynchronize(h->stream));
@@ -889,7 +926,7 @@ static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *
     memcpy(Htr, h->h_out->Htr, sizeof(double) * (size_t)hx);
   if (cnt)
     *cnt = h->h_out->cnt;
-  if (h->timing) {
+  if (h->timing == 1) {
     auto el = [&](int a, int b) {
       float ms = 0.f;
       if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
@@ -950,7 +987,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
   rc = consts_async(h, c, P);
   if (rc)
     return rc;
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[1], h->stream);
   if (ds) {
     rc = scan_downsample_async(h, leaf);
@@ -959,7 +996,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
       return rc;
     }
   }
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[2], h->stream);
   if (ds) {
     rc = scan_transform_async(h, T_LtoM);
@@ -968,7 +1005,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
       return rc;
     }
   }
-  if (h->timing)
+  if (h->timing == 1)
     cudaEventRecord(h->ev[9], h->stream);
   rc = linsys_async_and_wait(h, c, HtH, Htr, cnt);
   if (h->timing && rc >= 0) {
@@ -980,9 +1017,14 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
       }
       return ms;
     };
-    h->last_ms[0] = el(0, 1);
-    h->last_ms[1] = el(1, 2);
-    h->last_ms[2] = el(2, 9);
+    if (h->timing == 1) {
+      h->last_ms[0] = el(0, 1);
+      h->last_ms[1] = el(1, 2);
+      h->last_ms[2] = el(2, 9);
+    } else {
+      for (int q = 0; q < 7; q++)
+        h->last_ms[q] = 0.f;
+    }
     h->last_ms[7] = el(0, 8);
   }
   return rc;
@@ -1045,7 +1087,7 @@ void ml_abi_sizes(int out[4]) {
 int ml_set_timing(ml_handle *h, int on) {
   if (!h)
     return ML_ERR_ARG;
-  h->timing = on != 0;
+  h->timing = on < 0 ? 0 : (on > 2 ? 2 : on);
   return ML_OK;
 }
 
@@ -1113,3 +1155,5 @@ int ml_info_to_sqrt(const double *HtH, const double *Htr, int n, double *Rc, dou
 }
 
 } // extern "C"
+
+#include "icp_host.inl"

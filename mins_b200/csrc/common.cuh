@@ -22,6 +22,20 @@ __device__ __forceinline__ float norm3_ref(float x, float y, float z) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (sm_90+): the kernels of the per-scan pipeline are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, call pdl_launch() first thing (the next kernel's CTAs may become
+// resident as soon as every CTA of this one has started) and pdl_wait() before touching global memory (returns when the
+// preceding kernel has completed and flushed). Only launch latency and CTA scheduling overlap; the data dependencies are
+// those of plain stream order. Without the launch attribute both instructions are no-ops.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+  pdl_launch();
+  pdl_wait();
+}
+
+// ------------------------------------------------------------------------------------------------
 // Dense kNN grid over the map's bounding box. Cell id = (z*dimy + y)*dimx + x (x fastest, so the cells
 // of one x-run are one contiguous range of cell_pts).
 // ------------------------------------------------------------------------------------------------

@@ -424,6 +424,7 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
   __shared__ int scnt[5];
   __shared__ unsigned int s_last;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  pdl_enter();
   {
     const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
     const int *src = reinterpret_cast<const int *>(&dc->c);
@@ -642,7 +643,9 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     GT[r * ML_MAX_HX + j] = s;
   }
   __syncthreads();
-  // upper triangle computed once and mirrored: HtH is exactly symmetric
+  // upper triangle computed once and mirrored: HtH is exactly symmetric. Staged in shared memory and written out in
+  // full 128-byte lines: `out` is pinned HOST memory (the result crosses PCIe as ~150 posted writes, no D2H copy node).
+  double *Hs = GT + ML_G * ML_MAX_HX; // [hx][hx] + [hx]
   for (int idx = t; idx < hx * hx; idx += RR_BLOCK) {
     const int a = idx / hx, b2 = idx - a * hx;
     if (a > b2)
@@ -651,16 +654,22 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
       s += sT[l * ML_MAX_HX + a] * GT[l * ML_MAX_HX + b2];
-    out->HtH[idx] = s;
-    out->HtH[b2 * hx + a] = s;
+    Hs[idx] = s;
+    Hs[b2 * hx + a] = s;
   }
   for (int a = t; a < hx; a += RR_BLOCK) {
     double s = 0.0;
 #pragma unroll
     for (int l = 0; l < ML_G; l++)
       s += sT[l * ML_MAX_HX + a] * bv[l];
-    out->Htr[a] = s;
+    Hs[hx * hx + a] = s;
   }
+  __syncthreads();
+  for (int idx = t; idx < hx * hx; idx += RR_BLOCK)
+    out->HtH[idx] = Hs[idx];
+  for (int a = t; a < hx; a += RR_BLOCK)
+    out->Htr[a] = Hs[hx * hx + a];
+  __threadfence_system();
 }
 
 // parity export: h = T^T g for every point (n x hx)

@@ -43,6 +43,7 @@ template <bool VEC4>
 __global__ void __launch_bounds__(RF_BLOCK) k_range_count(const float *__restrict__ raw, int stride, int n, double rmin, double rmax,
                                                           ScanState *__restrict__ st, uint32_t *__restrict__ tile_sums) {
   __shared__ uint32_t wsum[RF_BLOCK / 32];
+  pdl_enter();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int wbase = blockIdx.x * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
   uint32_t cnt = 0;
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(RF_BLOCK)
                     float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map /* nullptr: transform later */) {
   __shared__ uint32_t wsum[RF_BLOCK / 32];
   __shared__ uint32_t tile_prefix;
+  pdl_enter();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (wid == 0) { // counts of the tiles before this one, fixed order
     uint32_t s = 0;

@@ -30,8 +30,11 @@ __device__ __forceinline__ void cell_unkey(unsigned long long k, int *cx, int *c
 __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
                                                   const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
                                                   uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= st->n_scan)
+  const bool live = i < st->n_scan;
+  const unsigned act = __ballot_sync(0xffffffffu, live);
+  if (!live)
     return;
   const double ox = gd->ox, oy = gd->oy, oz = gd->oz, inv = gd->inv_cell;
   float4 q = q_in_map[i];
@@ -42,21 +45,33 @@ __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_
   int cy = max(-lim, min(lim, cell_coord((double)q.y, oy, inv)));
   int cz = max(-lim, min(lim, cell_coord((double)q.z, oz, inv)));
   unsigned long long key = cell_key(cx, cy, cz);
-  uint32_t s = hash64(key) & mask;
-  for (;;) {
-    unsigned long long prev = atomicCAS(&tab[s].key, 0ull, key);
-    if (prev == 0ull || prev == key)
-      break;
-    s = (s + 1) & mask;
+  // warp-aggregated: consecutive rays mostly share a cell, so one lane per distinct key probes the table and reserves
+  // the ranks of all its peers with a single atomicAdd
+  const int lane = threadIdx.x & 31;
+  const unsigned peers = __match_any_sync(act, key);
+  const int leader = __ffs(peers) - 1;
+  uint32_t s = 0, base = 0;
+  if (lane == leader) {
+    s = hash64(key) & mask;
+    for (;;) {
+      unsigned long long prev = atomicCAS(&tab[s].key, 0ull, key);
+      if (prev == 0ull || prev == key)
+        break;
+      s = (s + 1) & mask;
+    }
+    base = atomicAdd(&tab[s].cnt, (uint32_t)__popc(peers));
   }
+  s = __shfl_sync(peers, s, leader);
+  base = __shfl_sync(peers, base, leader);
   q_slot[i] = s;
-  q_rank[i] = atomicAdd(&tab[s].cnt, 1u);
+  q_rank[i] = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
 }
 
 // every occupied slot gets a contiguous range of the sorted query array and ceil(cnt/32) warp units;
 // one atomic pair per block (block-level aggregation)
 __global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int nslots, ScanState *__restrict__ st, int ph,
                                                    KnnUnit *__restrict__ units, int units_cap) {
+  pdl_enter();
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t cnt = (s < nslots) ? tab[s].cnt : 0u;
   uint32_t nu = (cnt + 31u) >> 5;
@@ -89,6 +104,7 @@ __global__ void __launch_bounds__(256) k_unit_alloc(QSlot *__restrict__ tab, int
 __global__ void __launch_bounds__(256) k_query_scatter(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
                                                       const QSlot *__restrict__ tab, const uint32_t *__restrict__ q_slot,
                                                       const uint32_t *__restrict__ q_rank, float4 *__restrict__ q_sorted) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= st->n_scan)
     return;
@@ -139,11 +155,118 @@ template <int K> struct TopK {
 
 constexpr int KNN_WARPS = 4;
 
+// The cube walk of one unit (all 32 lanes of a warp call it together). `q` = this lane's query, `active` = lane owns one.
+// R = last level to visit (ceil(sqrt(max_d2) / cell)). Leaves the lane's k best in `best`.
+template <int K>
+__device__ __forceinline__ void knn_walk(const KnnUnit &un, const float4 q, const bool active, const GridDesc &g, const int R,
+                                         const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, TopK<K> &best) {
+  const int lane = threadIdx.x & 31;
+  // distance (in cells) from the query to the nearest face of its own cell
+  double fx = ((double)q.x - g.ox) * g.inv_cell - (double)un.cx;
+  double fy = ((double)q.y - g.oy) * g.inv_cell - (double)un.cy;
+  double fz = ((double)q.z - g.oz) * g.inv_cell - (double)un.cz;
+  double fmn = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
+  fmn = fmax(0.0, fmn);
+  best.init();
+
+  // levels below s_lo cannot touch the grid (Chebyshev distance from the unit's cell to the grid box); at s_hi the
+  // cube covers the whole grid, so every map point has been visited and the search is exact whatever max_d2 is
+  const int ox_ = max(max(-un.cx, un.cx - (g.dimx - 1)), 0), oy_ = max(max(-un.cy, un.cy - (g.dimy - 1)), 0),
+            oz_ = max(max(-un.cz, un.cz - (g.dimz - 1)), 0);
+  const int s_lo = max(1, max(ox_, max(oy_, oz_)));
+  const int s_hi = min(R, max(max(max(un.cx, g.dimx - 1 - un.cx), max(un.cy, g.dimy - 1 - un.cy)), max(un.cz, g.dimz - 1 - un.cz)));
+  // level 0: the unit's own cell first. Its points are the likeliest neighbours of all 32 queries, so the k-th best of
+  // every lane is tight before the 26 surrounding cells are scanned and most of their candidates fail the first compare
+  // of offer() for the whole warp (the insertion network then does not issue at all).
+  const bool own_in_grid = un.cx >= 0 && un.cx < g.dimx && un.cy >= 0 && un.cy < g.dimy && un.cz >= 0 && un.cz < g.dimz;
+  if (own_in_grid) {
+    const int c0 = (un.cz * g.dimy + un.cy) * g.dimx + un.cx;
+    const uint32_t beg = cell_start[c0], end = cell_start[c0 + 1];
+    for (uint32_t j = beg; j < end; j++) {
+      const float4 c = __ldg(&cell_pts[j]);
+      best.offer(dist2_ref(c.x, c.y, c.z, q.x, q.y, q.z), __float_as_int(c.w));
+    }
+  }
+  for (int s = s_lo; s <= s_hi; s++) {
+    // rows (y, z) of the cube clipped to the grid
+    const int y0 = max(un.cy - s, 0), y1 = min(un.cy + s, g.dimy - 1);
+    const int z0 = max(un.cz - s, 0), z1 = min(un.cz + s, g.dimz - 1);
+    const int nz = z1 - z0 + 1;
+    const int nrows = (y1 >= y0 && nz > 0) ? (y1 - y0 + 1) * nz : 0;
+    for (int rb = 0; rb < nrows; rb += 32) {
+      // lane-parallel row set-up: row t -> (y, z); segment A and (for inner rows of levels > s_lo) segment B
+      const int t = rb + lane;
+      uint32_t begA = 0, endA = 0, begB = 0, endB = 0;
+      if (t < nrows) {
+        const int y = y0 + t / nz, z = z0 + (t - (t / nz) * nz);
+        const int dy = y - un.cy, dz = z - un.cz;
+        const int rowbase = (z * g.dimy + y) * g.dimx;
+        const bool outer = (s == s_lo) || (abs(dy) == s) || (abs(dz) == s);
+        if (outer && own_in_grid && dy == 0 && dz == 0) {
+          // the row through the unit's own cell (only at the first level): skip the cell done at level 0
+          const int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
+          begA = cell_start[rowbase + x0];
+          endA = cell_start[rowbase + un.cx];
+          begB = cell_start[rowbase + un.cx + 1];
+          endB = cell_start[rowbase + x1 + 1];
+        } else if (outer) {
+          int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
+          if (x0 <= x1) {
+            begA = cell_start[rowbase + x0];
+            endA = cell_start[rowbase + x1 + 1];
+          }
+        } else {
+          int xa = un.cx - s, xb = un.cx + s;
+          if (xa >= 0 && xa < g.dimx) {
+            begA = cell_start[rowbase + xa];
+            endA = cell_start[rowbase + xa + 1];
+          }
+          if (xb >= 0 && xb < g.dimx) {
+            begB = cell_start[rowbase + xb];
+            endB = cell_start[rowbase + xb + 1];
+          }
+        }
+      }
+      // which lanes hold non-empty segments
+      unsigned mA = __ballot_sync(0xffffffffu, endA > begA);
+      unsigned mB = __ballot_sync(0xffffffffu, endB > begB);
+      for (int pass = 0; pass < 2; pass++) {
+        unsigned m = pass ? mB : mA;
+        while (m) {
+          const int src = __ffs(m) - 1;
+          m &= m - 1;
+          const uint32_t beg = __shfl_sync(0xffffffffu, pass ? begB : begA, src);
+          const uint32_t end = __shfl_sync(0xffffffffu, pass ? endB : endA, src);
+          uint32_t j = beg;
+          for (; j + 4 <= end; j += 4) {
+            const float4 c0 = __ldg(&cell_pts[j]), c1 = __ldg(&cell_pts[j + 1]), c2 = __ldg(&cell_pts[j + 2]),
+                         c3 = __ldg(&cell_pts[j + 3]);
+            best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+            best.offer(dist2_ref(c1.x, c1.y, c1.z, q.x, q.y, q.z), __float_as_int(c1.w));
+            best.offer(dist2_ref(c2.x, c2.y, c2.z, q.x, q.y, q.z), __float_as_int(c2.w));
+            best.offer(dist2_ref(c3.x, c3.y, c3.z, q.x, q.y, q.z), __float_as_int(c3.w));
+          }
+          for (; j < end; j++) {
+            const float4 c0 = __ldg(&cell_pts[j]);
+            best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+          }
+        }
+      }
+    }
+    // completeness test for this level
+    const double gs = (fmn + (double)s) * g.cell;
+    const bool done = !active || ((double)best.d[K - 1] < gs * gs * (1.0 - 1e-6));
+    if (__all_sync(0xffffffffu, done))
+      break;
+  }
+}
+
 template <int K>
 __global__ void __launch_bounds__(KNN_WARPS * 32)
     k_knn(const KnnUnit *__restrict__ units, ScanState *__restrict__ st, int ph, const float4 *__restrict__ q_sorted,
           const GridDesc *__restrict__ gd, const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
           int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok, QSlot *__restrict__ qtab, int q_slots) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -166,88 +289,8 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
     const KnnUnit un = units[u];
     const bool active = lane < un.cnt;
     const float4 q = q_sorted[un.qbase + (active ? lane : 0)];
-    // distance (in cells) from the query to the nearest face of its own cell
-    double fx = ((double)q.x - g.ox) * g.inv_cell - (double)un.cx;
-    double fy = ((double)q.y - g.oy) * g.inv_cell - (double)un.cy;
-    double fz = ((double)q.z - g.oz) * g.inv_cell - (double)un.cz;
-    double fmn = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
-    fmn = fmax(0.0, fmn);
     TopK<K> best;
-    best.init();
-
-    // levels below s_lo cannot touch the grid (Chebyshev distance from the unit's cell to the grid box); at s_hi the
-    // cube covers the whole grid, so every map point has been visited and the search is exact whatever max_d2 is
-    const int ox_ = max(max(-un.cx, un.cx - (g.dimx - 1)), 0), oy_ = max(max(-un.cy, un.cy - (g.dimy - 1)), 0),
-              oz_ = max(max(-un.cz, un.cz - (g.dimz - 1)), 0);
-    const int s_lo = max(1, max(ox_, max(oy_, oz_)));
-    const int s_hi = min(R, max(max(max(un.cx, g.dimx - 1 - un.cx), max(un.cy, g.dimy - 1 - un.cy)), max(un.cz, g.dimz - 1 - un.cz)));
-    for (int s = s_lo; s <= s_hi; s++) {
-      // rows (y, z) of the cube clipped to the grid
-      const int y0 = max(un.cy - s, 0), y1 = min(un.cy + s, g.dimy - 1);
-      const int z0 = max(un.cz - s, 0), z1 = min(un.cz + s, g.dimz - 1);
-      const int nz = z1 - z0 + 1;
-      const int nrows = (y1 >= y0 && nz > 0) ? (y1 - y0 + 1) * nz : 0;
-      for (int rb = 0; rb < nrows; rb += 32) {
-        // lane-parallel row set-up: row t -> (y, z); segment A and (for inner rows of levels > s_lo) segment B
-        const int t = rb + lane;
-        uint32_t begA = 0, endA = 0, begB = 0, endB = 0;
-        if (t < nrows) {
-          const int y = y0 + t / nz, z = z0 + (t - (t / nz) * nz);
-          const int dy = y - un.cy, dz = z - un.cz;
-          {
-            const int rowbase = (z * g.dimy + y) * g.dimx;
-            const bool outer = (s == s_lo) || (abs(dy) == s) || (abs(dz) == s);
-            if (outer) {
-              int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
-              if (x0 <= x1) {
-                begA = cell_start[rowbase + x0];
-                endA = cell_start[rowbase + x1 + 1];
-              }
-            } else {
-              int xa = un.cx - s, xb = un.cx + s;
-              if (xa >= 0 && xa < g.dimx) {
-                begA = cell_start[rowbase + xa];
-                endA = cell_start[rowbase + xa + 1];
-              }
-              if (xb >= 0 && xb < g.dimx) {
-                begB = cell_start[rowbase + xb];
-                endB = cell_start[rowbase + xb + 1];
-              }
-            }
-          }
-        }
-        // which lanes hold non-empty segments
-        unsigned mA = __ballot_sync(0xffffffffu, endA > begA);
-        unsigned mB = __ballot_sync(0xffffffffu, endB > begB);
-        for (int pass = 0; pass < 2; pass++) {
-          unsigned m = pass ? mB : mA;
-          while (m) {
-            const int src = __ffs(m) - 1;
-            m &= m - 1;
-            const uint32_t beg = __shfl_sync(0xffffffffu, pass ? begB : begA, src);
-            const uint32_t end = __shfl_sync(0xffffffffu, pass ? endB : endA, src);
-            uint32_t j = beg;
-            for (; j + 4 <= end; j += 4) {
-              const float4 c0 = __ldg(&cell_pts[j]), c1 = __ldg(&cell_pts[j + 1]), c2 = __ldg(&cell_pts[j + 2]),
-                           c3 = __ldg(&cell_pts[j + 3]);
-              best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
-              best.offer(dist2_ref(c1.x, c1.y, c1.z, q.x, q.y, q.z), __float_as_int(c1.w));
-              best.offer(dist2_ref(c2.x, c2.y, c2.z, q.x, q.y, q.z), __float_as_int(c2.w));
-              best.offer(dist2_ref(c3.x, c3.y, c3.z, q.x, q.y, q.z), __float_as_int(c3.w));
-            }
-            for (; j < end; j++) {
-              const float4 c0 = __ldg(&cell_pts[j]);
-              best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
-            }
-          }
-        }
-      }
-      // completeness test for this level
-      const double gs = (fmn + (double)s) * g.cell;
-      const bool done = !active || ((double)best.d[K - 1] < gs * gs * (1.0 - 1e-6));
-      if (__all_sync(0xffffffffu, done))
-        break;
-    }
+    knn_walk<K>(un, q, active, g, R, cell_start, cell_pts, best);
     if (active) {
       const int qi = __float_as_int(q.w);
       const bool found = best.i[K - 1] != 0x7fffffff;

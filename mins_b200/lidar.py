@@ -274,6 +274,19 @@ class LidarMap:
         self._ck(self.lib.ml_point_rows(self.h, rows, h.ctypes.data if want_h else None, n.value, C.byref(n)))
         return rows_to_numpy(rows, n.value), h
 
+    def icp(self, T_init, map_icp_dist, seed=0, **overrides):
+        """The ICP block of LidarHelper::transform_to_map (LidarHelper.cpp:156-187) on the current scan cloud.
+        Returns (T_LtoM fp32 4x4 to pass to transform_to_map, ml_icp_result)."""
+        o = capi.ml_icp_options()
+        self.lib.ml_icp_default_options(C.byref(o))
+        o.max_dist, o.seed = float(map_icp_dist), int(seed)
+        for k, v in overrides.items():
+            setattr(o, k, v)
+        T = _f32(T_init).reshape(4, 4)
+        res = capi.ml_icp_result()
+        self._ck(self.lib.ml_scan_icp(self.h, T.ctypes.data, C.byref(o), C.byref(res)))
+        return np.array(res.T_LtoM, np.float32).reshape(4, 4), res
+
     # ---- simulator LiDAR model (Simulator::get_lidar_pointcloud, Simulator.cpp:742-815) --------------
     def sim_set_world(self, planes22):
         a = _f64(planes22).reshape(-1, 22)
