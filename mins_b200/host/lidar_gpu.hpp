@@ -44,11 +44,15 @@ struct ml_api {
   decltype(&ml_scan_transform) scan_transform;
   decltype(&ml_scan_update) scan_update;
   decltype(&ml_info_to_sqrt) info_to_sqrt;
+  decltype(&ml_linsys) linsys;
+  decltype(&ml_icp_default_options) icp_default_options;
+  decltype(&ml_scan_icp) scan_icp;
 #ifndef MINS_GPU_NO_LINK
   static ml_api real() {
     return ml_api{&ml_create,      &ml_destroy,         &ml_last_error,  &ml_map_reset,   &ml_map_initialized, &ml_map_build_from_scan,
                   &ml_map_add_scan, &ml_map_reanchor,   &ml_map_flatten, &ml_map_size,    &ml_scan_upload,     &ml_scan_deskew,
-                  &ml_scan_downsample, &ml_scan_transform, &ml_scan_update, &ml_info_to_sqrt};
+                  &ml_scan_downsample, &ml_scan_transform, &ml_scan_update, &ml_info_to_sqrt, &ml_linsys, &ml_icp_default_options,
+                  &ml_scan_icp};
   }
 #endif
 };
@@ -61,6 +65,8 @@ struct OptionsLidar {
   double raw_downsample_size = 0.1, raw_noise = 0.01, raw_point_dt = 1e-6;
   bool map_do_downsample = true, map_use_icp = false;
   double map_downsample_size = 0.1, map_noise = 0.1, map_ngbr_max_d = 0.5, map_decay_time = 30, map_decay_dist = 100;
+  double map_icp_dist = 20; // OptionsLidar.h:97
+  unsigned long long icp_seed = 0; // the reference seeds its ICP samplers from std::random_device; here it is explicit
   int map_ngbr_num = 5;
   double plane_max_p2pd = 0.1, plane_max_condi = 100.0;
   bool do_calib_ext = false, do_calib_dt = false;

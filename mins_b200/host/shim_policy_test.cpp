@@ -5,6 +5,7 @@
 #include "lidar_gpu.hpp"
 
 #include <cstdio>
+#include <cstring>
 #include <string>
 
 using namespace mins_gpu;
@@ -84,6 +85,30 @@ static int m_update(ml_handle *h, const float *, int stride, int n, float t_rel,
   cnt->n_acc = g_update_rc == ML_OK ? n : 0;
   cnt->n_chi_rej = 1;
   return g_update_rc;
+}
+static int m_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
+  std::printf("h%d linsys hx=%d\n", h->id, c->total_hx);
+  for (int i = 0; i < c->total_hx * c->total_hx; i++)
+    HtH[i] = 0;
+  for (int i = 0; i < c->total_hx; i++) {
+    HtH[i * c->total_hx + i] = 4.0;
+    Htr[i] = 2.0;
+  }
+  cnt->n_acc = 10;
+  return ML_OK;
+}
+static void m_icp_defaults(ml_icp_options *o) {
+  std::memset(o, 0, sizeof(*o));
+  o->max_iter = 40;
+}
+static int m_icp(ml_handle *h, const float T[16], const ml_icp_options *o, ml_icp_result *r) {
+  std::printf("h%d scan_icp tx=%.3f max_dist=%.1f seed=%llu\n", h->id, T[3], o->max_dist, (unsigned long long)o->seed);
+  std::memset(r, 0, sizeof(*r));
+  for (int i = 0; i < 16; i++)
+    r->T_LtoM[i] = r->T_icp[i] = T[i];
+  r->T_LtoM[3] += 0.5f; // a visible correction
+  r->success = 1;
+  return ML_OK;
 }
 static int m_sqrt(const double *HtH, const double *Htr, int n, double *Rc, double *rc) {
   for (int i = 0; i < n * n; i++)
@@ -180,7 +205,8 @@ struct MockState : StateView {
 
 int main() {
   ml_api api{m_create, m_destroy, m_err,    m_reset, m_inited, m_build,     m_add_scan, m_reanchor,
-             m_flatten, m_size,   m_upload, m_deskew, m_down,  m_transform, m_update,   m_sqrt};
+             m_flatten, m_size,   m_upload, m_deskew, m_down,  m_transform, m_update,   m_sqrt,
+             m_linsys,  m_icp_defaults, m_icp};
   OptionsLidar op;
   op.max_n = 1, op.raw_do_downsample = true, op.raw_downsample_size = 0.3, op.map_downsample_size = 0.3, op.min_range = 1.0;
   op.do_calib_ext = true;
@@ -228,5 +254,11 @@ int main() {
   up.feed_measurement(0, 11.50, pts.data(), 10);
   state_of();
   std::printf("anchor=%.2f last_up=%.2f t_hist=%zu\n", up.ikd_data[0]->time, up.ikd_data[0]->last_up_time, up.t_hist[0].size());
+  std::printf("# map_use_icp: upload -> downsample -> ICP -> transform with the ICP result -> linsys; registration uses it too\n");
+  up.op.map_use_icp = true, up.op.map_icp_dist = 50.0;
+  up.feed_measurement(0, 11.56, pts.data(), 10);
+  up.try_update();
+  state_of();
+  std::printf("icp_success=%d\n", (int)up.last_icp_success);
   return 0;
 }

@@ -9,7 +9,7 @@ public:
   // history per LiDAR id. Capacities size the device buffers once (nothing is allocated on the per-scan path).
   UpdaterLidar(StateView *state, const OptionsLidar &op, const ml_api &api, int max_scan_points = 1 << 18, int max_map_points = 1 << 21,
                int device = 0)
-      : state(state), op(op), api(api) {
+      : op(op), state(state), api(api) {
     for (int i = 0; i < op.max_n; i++) {
       Chi.emplace_back();
       t_hist[i] = std::deque<double>();
@@ -102,6 +102,8 @@ public:
   double FT = -1;
   std::vector<std::shared_ptr<LiDARData>> stack_lidar_raw, stack_lidar_new, stack_lidar_used; // friend Initializer touches these
   ml_counters last_counters{};
+  bool last_icp_success = true; // LiDARData::icp_success of the last update (LidarTypes.h)
+  OptionsLidar op;              // the reference reads state->op->lidar; here the updater holds its copy
 
 private:
   struct Pending { // what register_scan needs from update(): the transform used (LiDARData::T_LtoM)
@@ -298,9 +300,33 @@ private:
     std::vector<double> HtH((size_t)total_hx * total_hx), Htr(total_hx);
     ml_counters cnt;
     std::memset(&cnt, 0, sizeof(cnt));
-    const int rc = api.scan_update(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
-                                   (float)op.max_range, op.raw_do_downsample ? (float)op.raw_downsample_size : 0.f, pend.T_LtoM, &c,
-                                   P.data(), HtH.data(), Htr.data(), &cnt);
+    int rc;
+    if (!op.map_use_icp) {
+      rc = api.scan_update(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
+                           (float)op.max_range, op.raw_do_downsample ? (float)op.raw_downsample_size : 0.f, pend.T_LtoM, &c,
+                           P.data(), HtH.data(), Htr.data(), &cnt);
+    } else {
+      // transform_to_map with the ICP block (LidarHelper.cpp:156-187): the scan cloud is matched against the map starting
+      // from the state's T_LtoM; on success the ICP transform replaces it for the data association AND for register_scan
+      // (lidar->T_LtoM), while the residual/Jacobian keep using the state estimate (UpdaterLidar.cpp:281-283).
+      ck(api.scan_upload(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
+                         (float)op.max_range, nullptr),
+         "ml_scan_upload", ikd->tree);
+      if (op.raw_do_downsample)
+        ck(api.scan_downsample(ikd->tree, (float)op.raw_downsample_size, nullptr), "ml_scan_downsample", ikd->tree);
+      ml_icp_options io;
+      api.icp_default_options(&io);
+      io.max_dist = op.map_icp_dist;
+      io.seed = op.icp_seed++;
+      ml_icp_result ir;
+      const int irc = api.scan_icp(ikd->tree, pend.T_LtoM, &io, &ir);
+      ck(irc, "ml_scan_icp", ikd->tree);
+      if (irc == ML_OK)
+        std::memcpy(pend.T_LtoM, ir.T_LtoM, sizeof(pend.T_LtoM));
+      last_icp_success = irc == ML_OK && ir.success; // lidar->icp_success
+      ck(api.scan_transform(ikd->tree, pend.T_LtoM), "ml_scan_transform", ikd->tree);
+      rc = api.linsys(ikd->tree, &c, P.data(), HtH.data(), Htr.data(), &cnt);
+    }
     ck(rc, "ml_scan_update", ikd->tree);
     resident[ikd->id] = lidar.get();
     last_counters = cnt;
@@ -319,7 +345,6 @@ private:
   }
 
   StateView *state;
-  OptionsLidar op;
   ml_api api;
 };
 

@@ -32,7 +32,8 @@ class OptionsLidar:
     map_ngbr_max_d: float = 1.0
     map_decay_time: float = 120.0
     map_decay_dist: float = 100.0
-    map_use_icp: bool = False
+    map_use_icp: bool = False    # reference default true; its ICP is non-deterministic
+    map_icp_dist: float = 50.0   # config/simulation/config_lidar.yaml:26
     plane_max_p2pd: float = 0.1
     plane_max_condi: float = 200.0
     do_calib_ext: bool = False

@@ -35,6 +35,7 @@ class SimConfig:
     init_ori_err: float = 0.01       # rad, 1 sigma of the initial perturbation
     init_pos_err: float = 0.02       # m
     use_lidar: bool = True
+    scan_source: str = "numpy"       # "numpy": host ray-caster (world.py); "cuda": ml_sim_raycast (Philox noise keyed by seed, scan index)
     op: OptionsLidar = field(default_factory=lambda: OptionsLidar(raw_do_downsample=True, map_use_icp=False))
 
 
@@ -103,6 +104,13 @@ def run(cfg, backend):
         ba_true = ba_true + cfg.accel_walk * np.sqrt(dt_imu) * rng_imu.standard_normal(3)
         return wm, am
 
+    caster = None
+    if cfg.use_lidar and cfg.scan_source == "cuda":
+        from ..lidar import LidarMap
+        caster = LidarMap(max_scan_points=max(1024, len(dirs_L)), max_map_points=1024, device=getattr(backend, "device", 0))
+        caster.sim_set_world(world.packed())
+        caster.sim_set_rays(dirs_L)
+    p_LinI = -R_ItoL.T @ p_IinL
     n_steps = int(round(cfg.duration * cfg.freq_imu))
     imu_per_clone = int(round(cfg.freq_imu / cfg.clone_freq))
     imu_per_scan = int(round(cfg.freq_imu / cfg.freq_lidar))
@@ -129,14 +137,21 @@ def run(cfg, backend):
             nees_p.append(float(e @ np.linalg.solve(st.P[3:6, 3:6], e)))
         if cfg.use_lidar and k % imu_per_scan == 0:  # SystemManager::feed_measurement_lidar (:177-185)
             R_gt, p_gt = spline.get_pose(t)
-            xyz = simulate_scan(world, R_gt, p_gt, R_ItoL, p_IinL, dirs_L, op.min_range, op.max_range, op.raw_noise, rng_ldr)
+            if caster is not None:
+                xyz = caster.sim_raycast(p_gt + R_gt.T @ p_LinI, R_gt.T @ R_ItoL.T, op.min_range, op.max_range, noise=op.raw_noise,
+                                         seed=(int(cfg.seed) << 32) | (k // imu_per_scan))[:, :3]
+            else:
+                xyz = simulate_scan(world, R_gt, p_gt, R_ItoL, p_IinL, dirs_L, op.min_range, op.max_range, op.raw_noise, rng_ldr)
             c0 = time.perf_counter()
             upd.feed_measurement(t, xyz)
             upd.try_update()
             t_ldr += time.perf_counter() - c0
+    if caster is not None:
+        caster.close()
     rmse_ori, rmse_pos = ate(est, gt)
     traj = np.array([[e[0], *e[2], *rot_to_quat_jpl(e[1])] for e in est])
     return dict(rmse_ori_deg=rmse_ori, rmse_pos_m=rmse_pos, nees_pos=float(np.mean(nees_p)) / 3.0, n_updates=upd.n_updates,
                 n_scans=n_steps // imu_per_scan, ldr_wall_s=t_ldr, map_points=backend.map_size() if cfg.use_lidar else 0,
                 traj=traj, final_pos_err=float(np.linalg.norm(est[-1][2] - gt[-1][2])),
-                n_acc=int(sum(c.n_acc for c in upd.counters)), n_points=int(sum(c.n_points for c in upd.counters)))
+                n_acc=int(sum(c.n_acc for c in upd.counters)), n_points=int(sum(c.n_points for c in upd.counters)),
+                icp_runs=getattr(backend, "icp_runs", 0), icp_ok=getattr(backend, "icp_ok", 0), icp_iters=getattr(backend, "icp_iters", 0))

@@ -4,6 +4,7 @@ oracle run in the SAME estimator:
 
   backend.initialized() / build_map_from_scan(xyz, t_rel, op) / scan_update(xyz, t_rel, op, T, consts, P) -> (rc, Hc, rc_vec, cnt)
   backend.register_scan(xyz, t_rel, op, T) / reanchor(T, now_rel, op)
+  backend.last_T : the transform transform_to_map ended up with (the ICP result when op.map_use_icp and ICP succeeded)
 
 GpuBackend (below) drives the C ABI; the oracle backend lives in oracle/backend.py (test infrastructure).
 """
@@ -19,8 +20,11 @@ class GpuBackend:
 
     def __init__(self, max_scan_points=1 << 16, max_map_points=1 << 20, device=0):
         self.m = LidarMap(max_scan_points=max_scan_points, max_map_points=max_map_points, device=device)
+        self.device = device
         self.resident = None
         self.device_ms = 0.0
+        self.last_T = None
+        self.icp_runs = self.icp_ok = self.icp_iters = 0
 
     def close(self):
         self.m.close()
@@ -36,7 +40,20 @@ class GpuBackend:
         self.resident = scan["key"]
 
     def scan_update(self, scan, op, T_LtoM, consts, P):
-        rc, HtH, Htr, cnt = self.m.scan_update(scan["xyz"], scan["t_rel"], op, T_LtoM, consts, P)
+        if op.map_use_icp:
+            # transform_to_map with the ICP block (LidarHelper.cpp:156-187), then the point loop on the resident scan
+            self.m.feed_scan(scan["xyz"], scan["t_rel"], op)
+            if op.raw_do_downsample:
+                self.m.downsample(op.raw_downsample_size)
+            T_LtoM, res = self.m.icp(T_LtoM, op.map_icp_dist, seed=scan["key"])
+            self.icp_runs += 1
+            self.icp_ok += int(res.success)
+            self.icp_iters += res.iterations
+            self.m.transform_to_map(T_LtoM)
+            rc, HtH, Htr, cnt = self.m.linsys(consts, P)
+        else:
+            rc, HtH, Htr, cnt = self.m.scan_update(scan["xyz"], scan["t_rel"], op, T_LtoM, consts, P)
+        self.last_T = np.array(T_LtoM, np.float32).reshape(4, 4)
         self.device_ms += self.m.timing()["total"]
         self.resident = scan["key"]
         if rc != 0:
@@ -181,6 +198,8 @@ class LidarUpdater:
             return False
         if not st.ekf_update(H_order, Hc, rcv):
             return False
-        scan["T_LtoM"] = T_LtoM
+        scan["T_LtoM"] = getattr(self.backend, "last_T", None) if op.map_use_icp else T_LtoM  # lidar->T_LtoM
+        if scan["T_LtoM"] is None:
+            scan["T_LtoM"] = T_LtoM
         self.n_updates += 1
         return True

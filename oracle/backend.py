@@ -15,6 +15,8 @@ class OracleBackend:
         self.map = np.zeros((0, 4), np.float32)
         self.init = False
         self.threads = threads
+        self.last_T = None
+        self.icp_runs = self.icp_ok = self.icp_iters = 0
 
     def close(self):
         pass
@@ -37,6 +39,14 @@ class OracleBackend:
         sc = self._scan(scan, op, op.raw_do_downsample)
         if len(sc) == 0:
             return capi.ML_SOFT_NO_ROWS, None, None, capi.ml_counters()
+        if op.map_use_icp:                                                            # LidarHelper.cpp:156-187
+            from . import icp_oracle
+            r = icp_oracle.icp(sc[:, :3], self.map, T_LtoM, op.map_icp_dist, seed=scan["key"])
+            T_LtoM = r["T_LtoM"]
+            self.icp_runs += 1
+            self.icp_ok += int(r["success"])
+            self.icp_iters += r["iterations"]
+        self.last_T = np.array(T_LtoM, np.float32).reshape(4, 4)
         sm = po.transform_f32(sc, T_LtoM)                                             # transform_to_map
         ref = po.scan_linsys(consts, P, self.map, sc, sm, threads=self.threads, want_compress=True)
         if ref["cnt"].n_acc == 0:

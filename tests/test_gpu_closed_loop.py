@@ -30,3 +30,29 @@ def test_gpu_and_oracle_updaters_give_the_same_trajectory(cuda_ok, seed, downsam
     assert r_gpu["rmse_pos_m"] == pytest.approx(r_cpu["rmse_pos_m"], abs=1e-5)
     assert r_gpu["rmse_ori_deg"] == pytest.approx(r_cpu["rmse_ori_deg"], abs=1e-4)
     assert r_gpu["rmse_pos_m"] < 0.05 and r_gpu["map_points"] == r_cpu["map_points"]
+
+
+def test_closed_loop_with_gpu_icp_and_gpu_raycaster(cuda_ok):
+    """BASELINE.json config 0 with the simulation's own default `map_use_icp: true` (config_lidar.yaml:27) and the scans
+    ray-cast on the device. The reference's ICP is non-deterministic, so GPU and oracle cannot follow the same trajectory;
+    the bar is statistical: ICP converges on (nearly) every scan on both sides, in a similar number of iterations, and the
+    two closed-loop runs end up equally accurate. (Measured: on this 17-ring LiDAR in the synthetic hall the restated
+    libpointmatcher chain makes the run LESS accurate than the plain path, ~0.10 m vs ~0.04 m, and the GPU chain shows the
+    same behaviour - ring-collinear neighbourhoods give poor normals; that is a property of the method, kept.)"""
+    from mins_b200.lidar import OptionsLidar
+    from mins_b200.sim.runner import SimConfig, run
+    from mins_b200.sim.updater import GpuBackend
+    from oracle.backend import OracleBackend
+    op = OptionsLidar(raw_do_downsample=True, map_use_icp=True, map_icp_dist=50.0)
+    gpu = GpuBackend(max_scan_points=1 << 14, max_map_points=1 << 18)
+    try:
+        r = run(SimConfig(seed=3, duration=4.0, op=op, scan_source="cuda"), gpu)
+    finally:
+        gpu.close()
+    r_cpu = run(SimConfig(seed=3, duration=4.0, op=op), OracleBackend())
+    for x in (r, r_cpu):
+        assert x["icp_runs"] >= 35 and x["icp_ok"] >= 0.9 * x["icp_runs"]
+        assert 4 < x["icp_iters"] / x["icp_runs"] < 25
+        assert x["rmse_pos_m"] < 0.3 and x["n_updates"] >= 35
+    assert 0.4 < r["rmse_pos_m"] / r_cpu["rmse_pos_m"] < 2.5
+    assert 0.5 < (r["icp_iters"] / r["icp_runs"]) / (r_cpu["icp_iters"] / r_cpu["icp_runs"]) < 2.0

@@ -14,7 +14,7 @@ def run(name, *args):
 
 
 def test_shim_links_against_the_real_abi():
-    assert "ml_api bound: 16 entries" in run("shim_link_check")
+    assert "ml_api bound: 19 entries" in run("shim_link_check")
 
 
 def test_queueing_policy_trace():
@@ -61,3 +61,13 @@ def test_queueing_policy_trace():
     expect("h0 map_build_from_scan")
     assert "anchor=11.50 last_up=11.50 t_hist=6" in expect("anchor")
     assert out.count("map_reanchor") == 1
+    # map_use_icp (LidarHelper.cpp:156-187): upload -> downsample -> ICP from the state's T_LtoM -> transform with the ICP
+    # result -> point loop; the scan is then registered with the ICP transform (lidar->T_LtoM, LidarHelper.cpp:203)
+    expect("h0 scan_upload")
+    expect("h0 scan_downsample leaf=0.30")
+    assert "tx=0.060 max_dist=50.0 seed=0" in expect("h0 scan_icp")
+    assert "tx=0.560" in expect("h0 scan_transform")
+    expect("h0 linsys hx=30")
+    expect("EKFUpdate")
+    expect("h0 map_add_scan")
+    expect("icp_success=1")
