@@ -776,17 +776,21 @@ template <int K> static void launch_knn(ml_handle *h, float max_d2, int ph) {
          h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots);
 }
 // fused rows + reduction + finalize; rows_out != nullptr only for the parity export
-template <int K> static int launch_rows(ml_handle *h, PointRow *rows_out) {
+template <int K, int NB> static int launch_rows_nb(ml_handle *h, PointRow *rows_out) {
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(k_rows_reduce<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM));
+    CK(cudaFuncSetAttribute(k_rows_reduce<K, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM));
     attr_set = true;
   }
   const int nb = std::max(1, std::min(h->n_sm, cdiv(std::max(h->n_raw, 1), 256)));
-  launch_pdl(h, k_rows_reduce<K>, nb, RR_BLOCK, RR_SMEM, (const ScanState *)h->d_st, (const float4 *)h->scan_pts,
+  launch_pdl(h, k_rows_reduce<K, NB>, nb, RR_BLOCK, RR_SMEM, (const ScanState *)h->d_st, (const float4 *)h->scan_pts,
              (const float4 *)h->map_pts[h->cur], (const int32_t *)h->knn_idx, (const uint8_t *)h->knn_ok, (const DevConsts *)h->d_consts,
              rows_out, h->parts, h->ticket, h->h_out /* pinned host memory, written by the last CTA */);
   return ML_OK;
+}
+// NB = 3-wide blocks of the folded Jacobian direction that can be non-zero: 3 without extrinsic calibration, 5 with
+template <int K> static int launch_rows(ml_handle *h, PointRow *rows_out) {
+  return h->h_in->c.calib_col >= 0 ? launch_rows_nb<K, 5>(h, rows_out) : launch_rows_nb<K, 3>(h, rows_out);
 }
 static int launch_rows_k(ml_handle *h, int k, PointRow *rows_out) {
   switch (k) {

@@ -70,10 +70,15 @@ struct KnnUnit {
 };
 
 // Derived per-scan constants living in device memory (built by k_prep_consts from ml_scan_consts + P).
-#define ML_G 18 // [n*dpfinM_dI (6) | n*dpfinM_dA (6) | n*dpfinM_dcalib (6)]
+// Per-point Jacobian direction g (UpdaterLidar.cpp:320-329), folded: the reference's 18 numbers
+// [n dpfinM_dI (6) | n dpfinM_dA (6) | n dpfinM_dcalib (6)] contain n^T RGtoM twice with opposite signs (position block of I,
+// position block of A), so 15 independent numbers remain:
+//   [ I rotation (3) | n^T RGtoM (3; multiplies dTdxI position rows MINUS dTdxA position rows) | A rotation (3) | calib (6) ]
+// and only the first 9 are non-zero without extrinsic calibration.
+#define ML_G 15
 struct DevConsts {
   ml_scan_consts c;
-  double T[ML_G * ML_MAX_HX]; // h = g^T T   (rows: the 18 pose-space directions, cols: state columns)
+  double T[ML_G * ML_MAX_HX]; // h = g^T T   (rows: the 15 folded pose-space directions, cols: state columns)
   double Q[ML_G * ML_G];      // Q = T P T^T  =>  h^T P h = g^T Q g
   double Qu[ML_G * (ML_G + 1) / 2]; // packed upper triangle of Q by rows, off-diagonal entries doubled
 };
@@ -93,7 +98,7 @@ struct PointRow {
 };
 
 #define ML_NPART_MAX 256 // >= number of CTAs of the fused rows+reduce kernel (one per SM)
-#define ML_GSYM (ML_G * (ML_G + 1) / 2) // 171
+#define ML_GSYM (ML_G * (ML_G + 1) / 2) // 120
 
 // result block copied back to the host in one D2H
 struct LinsysOut {

@@ -70,16 +70,21 @@ __global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc
   if (threadIdx.x < ML_G) {
     const int r = threadIdx.x;
     double *Tr = sT + r * ML_MAX_HX;
-    if (r < 6) {
+    if (r < 6) { // I rotation rows 0-2, I position rows 3-5
       for (int b = 0; b < c.nI; b++)
         for (int cc = 0; cc < c.dTdxI[b].width; cc++)
           Tr[c.dTdxI[b].col + cc] += c.dTdxI[b].D[6 * r + cc];
-    } else if (r < 12) {
+    }
+    if (r >= 3 && r < 6) { // ... minus A position rows (g_A,pos = -g_I,pos)
+      for (int b = 0; b < c.nA; b++)
+        for (int cc = 0; cc < c.dTdxA[b].width; cc++)
+          Tr[c.dTdxA[b].col + cc] -= c.dTdxA[b].D[6 * r + cc];
+    } else if (r >= 6 && r < 9) { // A rotation rows
       for (int b = 0; b < c.nA; b++)
         for (int cc = 0; cc < c.dTdxA[b].width; cc++)
           Tr[c.dTdxA[b].col + cc] += c.dTdxA[b].D[6 * (r - 6) + cc];
-    } else if (c.calib_col >= 0) {
-      Tr[c.calib_col + (r - 12)] += 1.0;
+    } else if (r >= 9 && c.calib_col >= 0) {
+      Tr[c.calib_col + (r - 9)] += 1.0;
     }
   }
   __syncthreads();
@@ -129,7 +134,7 @@ __global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc
 // One scan point: neighbours -> plane -> gates -> g, w, vr, chi2 (see the header of this file). `c` and `sQ` live in
 // shared memory; `out` arrives zeroed with status 1. out.status: 0 accepted, 1 kNN fail, 2 plane fail, 3 bad match,
 // 4 chi2 reject.
-template <int K>
+template <int K, int NB>
 __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, const double *__restrict__ sQ,
                                           const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
                                           const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, PointRow &out) {
@@ -275,7 +280,7 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
     d_mat3_vec(c.RGtoA_fej, v, u);
     d_cross(a2, u, cr);
     g[6] = cr[0], g[7] = cr[1], g[8] = cr[2];
-    g[9] = -nG[0], g[10] = -nG[1], g[11] = -nG[2];
+    // (the A position block is -nG: folded into rows 3-5 of T, see ML_G)
     // n^T (skew(c1) - skew(c2) + RLtoM skew(c3)) = (n x c1) - (n x c2) + (a3 x c3)
     double c1[3], c2[3], c3[3], a3[3], x1[3], x2[3], x3[3];
 #pragma unroll
@@ -292,12 +297,12 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
     d_cross(a3, c3, x3);
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-      g[12 + a] = x1[a] - x2[a] + x3[a];
-      g[15 + a] = n[a] - a3[a];
+      g[9 + a] = x1[a] - x2[a] + x3[a];
+      g[12 + a] = n[a] - a3[a];
     }
     if (c.calib_col < 0) {
 #pragma unroll
-      for (int a = 12; a < 18; a++)
+      for (int a = 9; a < ML_G; a++)
         g[a] = 0.0;
     }
   }
@@ -352,16 +357,16 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
 #pragma unroll
   for (int a = 0; a < ML_G; a++)
     g[a] *= ir;
-  // sQ = packed upper triangle of Q by rows, off-diagonal entries doubled (Q is symmetric): 171 terms instead of 324
+  // sQ = packed upper triangle of Q (ML_G x ML_G) by rows, off-diagonal entries doubled (Q is symmetric). Only the leading
+  // 3*NB entries of g are non-zero (NB = 3 without extrinsic calibration: 45 terms; NB = 5: 120 terms).
   double s = 0.0;
   {
-    int q = 0;
 #pragma unroll
-    for (int a = 0; a < ML_G; a++) {
+    for (int a = 0; a < 3 * NB; a++) {
       double acc = 0.0;
 #pragma unroll
-      for (int bq = a; bq < ML_G; bq++)
-        acc += sQ[q++] * g[bq];
+      for (int bq = a; bq < 3 * NB; bq++)
+        acc += sQ[a * ML_G - (a * (a - 1)) / 2 + (bq - a)] * g[bq];
       s += g[a] * acc;
     }
   }
@@ -382,36 +387,37 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
 // Fused rows + reduction + finalize (one launch per scan). Warp-autonomous: no CTA-wide barrier in the main loop.
 //  * the scan is cut into tiles of 32 points; tile j belongs to global warp j mod NW, with global warp id
 //    gw = warp_in_cta * gridDim + cta (so a partial last round spreads over all SMs). A warp walks its tiles in order.
-//  * phase 1 (32 lanes): lane computes point_row of its point and leaves g (18), w, v^T r in the warp's shared-memory
-//    slab (never in HBM unless the parity export `rows_out` is requested); chi2 statistics by a fixed shuffle tree.
-//  * phase 2 (21 lanes): G = sum w g g^T is cut into 3x3 blocks; lane r < 21 owns upper-triangle block (bi, bj) and adds
-//    the 32 points in order (7 shared loads for 9 to 12 FMAs); diagonal blocks also carry b = sum g (v^T r).
-//    The running sums live in the warp's slab.
-//  * end: one barrier, CTA partial = sum over its warps in warp order -> parts[e][cta] (entry-major so the final pass reads
-//    coalesced); the last CTA to finish (ticket) adds the partials in CTA order, expands HtH = T^T G T, Htr = T^T b and
-//    writes the result block. Every sum has a fixed order for a given scan size and SM count: bit-reproducible.
+//  * phase 1 (32 lanes): lane computes point_row of its point and leaves g (ML_G = 15 folded numbers, 9 non-zero without
+//    extrinsic calibration), w, v^T r in the warp's shared-memory slab (never in HBM unless the parity export `rows_out` is
+//    requested); chi2 statistics by a fixed shuffle tree.
+//  * phase 2: G = sum w g g^T is cut into 3x3 blocks; with NB = 3 (no calibration) or 5 block rows there are
+//    NB(NB+1)/2 = 6 or 15 upper-triangle blocks ("roles"). The 32 lanes are split into 5 (or 2) groups of roles; group j
+//    adds the points p = j, j + groups, ... of the tile, so one tile costs 7 (or 16) iterations of 7 shared loads and 9 to 12
+//    FMAs instead of 32; diagonal blocks also carry b = sum g (v^T r). Running sums live in the warp's slab, one slot per lane.
+//  * end: one barrier, CTA partial = sum over its warps and groups in fixed order -> parts[e][cta] (entry-major so the final
+//    pass reads coalesced); the last CTA to finish (ticket) adds the partials in CTA order, expands HtH = T^T G T,
+//    Htr = T^T b and writes the result block. Every sum has a fixed order for a given scan size and SM count: bit-reproducible.
 // ------------------------------------------------------------------------------------------------
 #ifndef ML_RR_BLOCK
 #define ML_RR_BLOCK 512
 #endif
 constexpr int RR_BLOCK = ML_RR_BLOCK;
 constexpr int RR_WARPS = RR_BLOCK / 32;
-constexpr int RR_NE = ML_GSYM + ML_G; // 189
-constexpr int RR_ROW = ML_G + 1;      // padded row of g in shared memory
-constexpr int RR_ROLES = 21;          // upper-triangle 3x3 blocks of the 18x18 matrix
+constexpr int RR_NE = ML_GSYM + ML_G; // 135
+constexpr int RR_ROW = ML_G + 2;      // odd row stride of g in shared memory (bank-conflict-free stores)
 constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diagonal blocks)
 #define ML_NRED (RR_NE + 3)           // + sum_chi, sum_chi2, sum_res2
 struct RRParts {
   double v[ML_NRED][ML_NPART_MAX];
   int c[5][ML_NPART_MAX];
 };
-// per-warp slab: g rows | w | vr | running sums | 4 statistics
-constexpr int RR_SLAB = 32 * RR_ROW + 32 + 32 + RR_ROLES * RR_RACC + 4;
+// per-warp slab: g rows | w | vr | running sums (one slot per lane) | 4 statistics
+constexpr int RR_SLAB = 32 * RR_ROW + 32 + 32 + 32 * RR_RACC + 4;
 constexpr size_t RR_SMEM = sizeof(double) * ((size_t)RR_WARPS * RR_SLAB + ML_GSYM + 1) + sizeof(ml_scan_consts) + 64;
 
-__device__ __forceinline__ int rr_role_of(int bi, int bj) { return bi * 6 - (bi * (bi - 1)) / 2 + (bj - bi); }
+template <int NB> __device__ __forceinline__ int rr_role_of(int bi, int bj) { return bi * NB - (bi * (bi - 1)) / 2 + (bj - bi); }
 
-template <int K>
+template <int K, int NB>
 __global__ void __launch_bounds__(RR_BLOCK, 1)
     k_rows_reduce(const ScanState *__restrict__ st, const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
                   const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, const DevConsts *__restrict__ dc,
@@ -439,9 +445,9 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
   double *sg = slabs + (size_t)wid * RR_SLAB; // [32][RR_ROW]
   double *sw = sg + 32 * RR_ROW;               // [32]
   double *svr = sw + 32;                       // [32]
-  double *sacc = svr + 32;                     // [RR_ROLES][RR_RACC]
-  double *sstat = sacc + RR_ROLES * RR_RACC;   // chi, chi^2, rss
-  for (int e = lane; e < RR_ROLES * RR_RACC + 4; e += 32)
+  double *sacc = svr + 32;                     // [32 lanes][RR_RACC]
+  double *sstat = sacc + 32 * RR_RACC;         // chi, chi^2, rss
+  for (int e = lane; e < 32 * RR_RACC + 4; e += 32)
     sacc[e] = 0.0;
   __syncthreads();
   const ml_scan_consts &c = *scp;
@@ -450,12 +456,16 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
   const int NW = nb * RR_WARPS;
   const int gw = wid * nb + (int)blockIdx.x;
   const int ntiles = (n + 31) >> 5;
-  // phase-2 role of this lane: block (bi, bj), bi <= bj
+  // phase-2 role of this lane: group `grp` of points, block (bi, bj), bi <= bj
+  constexpr int ROLES = NB * (NB + 1) / 2;
+  constexpr int GROUPS = 32 / ROLES;
+  const int grp = lane / ROLES, role = lane - grp * ROLES;
+  const bool p2_lane = lane < ROLES * GROUPS;
   int bi = 0, bj = 0;
-  if (lane < RR_ROLES) {
-    int r = 0, rem = lane;
-    while (rem >= 6 - r) {
-      rem -= 6 - r;
+  {
+    int r = 0, rem = role;
+    while (rem >= NB - r) {
+      rem -= NB - r;
       r++;
     }
     bi = r;
@@ -475,7 +485,7 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     pr.pad = 0;
     pr.status = 1;
     if (i < n) {
-      point_row<K>(i, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
+      point_row<K, NB>(i, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
       if (rows_out)
         rows_out[i] = pr;
     }
@@ -507,12 +517,12 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     const unsigned any_ok = __ballot_sync(0xffffffffu, okp);
     __syncwarp();
     // ---- phase 2 ----
-    if (any_ok && lane < RR_ROLES) {
+    if (any_ok && p2_lane) {
       double a9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       double b3[3] = {0, 0, 0};
       const double *gI = sg + 3 * bi, *gJ = sg + 3 * bj;
 #pragma unroll 4
-      for (int p = 0; p < 32; p++) {
+      for (int p = grp; p < 32; p += GROUPS) {
         const double w = sw[p];
         const double x0 = gI[p * RR_ROW] * w, x1 = gI[p * RR_ROW + 1] * w, x2 = gI[p * RR_ROW + 2] * w;
         const double y0 = gJ[p * RR_ROW], y1 = gJ[p * RR_ROW + 1], y2 = gJ[p * RR_ROW + 2];
@@ -543,7 +553,7 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
   __syncthreads();
   // ---- CTA partial: sum over the warps in warp order ----
   if (t < RR_NE) {
-    int role, q;
+    int erole = -1, q = 0;
     if (t < ML_GSYM) {
       int r = 0, rem = t;
       while (rem >= ML_G - r) {
@@ -551,23 +561,30 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
         r++;
       }
       const int gi = r, gj = r + rem;
-      role = rr_role_of(gi / 3, gj / 3);
-      q = (gi % 3) * 3 + (gj % 3);
+      if (gj < 3 * NB) {
+        erole = rr_role_of<NB>(gi / 3, gj / 3);
+        q = (gi % 3) * 3 + (gj % 3);
+      }
     } else {
       const int a = t - ML_GSYM;
-      role = rr_role_of(a / 3, a / 3);
-      q = 9 + a % 3;
+      if (a < 3 * NB) {
+        erole = rr_role_of<NB>(a / 3, a / 3);
+        q = 9 + a % 3;
+      }
     }
     double v = 0.0;
-#pragma unroll 4
-    for (int w = 0; w < RR_WARPS; w++)
-      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + role * RR_RACC + q];
+    if (erole >= 0) {
+      for (int w = 0; w < RR_WARPS; w++)
+#pragma unroll
+        for (int gq = 0; gq < GROUPS; gq++)
+          v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + (gq * ROLES + erole) * RR_RACC + q];
+    }
     parts->v[t][blockIdx.x] = v;
   } else if (t < RR_NE + 3) {
     const int q = t - RR_NE;
     double v = 0.0;
     for (int w = 0; w < RR_WARPS; w++)
-      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + RR_ROLES * RR_RACC + q];
+      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + 32 * RR_RACC + q];
     parts->v[t][blockIdx.x] = v;
   } else if (t >= 192 && t < 197) {
     parts->c[t - 192][blockIdx.x] = scnt[t - 192];
