@@ -179,6 +179,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--warmup-seconds", type=float, default=0.5, help="minimum duration of the warm-up (0 for profiler runs)")
+    ap.add_argument("--no-aux", action="store_true", help="skip the informational aux block (profiler runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -256,7 +258,7 @@ def main():
     # ~180 us instead of 46 us (link / DMA path still ramping up); the metric is defined at steady state.
     t_w = time.perf_counter()
     n_w = 0
-    while n_w < max(3, args.warmup) or time.perf_counter() - t_w < 0.5:
+    while n_w < max(3, args.warmup) or time.perf_counter() - t_w < args.warmup_seconds:
         flush_l2()
         step(dev_ptr)
         step(host_ptr)
@@ -351,7 +353,7 @@ def main():
                          "note": "algorithmic 96 B/point x points per launch / that kernel's CUDA-event time; the map (16 MB) is "
                                  "L2-resident by nature, the path is latency/issue bound, not HBM bound (DESIGN.md)"},
         }
-        if world == 1:
+        if world == 1 and not args.no_aux:
             try:
                 line["aux"] = aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx)
             except Exception as e:  # informational block, never required for the headline

@@ -58,6 +58,10 @@ struct ml_handle {
   float *h_raw = nullptr; // pinned staging
   float4 *scan_pts = nullptr, *scan_orig = nullptr, *scan_map = nullptr, *scan_tmp = nullptr;
   ScanState *d_st = nullptr;
+  unsigned long long *lb_state = nullptr; // decoupled look-back tile states of k_range_filter_bin
+  unsigned int *lb_ctr = nullptr;         // its tile ticket (monotonic; lb_tickets = tickets handed out so far)
+  unsigned int lb_tickets = 0, lb_epoch = 0;
+  bool bin_done = false; // the queries of the resident scan are already in the hash table (fused front end)
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
   Tf32 T_LtoM;
@@ -108,6 +112,7 @@ struct ml_handle {
   cudaEvent_t ev[10];
   int timing = 1; // 0 off, 1 per-stage events (diagnostic: event records between kernels defeat the launch overlap), 2 total only
   bool use_pdl = true;
+  bool use_fused_front = true;
   float last_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
@@ -159,6 +164,15 @@ static int fail(ml_handle *h, int code, const char *msg) {
   else
     g_global_error = msg;
   return code;
+}
+
+// the fused front end leaves the scan's queries in the hash table for the kNN that normally follows; if that kNN never ran
+// (error path, new upload), the table must be emptied before anybody bins into it again
+static void drop_stale_bins(ml_handle *h) {
+  if (h->bin_done) {
+    cudaMemsetAsync(h->qtab, 0, sizeof(QSlot) * (size_t)h->q_slots, h->stream);
+    h->bin_done = false;
+  }
 }
 
 static int check_launch(ml_handle *h) {
@@ -237,8 +251,10 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   h->cap_cells = cfg->max_grid_cells > 0 ? cfg->max_grid_cells : (1 << 24);
   h->cap_all = h->cap_map + h->cap_scan;
   h->grid_cell = cfg->grid_cell > 0 ? (double)cfg->grid_cell : 0.5;
-  if (const char *e = getenv("MINS_NO_PDL")) // A/B switch for profiling
+  if (const char *e = getenv("MINS_NO_PDL")) // A/B switches for profiling
     h->use_pdl = !(e[0] == '1');
+  if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
+    h->use_fused_front = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&h->ev_prep, cudaEventDisableTiming));
@@ -282,6 +298,10 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->scan_tmp, sizeof(float4) * ca));
   CK(cudaMalloc(&h->d_st, sizeof(ScanState)));
   CK(cudaMemset(h->d_st, 0, sizeof(ScanState)));
+  CK(cudaMalloc(&h->lb_state, sizeof(unsigned long long) * (cs / RF_TILE + 2)));
+  CK(cudaMemset(h->lb_state, 0, sizeof(unsigned long long) * (cs / RF_TILE + 2)));
+  CK(cudaMalloc(&h->lb_ctr, sizeof(unsigned int)));
+  CK(cudaMemset(h->lb_ctr, 0, sizeof(unsigned int)));
   for (int b = 0; b < 2; b++) {
     CK(cudaMalloc(&h->sort_keys[b], sizeof(uint32_t) * ca));
     CK(cudaMalloc(&h->sort_vals[b], sizeof(uint32_t) * ca));
@@ -327,7 +347,7 @@ void ml_destroy(ml_handle *h) {
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -534,6 +554,7 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
     return fail(h, ML_ERR_ARG, "ml_scan_upload: bad argument (stride must be 3 or 4)");
   if (n > h->cap_scan)
     return fail(h, ML_ERR_CAPACITY, "ml_scan_upload: more points than max_scan_points");
+  drop_stale_bins(h);
   h->n_raw = n;
   h->have_T = false;
   h->rows_valid = false;
@@ -569,6 +590,23 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   }
   const int tiles = cdiv(n, RF_TILE);
   float4 *in_map = T_LtoM ? h->scan_map : nullptr;
+  if (T_LtoM && h->map_init && h->use_fused_front) {
+    // one launch: range filter (single-pass stable compaction) + transform + query binning
+    const unsigned int base = h->lb_tickets;
+    h->lb_tickets += (unsigned int)tiles;
+    h->lb_epoch = (h->lb_epoch + 1u) & 0x3fffffffu;
+    if (h->lb_epoch == 0u)
+      h->lb_epoch = 1u;
+    const uint32_t mask = (uint32_t)h->q_slots - 1u;
+    if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0)
+      LAUNCHP(k_range_filter_bin<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
+              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, base, h->lb_epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+    else
+      LAUNCHP(k_range_filter_bin<false>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
+              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, base, h->lb_epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+    h->bin_done = true;
+    return check_launch(h);
+  }
   if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0) {
     LAUNCHP(k_range_count<true>, tiles, RF_BLOCK, raw_src, stride, n, (double)rmin, (double)rmax, h->d_st, h->tile_sums);
     LAUNCHP(k_range_compact<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->tile_sums, h->d_st,
@@ -601,6 +639,7 @@ int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
     return fail(h, ML_ERR_ARG, "ml_scan_set: bad argument");
   if (n > h->cap_scan)
     return fail(h, ML_ERR_CAPACITY, "ml_scan_set: more points than max_scan_points");
+  drop_stale_bins(h);
   h->n_raw = n;
   h->have_T = false;
   h->rows_valid = false;
@@ -659,6 +698,7 @@ int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds) {
 }
 
 static int scan_transform_async(ml_handle *h, const float T[16]) {
+  drop_stale_bins(h);
   for (int r = 0; r < 3; r++)
     for (int c = 0; c < 4; c++)
       h->T_LtoM.m[4 * r + c] = T[4 * r + c];
@@ -820,7 +860,9 @@ static int knn_async(ml_handle *h, int k, float max_d2) {
   h->knn_calls++;
   if (h->timing == 1)
     cudaEventRecord(h->ev[3], h->stream);
-  LAUNCHP(k_query_bin, cdiv(n, 256), 256, h->scan_map, h->d_st, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+  if (!h->bin_done)
+    LAUNCHP(k_query_bin, cdiv(n, 256), 256, h->scan_map, h->d_st, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+  h->bin_done = false;
   LAUNCHP(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, ph, h->units, h->units_cap);
   LAUNCHP(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
   if (h->timing == 1)

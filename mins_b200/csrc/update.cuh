@@ -4,6 +4,7 @@
 #pragma once
 #include "prims.cuh"
 #include "map.cuh"
+#include "scan.cuh"
 
 namespace ml {
 
@@ -27,26 +28,18 @@ __device__ __forceinline__ void cell_unkey(unsigned long long k, int *cx, int *c
   *cz = (int)(k & 0x1fffffull) - B;
 }
 
-__global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
-                                                  const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
-                                                  uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
-  pdl_enter();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = i < st->n_scan;
-  const unsigned act = __ballot_sync(0xffffffffu, live);
-  if (!live)
-    return;
+// Places one query into the hash table. Called by all lanes of `act` together. Warp-aggregated: consecutive rays mostly
+// share a cell, so one lane per distinct key probes the table and reserves the ranks of all its peers with one atomicAdd.
+__device__ __forceinline__ void bin_query(const float4 q, const unsigned act, const GridDesc *__restrict__ gd, QSlot *__restrict__ tab,
+                                          const uint32_t mask, uint32_t *slot_out, uint32_t *rank_out) {
   const double ox = gd->ox, oy = gd->oy, oz = gd->oz, inv = gd->inv_cell;
-  float4 q = q_in_map[i];
   // clamp far-away queries to a band around the grid so the key packing cannot overflow; such queries have no
   // candidate within reach anyway
   const int lim = 1 << 19;
-  int cx = max(-lim, min(lim, cell_coord((double)q.x, ox, inv)));
-  int cy = max(-lim, min(lim, cell_coord((double)q.y, oy, inv)));
-  int cz = max(-lim, min(lim, cell_coord((double)q.z, oz, inv)));
-  unsigned long long key = cell_key(cx, cy, cz);
-  // warp-aggregated: consecutive rays mostly share a cell, so one lane per distinct key probes the table and reserves
-  // the ranks of all its peers with a single atomicAdd
+  const int cx = max(-lim, min(lim, cell_coord((double)q.x, ox, inv)));
+  const int cy = max(-lim, min(lim, cell_coord((double)q.y, oy, inv)));
+  const int cz = max(-lim, min(lim, cell_coord((double)q.z, oz, inv)));
+  const unsigned long long key = cell_key(cx, cy, cz);
   const int lane = threadIdx.x & 31;
   const unsigned peers = __match_any_sync(act, key);
   const int leader = __ffs(peers) - 1;
@@ -63,8 +56,141 @@ __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_
   }
   s = __shfl_sync(peers, s, leader);
   base = __shfl_sync(peers, base, leader);
+  *slot_out = s;
+  *rank_out = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_in_map, const ScanState *__restrict__ st,
+                                                  const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
+                                                  uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
+  pdl_enter();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < st->n_scan;
+  const unsigned act = __ballot_sync(0xffffffffu, live);
+  if (!live)
+    return;
+  uint32_t s, r;
+  bin_query(q_in_map[i], act, gd, tab, mask, &s, &r);
   q_slot[i] = s;
-  q_rank[i] = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+  q_rank[i] = r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// One-pass front end of the un-down-sampled path: LiDARData's range filter (LidarTypes.cpp:36-55) as a stable compaction
+// with decoupled look-back (tile b publishes its count, then the running prefix; a later tile adds counts backwards until
+// it meets a prefix), the fp32 transform into the map frame (LidarHelper.cpp:192) and the query binning, all on the
+// registers that hold the freshly loaded points. Replaces k_range_count + k_range_compact + k_query_bin (3 launches, 2 extra
+// passes over the scan). Tiles are handed out by an atomic ticket, so every tile a CTA waits for belongs to a CTA that is
+// already running: the look-back cannot deadlock whatever the grid size. States carry a per-scan epoch: no reset pass.
+// ------------------------------------------------------------------------------------------------
+constexpr unsigned long long LB_AGG = 1ull, LB_PREFIX = 2ull;
+__device__ __forceinline__ unsigned long long lb_pack(uint32_t epoch, unsigned long long flag, uint32_t v) {
+  return ((unsigned long long)epoch << 34) | (flag << 32) | (unsigned long long)v;
+}
+template <bool VEC4>
+__global__ void __launch_bounds__(RF_BLOCK)
+    k_range_filter_bin(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax, ScanState *__restrict__ st,
+                       float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
+                       unsigned long long *tile_state, unsigned int *tile_ctr, unsigned int ticket_base, uint32_t epoch,
+                       const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask, uint32_t *__restrict__ q_slot,
+                       uint32_t *__restrict__ q_rank) {
+  __shared__ uint32_t wsum[RF_BLOCK / 32];
+  __shared__ uint32_t s_tile, s_prefix;
+  pdl_enter();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0)
+    s_tile = atomicAdd(tile_ctr, 1u) - ticket_base;
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const int wbase = (int)tile * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
+  float4 pt[8];
+  uint32_t bal[8];
+  uint32_t cnt = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int i = wbase + r * 32 + lane;
+    pt[r] = i < n ? load_raw<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool k = i < n && range_keep(pt[r], rmin, rmax);
+    bal[r] = __ballot_sync(0xffffffffu, k);
+    cnt += __popc(bal[r]);
+  }
+  if (lane == 0)
+    wsum[wid] = cnt;
+  __syncthreads();
+  if (wid == 0) {
+    uint32_t tot = lane < RF_BLOCK / 32 ? wsum[lane] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    volatile unsigned long long *vs = tile_state;
+    if (lane == 0) {
+      vs[tile] = lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, tot);
+      __threadfence();
+    }
+    uint32_t excl = 0;
+    if (tile > 0) {
+      int base = (int)tile - 1;
+      for (;;) {
+        const int b = base - lane;
+        unsigned long long sv = lb_pack(epoch, LB_PREFIX, 0u); // tiles before the first: prefix 0
+        if (b >= 0) {
+          do {
+            sv = vs[b];
+          } while ((uint32_t)(sv >> 34) != epoch);
+        }
+        const bool is_prefix = ((sv >> 32) & 3ull) == LB_PREFIX;
+        const uint32_t val = (uint32_t)sv;
+        const unsigned pm = __ballot_sync(0xffffffffu, is_prefix);
+        // lanes up to (and including) the nearest tile that already knows its prefix contribute
+        const int first = pm ? __ffs(pm) - 1 : 31;
+        uint32_t part = lane <= first ? val : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+          part += __shfl_xor_sync(0xffffffffu, part, o);
+        excl += part;
+        if (pm)
+          break;
+        base -= 32;
+      }
+      if (lane == 0) {
+        vs[tile] = lb_pack(epoch, LB_PREFIX, excl + tot);
+        __threadfence();
+      }
+    }
+    if (lane == 0) {
+      s_prefix = excl;
+      if (tile == 0) {
+        st->n_raw = n;
+        st->vox_n = 0;
+        st->vox_passthrough = 0;
+      }
+      if (tile == gridDim.x - 1) {
+        st->n_orig = (int)(excl + tot);
+        st->n_scan = (int)(excl + tot);
+      }
+    }
+  }
+  __syncthreads();
+  uint32_t pos = s_prefix;
+  for (int w = 0; w < wid; w++)
+    pos += wsum[w];
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    if ((bal[r] >> lane) & 1u) {
+      const uint32_t o = pos + __popc(bal[r] & lt);
+      const float4 q = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
+      cloud[o] = q;
+      orig[o] = q;
+      const float4 qm = tf_apply(T, q);
+      in_map[o] = qm;
+      uint32_t s, rk;
+      bin_query(qm, bal[r], gd, tab, mask, &s, &rk);
+      q_slot[o] = s;
+      q_rank[o] = rk;
+    }
+    pos += __popc(bal[r]);
+  }
 }
 
 // every occupied slot gets a contiguous range of the sorted query array and ceil(cnt/32) warp units;
