@@ -113,6 +113,7 @@ struct ml_handle {
   int timing = 1; // 0 off, 1 per-stage events (diagnostic: event records between kernels defeat the launch overlap), 2 total only
   bool use_pdl = true;
   bool use_fused_front = true;
+  bool zero_copy = true; // MINS_ZERO_COPY=0 restores the DMA copy of pinned input
   float last_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
@@ -253,6 +254,8 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   h->grid_cell = cfg->grid_cell > 0 ? (double)cfg->grid_cell : 0.5;
   if (const char *e = getenv("MINS_NO_PDL")) // A/B switches for profiling
     h->use_pdl = !(e[0] == '1');
+  if (const char *e = getenv("MINS_ZERO_COPY"))
+    h->zero_copy = !(e[0] == '0');
   if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
     h->use_fused_front = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -579,6 +582,10 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
     if (on_device) {
       // scan already resident in HBM (e.g. produced by a device-side driver): used in place, no copy
       raw_src = xyz;
+    } else if (pinned && h->zero_copy && at.devicePointer && T_LtoM && h->map_init && h->use_fused_front) {
+      // pinned, device-mapped host memory and the one-pass front end: the kernel reads the scan straight over PCIe (each
+      // point is read exactly once), so there is no separate DMA copy to wait for
+      raw_src = (const float *)at.devicePointer;
     } else {
       const float *src = xyz;
       if (!pinned) { // pageable host memory: stage through the handle's pinned buffer
@@ -945,14 +952,14 @@ static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) 
 // everything after the transform; one synchronisation at the end. consts_async must have been issued.
 static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *HtH, double *Htr, ml_counters *cnt) {
   const int hx = c->total_hx, k = c->map_ngbr_num;
-  // join the constants' stream BEFORE the binning kernels (k_prep_consts is long done by then): bin -> alloc -> scatter ->
-  // knn -> rows then form one uninterrupted chain of programmatically dependent launches
-  CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   int rc = knn_async(h, k, (float)c->map_ngbr_max_d);
   if (rc) {
     cudaStreamSynchronize(h->stream2);
     return rc;
   }
+  // join the constants' stream as late as possible: k_prep_consts (~20 us, one CTA) and its two small H2D copies run
+  // beside front end + binning + kNN; only the rows kernel reads d_consts
+  CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   rc = launch_rows_k(h, k, nullptr);
   if (rc)
     return rc;
