@@ -8,8 +8,9 @@ configuration the metric's target is quoted on; it fits one GPU.
 
   value : whole-job points/s with the raw scan already resident in HBM (device-pointer input), device time from CUDA
           events on the handle's own stream (ml_last_timing), L2 flushed between steps.
-  e2e   : the same through the C-ABI call with PINNED HOST input, H2D and D2H inside the timed region (wall clock of the
-          blocking call).
+  e2e   : the same through the C-ABI call with PINNED HOST input and HOST output inside the timed region (wall clock of the
+          blocking call). The bytes cross PCIe inside the call: the front-end kernel reads the pinned scan directly
+          (zero-copy, each point once) and the last CTA of the rows kernel writes the result block to pinned host memory.
   N > 1 : independent Monte-Carlo replicas, one process per GPU, no data-path collective: weak scaling.
   --impl reference : the reference CPU path on the host cores (reference ikd-Tree compiled unmodified + restated rows).
 """
@@ -323,15 +324,15 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        kern = {"knn": "k_knn<5>", "rows_reduce": "k_rows_reduce<5> (plane fit + residual/Jacobian + chi2 + reduction + finalize)",
-                "bin": "query binning (3 kernels)", "upload_filter": "range filter + transform (2 kernels)"}
+        kern = {"knn": "k_knn<5>", "rows_reduce": "k_rows_reduce<5,3> (plane fit + residual/Jacobian + chi2 + reduction + finalize)",
+                "bin": "k_unit_alloc + k_query_scatter", "upload_filter": "k_range_filter_bin (range filter + transform + query binning)"}
         cand = {k_: stage.get(k_, 0.0) / args.steps for k_ in kern}
         dom = max(cand, key=cand.get)
         ach = ALG_BYTES_PER_POINT * n / (cand[dom] * 1e-3) / 1e9
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
-            traffic = prof.get(dom, {}).get("dram_bytes_per_launch")
+            traffic = prof.get({"upload_filter": "front"}.get(dom, dom), {}).get("dram_bytes_per_launch")
         except Exception:
             pass
         line = {
