@@ -144,6 +144,21 @@ def aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx, reps=10):
         t_upd.append(time.perf_counter() - t0)
         assert np.isfinite(dx).all() and np.isfinite(Pn).all()
     aux = {"ms_per_lidar_ekf_update": float(np.median(t_upd) * 1e3), "ekf_state_dim": 100, "total_hx": int(hx)}
+    # mode B of SURVEY.md 8(d): raw_do_downsample with leaf 0.3 (PCL VoxelGrid restatement on the device before the kNN)
+    import ctypes as C
+    T = np.ascontiguousarray(w["T_LtoM"], np.float32)
+    P = np.ascontiguousarray(w["P"], np.float64)
+    t_b = []
+    for _ in range(reps):
+        flush_l2()
+        t0 = time.perf_counter()
+        rc = m.lib.ml_scan_update(m.h, host_ptr, 4, int(w["n_rays"]), w["t_rel"], op.min_range, op.max_range, 0.3, T.ctypes.data,
+                                  C.byref(w["consts"]), P.ctypes.data, out[0].ctypes.data, out[1].ctypes.data, C.byref(out[2]))
+        t_b.append(time.perf_counter() - t0)
+        assert rc in (0, 1)
+    aux["mode_B_downsample_leaf_0.3"] = {"e2e_ms_per_scan": float(np.median(t_b) * 1e3), "points_after_downsample": int(out[2].n_points),
+                                         "raw_points_per_s": float(w["n_rays"] / np.median(t_b))}
+    step(host_ptr)  # back to mode A: the resident scan is the full one again
     # ICP pre-alignment of the resident scan against the 1 M-point map (map_icp_dist 50 m)
     t_icp, iters = [], []
     for r in range(3):

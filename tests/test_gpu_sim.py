@@ -100,3 +100,27 @@ def test_raycast_scan_feeds_the_update_in_place(sim_map, po, workload):
     hst = upd(host.ctypes.data)
     assert np.array_equal(kept_dev, m.scan(2))
     assert dev[2] == hst[2] and np.array_equal(dev[0], hst[0]) and np.array_equal(dev[1], hst[1])
+
+
+def test_raycast_with_more_planes_than_one_shared_memory_pass(sim_map, po):
+    """> 256 planes: k_ray_cast stages the world in several shared-memory passes; plus the empty-result edge case."""
+    from mins_b200.sim.world import PlaneWorld, lidar_ray_dirs
+    rng = np.random.default_rng(5)
+    segs = []
+    for _ in range(90):  # 90 boxes x 4 walls = 360 wall planes (+ floor and ceiling)
+        cx, cy, s = rng.uniform(-30, 30), rng.uniform(-30, 30), rng.uniform(0.3, 1.5)
+        if abs(cx) < 3 and abs(cy) < 3:
+            cx += 6
+        segs += [[cx - s, cy - s, cx - s, cy + s], [cx - s, cy - s, cx + s, cy - s], [cx - s, cy + s, cx + s, cy + s], [cx + s, cy - s, cx + s, cy + s]]
+    world = PlaneWorld(np.array(segs))
+    assert len(world.quads) > 256
+    dirs = lidar_ray_dirs(np.arange(-30, 31, 5), -180, 180, 0.5)
+    p, R = np.array([0.0, 0.0, 0.5]), np.eye(3)
+    sim_map.sim_set_world(world.packed())
+    sim_map.sim_set_rays(dirs)
+    got = sim_map.sim_raycast(p, R, 0.5, 100.0)
+    want, keep, best = po.sim_lidar_scan(world.quads, p, R, dirs, 0.5, 100.0)
+    assert len(got) == len(want) > 1000 and np.abs(got - want).max() <= 4e-6
+    # a range gate nothing passes
+    none = sim_map.sim_raycast(p, R, 1000.0, 2000.0)
+    assert none.shape == (0, 4)
