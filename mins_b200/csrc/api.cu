@@ -65,7 +65,7 @@ struct ml_handle {
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
   Tf32 T_LtoM;
-  uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}, *radix_table = nullptr;
+  uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}, *radix_table = nullptr, *radix_dtot = nullptr;
   int radix_tiles_cap = 0;
   VoxGridDesc *d_vg = nullptr;
   float *d_knots = nullptr;
@@ -197,9 +197,9 @@ static void radix_sort(ml_handle *h, const int *d_n, int n_ub, int bits) {
   int src = 0;
   for (int p = 0; p < passes; p++) {
     LAUNCH(k_radix_hist, tiles, RS_BLOCK, h->sort_keys[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap);
-    LAUNCH(k_radix_scan, 1, 1024, h->radix_table, d_n, h->radix_tiles_cap);
+    LAUNCH(k_radix_scan, 256, 256, h->radix_table, d_n, h->radix_tiles_cap, h->radix_dtot);
     LAUNCH(k_radix_scatter, tiles, RS_BLOCK, h->sort_keys[src], h->sort_vals[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap,
-           h->sort_keys[1 - src], h->sort_vals[1 - src]);
+           h->radix_dtot, h->sort_keys[1 - src], h->sort_vals[1 - src]);
     src = 1 - src;
   }
 }
@@ -311,6 +311,7 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   }
   h->radix_tiles_cap = cdiv((long long)ca, RS_TILE) + 1;
   CK(cudaMalloc(&h->radix_table, sizeof(uint32_t) * 256 * (size_t)h->radix_tiles_cap));
+  CK(cudaMalloc(&h->radix_dtot, sizeof(uint32_t) * 256));
   CK(cudaMalloc(&h->d_vg, sizeof(VoxGridDesc)));
   h->q_slots = 1;
   while ((size_t)h->q_slots < 2 * cs)
@@ -350,7 +351,7 @@ void ml_destroy(ml_handle *h) {
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot};
   for (void *p : dev)
     if (p)
       cudaFree(p);

@@ -115,8 +115,8 @@ __global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(const uint32_t *__res
 // table) -> k_radix_scatter (stable in-tile ranking with warp match_any, warps own consecutive chunks).
 // ------------------------------------------------------------------------------------------------
 constexpr int RS_BLOCK = 256;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_BLOCK * RS_ITEMS; // 4096
+constexpr int RS_ITEMS = 4;
+constexpr int RS_TILE = RS_BLOCK * RS_ITEMS; // 1024: a 131 072-point scan sorts on 128 CTAs
 constexpr int RS_WARPS = RS_BLOCK / 32;
 
 __global__ void __launch_bounds__(RS_BLOCK) k_radix_hist(const uint32_t *__restrict__ keys, const int *__restrict__ d_n, int shift,
@@ -138,39 +138,33 @@ __global__ void __launch_bounds__(RS_BLOCK) k_radix_hist(const uint32_t *__restr
   table[threadIdx.x * ntiles_cap + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of the digit-major table restricted to the live tiles: order (digit 0: tiles 0..nt-1, digit 1: ...)
-__global__ void __launch_bounds__(1024) k_radix_scan(uint32_t *__restrict__ table, const int *__restrict__ d_n, int ntiles_cap) {
+// Row scan of the digit-major table: CTA d scans row d (the counts of digit d over the live tiles) in place to exclusive
+// prefixes and leaves the digit total in dtot[d]. 256 CTAs, all loads in flight at once; the scatter kernel turns the 256
+// digit totals into digit bases itself (one block scan), so there is no serial pass over the table.
+__global__ void __launch_bounds__(256) k_radix_scan(uint32_t *__restrict__ table, const int *__restrict__ d_n, int ntiles_cap,
+                                                   uint32_t *__restrict__ dtot) {
   const int n = *d_n;
   const int ntiles = (n + RS_TILE - 1) / RS_TILE;
-  const int total = 256 * ntiles;
-  __shared__ uint32_t carry;
-  if (threadIdx.x == 0)
-    carry = 0;
-  __syncthreads();
-  for (int base = 0; base < total; base += 1024) {
-    int e = base + threadIdx.x;
-    uint32_t v = 0;
-    int addr = 0;
-    if (e < total) {
-      int d = e / ntiles, t = e - d * ntiles;
-      addr = d * ntiles_cap + t;
-      v = table[addr];
-    }
+  uint32_t *row = table + (size_t)blockIdx.x * ntiles_cap;
+  uint32_t carry = 0;
+  for (int base = 0; base < ntiles; base += 256) {
+    const int t = base + threadIdx.x;
+    const uint32_t v = t < ntiles ? row[t] : 0u;
     uint32_t tot;
-    uint32_t ex = block_excl_scan<1024>(v, &tot);
-    if (e < total)
-      table[addr] = ex + carry;
-    __syncthreads();
-    if (threadIdx.x == 0)
-      carry += tot;
-    __syncthreads();
+    const uint32_t ex = block_excl_scan<256>(v, &tot);
+    if (t < ntiles)
+      row[t] = carry + ex;
+    carry += tot;
   }
+  if (threadIdx.x == 0)
+    dtot[blockIdx.x] = carry;
 }
 
 __global__ void __launch_bounds__(RS_BLOCK) k_radix_scatter(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
                                                            const int *__restrict__ d_n, int shift,
                                                            const uint32_t *__restrict__ table, int ntiles_cap,
-                                                           uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out) {
+                                                           const uint32_t *__restrict__ dtot, uint32_t *__restrict__ keys_out,
+                                                           uint32_t *__restrict__ vals_out) {
   __shared__ uint32_t wcnt[RS_WARPS][256]; // per-warp digit counts -> per-warp bases
   const int n = *d_n;
   const int ntiles = (n + RS_TILE - 1) / RS_TILE;
@@ -208,7 +202,8 @@ __global__ void __launch_bounds__(RS_BLOCK) k_radix_scatter(const uint32_t *__re
   // per digit: exclusive prefix over warps + global base of this tile
   {
     const int d = threadIdx.x; // 256 threads == 256 digits
-    uint32_t run = table[d * ntiles_cap + blockIdx.x];
+    const uint32_t dbase = block_excl_scan<RS_BLOCK>(dtot[d], nullptr); // elements with a smaller digit
+    uint32_t run = dbase + table[d * ntiles_cap + blockIdx.x];
 #pragma unroll
     for (int w = 0; w < RS_WARPS; w++) {
       uint32_t c = wcnt[w][d];
