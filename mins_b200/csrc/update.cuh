@@ -261,13 +261,20 @@ template <int K> struct TopK {
       i[j] = 0x7fffffff;
     }
   }
+  // (d2, index) ascending as ONE unsigned 64-bit compare: squared distances are non-negative, so their bit patterns order
+  // like their values (+inf = 0x7f800000 included) and the pair (bits(d2), index) orders like the 64-bit number
+  // bits(d2) << 32 | index. The compiler keeps d and i in separate registers and emits a two-instruction wide compare
+  // instead of FSETP.LT + FSETP.EQ + ISETP.LT + a predicate combine.
+  static __device__ __forceinline__ unsigned long long key(float d2, int idx) {
+    return ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned long long)(unsigned int)idx;
+  }
   __device__ __forceinline__ void offer(float d2, int idx) {
-    if (d2 < d[K - 1] || (d2 == d[K - 1] && idx < i[K - 1])) {
+    if (key(d2, idx) < key(d[K - 1], i[K - 1])) {
       d[K - 1] = d2;
       i[K - 1] = idx;
 #pragma unroll
       for (int s = K - 1; s > 0; --s) {
-        bool sw = d[s] < d[s - 1] || (d[s] == d[s - 1] && i[s] < i[s - 1]);
+        const bool sw = key(d[s], i[s]) < key(d[s - 1], i[s - 1]);
         float td = sw ? d[s - 1] : d[s];
         int ti = sw ? i[s - 1] : i[s];
         d[s - 1] = sw ? d[s] : d[s - 1];
