@@ -942,9 +942,8 @@ static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) 
   memcpy(h->h_in->P, P, sizeof(double) * (size_t)hx * hx);
   // no fork event: every entry point that launches the rows kernel (the only reader of d_consts) synchronises the main
   // stream before it returns, so d_consts is idle here; an event record here would also split the kernel chain
-  CK(cudaMemcpyAsync(&h->d_consts->c, &h->h_in->c, sizeof(ml_scan_consts), cudaMemcpyHostToDevice, h->stream2));
-  CK(cudaMemcpyAsync(h->d_P, h->h_in->P, sizeof(double) * (size_t)hx * hx, cudaMemcpyHostToDevice, h->stream2));
-  k_prep_consts<<<1, 1024, 0, h->stream2>>>(h->d_consts, h->d_P);
+  // no copy nodes: k_prep_consts reads the pinned staging block over PCIe (24 KB) and leaves c, T, Q in device memory
+  k_prep_consts<<<1, 1024, 0, h->stream2>>>(h->d_consts, &h->h_in->c, h->h_in->P);
   h->launches++;
   CK(cudaEventRecord(h->ev_prep, h->stream2));
   return ML_OK;

@@ -58,11 +58,24 @@ __device__ __forceinline__ void sym3_eig_minmax(double a00, double a01, double a
 
 // T (18 x hx) and Q = T P T^T from the scan constants. One block of 1024; T and T P staged in shared memory, P read
 // coalesced (thread index runs along P's rows).
-__global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc, const double *__restrict__ P) {
+// `c_in` and `P` may live in pinned HOST memory (the library's staging block): the kernel pulls the ~24 KB over PCIe itself, so
+// the side stream carries no copy nodes at all.
+__global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *dc, const ml_scan_consts *__restrict__ c_in, const double *__restrict__ P) {
   __shared__ double sT[ML_G * ML_MAX_HX];
   __shared__ double sTP[ML_G * ML_MAX_HX];
+  __shared__ double sP[ML_MAX_HX * ML_MAX_HX]; // 32 KB: P staged with every load in flight at once (one DRAM round trip)
+  const int hx = c_in->total_hx;
+  for (int e = threadIdx.x; e < hx * hx; e += blockDim.x)
+    sP[e] = __ldg(&P[e]);
+  {
+    const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
+    const int *src = reinterpret_cast<const int *>(c_in);
+    int *dst = reinterpret_cast<int *>(&dc->c);
+    for (int e = threadIdx.x; e < nw; e += blockDim.x)
+      dst[e] = __ldg(&src[e]);
+  }
+  __syncthreads(); // dc->c is complete and visible to the whole CTA from here on
   const ml_scan_consts &c = dc->c;
-  const int hx = c.total_hx;
   for (int e = threadIdx.x; e < ML_G * ML_MAX_HX; e += blockDim.x)
     sT[e] = 0.0;
   __syncthreads();
@@ -95,13 +108,13 @@ __global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *__restrict__ dc
     double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
     int l = 0;
     for (; l + 4 <= hx; l += 4) {
-      s0 += sT[r * ML_MAX_HX + l] * __ldg(&P[(size_t)l * hx + j]);
-      s1 += sT[r * ML_MAX_HX + l + 1] * __ldg(&P[(size_t)(l + 1) * hx + j]);
-      s2 += sT[r * ML_MAX_HX + l + 2] * __ldg(&P[(size_t)(l + 2) * hx + j]);
-      s3 += sT[r * ML_MAX_HX + l + 3] * __ldg(&P[(size_t)(l + 3) * hx + j]);
+      s0 += sT[r * ML_MAX_HX + l] * sP[l * hx + j];
+      s1 += sT[r * ML_MAX_HX + l + 1] * sP[(l + 1) * hx + j];
+      s2 += sT[r * ML_MAX_HX + l + 2] * sP[(l + 2) * hx + j];
+      s3 += sT[r * ML_MAX_HX + l + 3] * sP[(l + 3) * hx + j];
     }
     for (; l < hx; l++)
-      s0 += sT[r * ML_MAX_HX + l] * __ldg(&P[(size_t)l * hx + j]);
+      s0 += sT[r * ML_MAX_HX + l] * sP[l * hx + j];
     sTP[r * ML_MAX_HX + j] = (s0 + s1) + (s2 + s3);
   }
   __syncthreads();
