@@ -446,3 +446,50 @@ def test_full_size_g64_properties(make_map, po, workload):
     n_before = m.size()
     n_after = m.register_scan(op)
     assert n_before < n_after <= n_before + c["n_points"]
+
+
+def test_one_launch_front_end_equals_the_multi_call_path(make_map, po, workload):
+    """ml_scan_update's fused front end (single-pass compaction + transform + binning, zero-copy pinned input) must leave
+    exactly the state the separate calls leave: same clouds, same kNN, same reduced system - for packed xyz (stride 3),
+    PointXYZ (stride 4), pageable and pinned host buffers, device buffers, ragged sizes, and over many consecutive scans."""
+    import ctypes as C
+    import torch
+    from mins_b200 import capi
+    w = workload("G-vlp")
+    op = w["op"]
+    m = make_map(max_map_points=1 << 19)
+    m.Build(w["map"])
+    hx = w["total_hx"]
+    T = np.ascontiguousarray(w["T_LtoM"], np.float32)
+    P = np.ascontiguousarray(w["P"], np.float64)
+
+    def one_call(ptr, stride, n):
+        HtH, Htr, cnt = np.zeros((hx, hx)), np.zeros(hx), capi.ml_counters()
+        rc = m.lib.ml_scan_update(m.h, ptr, stride, n, w["t_rel"], op.min_range, op.max_range, 0.0, T.ctypes.data,
+                                  C.byref(w["consts"]), P.ctypes.data, HtH.ctypes.data, Htr.ctypes.data, C.byref(cnt))
+        assert rc in (0, 1)
+        return HtH, Htr, cnt.as_dict(), m.scan(0), m.scan(1), m.scan(2)
+
+    raw = np.ascontiguousarray(w["raw"], np.float32)
+    # make a third of the points fall outside the range gate so that the compaction is non-trivial in every tile
+    raw = raw.copy()
+    raw[::3, :3] *= 1000.0
+    for n in (len(raw), 2048 * 3 + 17, 2047, 1):
+        sub = np.ascontiguousarray(raw[:n])
+        # reference state: the multi-call path
+        kept = m.feed_scan(sub, w["t_rel"], op)
+        m.transform_to_map(T)
+        idx0, d20, ok0 = m.get_neighbors(op.map_ngbr_num, op.map_ngbr_max_d)
+        rc0, HtH0, Htr0, cnt0 = m.linsys(w["consts"], P)
+        s0 = (m.scan(0), m.scan(1), m.scan(2))
+        assert len(s0[0]) == kept == len(po.range_filter(sub, w["t_rel"], op.max_range, op.min_range))
+        pinned = torch.from_numpy(sub).pin_memory()
+        dev = torch.from_numpy(sub).cuda()
+        xyz3 = np.ascontiguousarray(sub[:, :3])
+        for ptr, stride in ((sub.ctypes.data, 4), (pinned.data_ptr(), 4), (dev.data_ptr(), 4), (xyz3.ctypes.data, 3)):
+            for _ in range(3):
+                HtH, Htr, cnt, a, b, c = one_call(ptr, stride, n)
+                assert np.array_equal(a, s0[0]) and np.array_equal(b, s0[1]) and np.array_equal(c, s0[2])
+                assert cnt == cnt0.as_dict() and np.array_equal(HtH, HtH0) and np.array_equal(Htr, Htr0)
+            idx, d2, ok = m.get_neighbors(op.map_ngbr_num, op.map_ngbr_max_d)
+            assert np.array_equal(idx, idx0) and np.array_equal(d2, d20) and np.array_equal(ok, ok0)
