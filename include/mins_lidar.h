@@ -214,6 +214,12 @@ int ml_sim_set_rays(ml_handle *h, const double *dirs_L, int n_rays);
  * becomes the raw-scan buffer, see ml_sim_scan_device); xyz_out (stride 4, may be NULL) receives min(cap, n) points. */
 int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9], double min_range, double max_range, float noise,
                    uint64_t seed, float *xyz_out, int cap, int *n_out);
+/* The same with the motion distortion of Simulator.cpp:761-771 (`raw_remove_motion_blur`): ray i of n_rays is cast from the
+ * sensor pose at time - (n_rays - i) * raw_point_dt. pose_knots: n_knots >= 2 poses [R_LtoG row-major (9) | p_LinG (3)] sampled
+ * uniformly over [time - n_rays * raw_point_dt, time]; a ray blends its two bracketing knots linearly. The inverse operation
+ * on the estimator side is ml_scan_deskew. */
+int ml_sim_raycast_sweep(ml_handle *h, const double *pose_knots, int n_knots, double min_range, double max_range, float noise,
+                         uint64_t seed, float *xyz_out, int cap, int *n_out);
 /* device pointer (stride 4) and size of the last ray-cast scan: pass them to ml_scan_upload / ml_scan_update, which use
  * device-resident input in place. Valid until the next upload of a host scan. */
 int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n);

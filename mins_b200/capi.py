@@ -78,7 +78,7 @@ SYMBOLS = [
     "ml_map_build_from_scan", "ml_map_add", "ml_map_add_scan", "ml_map_reanchor", "ml_map_flatten", "ml_map_size",
     "ml_scan_upload", "ml_scan_deskew", "ml_scan_downsample", "ml_scan_transform", "ml_scan_download", "ml_scan_set",
     "ml_knn", "ml_linsys", "ml_scan_update", "ml_point_rows", "ml_info_to_sqrt", "ml_last_timing", "ml_set_timing",
-    "ml_abi_sizes", "ml_launch_count", "ml_sim_set_world", "ml_sim_set_rays", "ml_sim_raycast", "ml_sim_scan_device",
+    "ml_abi_sizes", "ml_launch_count", "ml_sim_set_world", "ml_sim_set_rays", "ml_sim_raycast", "ml_sim_raycast_sweep", "ml_sim_scan_device",
     "ml_icp_default_options", "ml_scan_icp",
 ]
 
@@ -135,6 +135,7 @@ def load():
     lib.ml_sim_set_world.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_set_rays.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_raycast.argtypes = [vp, vp, vp, C.c_double, C.c_double, C.c_float, C.c_uint64, vp, C.c_int, ip]
+    lib.ml_sim_raycast_sweep.argtypes = [vp, vp, C.c_int, C.c_double, C.c_double, C.c_float, C.c_uint64, vp, C.c_int, ip]
     lib.ml_sim_scan_device.argtypes = [vp, C.POINTER(vp), ip]
     sizes = (C.c_int * 4)()
     lib.ml_abi_sizes(sizes)

@@ -75,6 +75,8 @@ struct ml_handle {
   int sim_n_planes = 0, sim_n_rays = 0;
   int *sim_n_out = nullptr;
   int sim_last_n = 0;
+  double *sim_knots = nullptr;
+  size_t sim_knots_cap = 0;
   // ICP pre-alignment (ml_scan_icp), allocated on first use
   uint8_t *icp_keep = nullptr;
   float4 *icp_normals = nullptr, *icp_cell_pts = nullptr, *icp_read = nullptr, *icp_q = nullptr;
@@ -351,7 +353,7 @@ void ml_destroy(ml_handle *h) {
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot, h->sim_knots};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -778,20 +780,15 @@ int ml_sim_set_rays(ml_handle *h, const double *dirs_L, int n_rays) {
   return ML_OK;
 }
 
-int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9], double min_range, double max_range, float noise,
-                   uint64_t seed, float *xyz_out, int cap, int *n_out) {
-  if (!h || !p_LinG || !R_LtoG)
-    return fail(h, ML_ERR_ARG, "ml_sim_raycast: bad argument");
-  if (!h->sim_planes || !h->sim_dirs)
-    return fail(h, ML_ERR_ARG, "ml_sim_raycast: ml_sim_set_world / ml_sim_set_rays have not been called");
-  SimPose pose;
-  for (int a = 0; a < 3; a++)
-    pose.o[a] = p_LinG[a];
-  for (int a = 0; a < 9; a++)
-    pose.R[a] = R_LtoG[a];
+static int sim_raycast_common(ml_handle *h, const SimPose &pose, const double *d_knots, int n_knots, double min_range, double max_range,
+                              float noise, uint64_t seed, float *xyz_out, int cap, int *n_out) {
   const int n = h->sim_n_rays, tiles = cdiv(n, RF_TILE);
-  LAUNCH(k_ray_cast, tiles, SIM_BLOCK, h->sim_planes, h->sim_n_planes, h->sim_dirs, n, pose, min_range, max_range, h->sim_dist,
-         h->tile_sums);
+  if (d_knots)
+    LAUNCH(k_ray_cast<true>, tiles, SIM_BLOCK, h->sim_planes, h->sim_n_planes, h->sim_dirs, n, pose, d_knots, n_knots, min_range, max_range,
+           h->sim_dist, h->tile_sums);
+  else
+    LAUNCH(k_ray_cast<false>, tiles, SIM_BLOCK, h->sim_planes, h->sim_n_planes, h->sim_dirs, n, pose, d_knots, n_knots, min_range, max_range,
+           h->sim_dist, h->tile_sums);
   LAUNCH(k_ray_emit, tiles, SIM_BLOCK, h->sim_dist, h->sim_dirs, n, h->tile_sums, noise, (uint32_t)(seed & 0xffffffffu),
          (uint32_t)(seed >> 32), reinterpret_cast<float4 *>(h->d_raw), h->sim_n_out);
   CK(cudaMemcpyAsync(&h->sim_last_n, h->sim_n_out, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
@@ -805,6 +802,41 @@ int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9],
   if (n_out)
     *n_out = h->sim_last_n;
   return ML_OK;
+}
+
+int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9], double min_range, double max_range, float noise,
+                   uint64_t seed, float *xyz_out, int cap, int *n_out) {
+  if (!h || !p_LinG || !R_LtoG)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast: bad argument");
+  if (!h->sim_planes || !h->sim_dirs)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast: ml_sim_set_world / ml_sim_set_rays have not been called");
+  SimPose pose;
+  for (int a = 0; a < 3; a++)
+    pose.o[a] = p_LinG[a];
+  for (int a = 0; a < 9; a++)
+    pose.R[a] = R_LtoG[a];
+  return sim_raycast_common(h, pose, nullptr, 0, min_range, max_range, noise, seed, xyz_out, cap, n_out);
+}
+
+int ml_sim_raycast_sweep(ml_handle *h, const double *pose_knots, int n_knots, double min_range, double max_range, float noise,
+                         uint64_t seed, float *xyz_out, int cap, int *n_out) {
+  if (!h || !pose_knots || n_knots < 2)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast_sweep: bad argument (at least 2 pose knots)");
+  if (!h->sim_planes || !h->sim_dirs)
+    return fail(h, ML_ERR_ARG, "ml_sim_raycast_sweep: ml_sim_set_world / ml_sim_set_rays have not been called");
+  const size_t need = (size_t)n_knots * 12;
+  if (need > h->sim_knots_cap) {
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->sim_knots)
+      cudaFree(h->sim_knots);
+    h->sim_knots = nullptr;
+    CK(cudaMalloc(&h->sim_knots, sizeof(double) * need));
+    h->sim_knots_cap = need;
+  }
+  CK(cudaMemcpyAsync(h->sim_knots, pose_knots, sizeof(double) * need, cudaMemcpyHostToDevice, h->stream));
+  SimPose pose;
+  memset(&pose, 0, sizeof(pose));
+  return sim_raycast_common(h, pose, h->sim_knots, n_knots, min_range, max_range, noise, seed, xyz_out, cap, n_out);
 }
 
 int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n) {

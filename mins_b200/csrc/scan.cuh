@@ -144,8 +144,8 @@ __global__ void __launch_bounds__(256) k_transform(const float4 *__restrict__ in
 
 // ---- LidarHelper::remove_motion_blur loop body, LidarHelper.cpp:71-85 ---------------------------------
 // transformPoint(p, Affine3f): ((r0*x + r1*y) + r2*z) + t. Knots: n_knots 3x4 transforms; point i sits at sweep
-// fraction 1 - (total - i)/total; with n_knots == total every point has its own transform (the reference's case),
-// otherwise the two bracketing knots are blended linearly (documented approximation).
+// fraction 1 - (total - i)/total = i/total of [t - total * raw_point_dt, t]; with n_knots == total every point has its own
+// transform (the reference's case), otherwise the two bracketing knots are blended linearly (documented approximation).
 __global__ void __launch_bounds__(256) k_deskew(float4 *__restrict__ cloud, const int *__restrict__ d_n, const float *__restrict__ knots,
                                                int n_knots, int total) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) k_deskew(float4 *__restrict__ cloud, cons
     for (int k = 0; k < 12; k++)
       T[k] = knots[(size_t)i * 12 + k];
   } else {
-    float u = (float)i / (float)(total > 1 ? total - 1 : 1) * (float)(n_knots - 1);
+    float u = (float)i / (float)total * (float)(n_knots - 1); // point i sits (total - i) * raw_point_dt before the scan time (:68)
     int k0 = min((int)u, n_knots - 2);
     float a = u - (float)k0;
 #pragma unroll

@@ -44,15 +44,21 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float *z0, fl
 }
 
 // pass 1: nearest hit distance per ray + per-tile count of rays inside [min_range, max_range]
+// SWEEP: motion distortion of Simulator.cpp:761-771 (raw_remove_motion_blur): ray i of `total` is cast from the pose at
+// time - (total - i) * raw_point_dt. The pose track arrives as n_knots poses [R_LtoG (9) | p_LinG (3)] sampled uniformly over
+// [time - total * raw_point_dt, time]; a ray blends its two bracketing knots linearly (the same rule as k_deskew).
+template <bool SWEEP>
 __global__ void __launch_bounds__(SIM_BLOCK)
     k_ray_cast(const double *__restrict__ planes, int n_planes, const double *__restrict__ dirs_L, int n_rays, SimPose pose,
-               double rmin, double rmax, double *__restrict__ dist, uint32_t *__restrict__ tile_sums) {
+               const double *__restrict__ knots, int n_knots, double rmin, double rmax, double *__restrict__ dist,
+               uint32_t *__restrict__ tile_sums) {
   __shared__ double sp[SIM_PLANES_SMEM * SIM_PLANE_STRIDE];
   __shared__ double snum[SIM_PLANES_SMEM];
   __shared__ uint32_t wsum[SIM_BLOCK / 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   double best[RF_TILE / SIM_BLOCK];
   double dg[RF_TILE / SIM_BLOCK][3];
+  double og[SWEEP ? RF_TILE / SIM_BLOCK : 1][3]; // per-ray origin (SWEEP only)
   const int base = blockIdx.x * RF_TILE;
 #pragma unroll
   for (int r = 0; r < RF_TILE / SIM_BLOCK; r++) {
@@ -61,9 +67,23 @@ __global__ void __launch_bounds__(SIM_BLOCK)
     double dx = 0, dy = 0, dz = 0;
     if (i < n_rays)
       dx = dirs_L[3 * (size_t)i], dy = dirs_L[3 * (size_t)i + 1], dz = dirs_L[3 * (size_t)i + 2];
-    dg[r][0] = pose.R[0] * dx + pose.R[1] * dy + pose.R[2] * dz;
-    dg[r][1] = pose.R[3] * dx + pose.R[4] * dy + pose.R[5] * dz;
-    dg[r][2] = pose.R[6] * dx + pose.R[7] * dy + pose.R[8] * dz;
+    if (SWEEP) {
+      double P[12];
+      const double u = (double)min(i, n_rays - 1) / (double)n_rays * (double)(n_knots - 1);
+      const int k0 = min((int)u, n_knots - 2);
+      const double a = u - (double)k0;
+#pragma unroll
+      for (int e = 0; e < 12; e++)
+        P[e] = (1.0 - a) * knots[(size_t)k0 * 12 + e] + a * knots[(size_t)(k0 + 1) * 12 + e];
+      dg[r][0] = P[0] * dx + P[1] * dy + P[2] * dz;
+      dg[r][1] = P[3] * dx + P[4] * dy + P[5] * dz;
+      dg[r][2] = P[6] * dx + P[7] * dy + P[8] * dz;
+      og[r][0] = P[9], og[r][1] = P[10], og[r][2] = P[11];
+    } else {
+      dg[r][0] = pose.R[0] * dx + pose.R[1] * dy + pose.R[2] * dz;
+      dg[r][1] = pose.R[3] * dx + pose.R[4] * dy + pose.R[5] * dz;
+      dg[r][2] = pose.R[6] * dx + pose.R[7] * dy + pose.R[8] * dz;
+    }
   }
   for (int p0 = 0; p0 < n_planes; p0 += SIM_PLANES_SMEM) {
     const int np = min(SIM_PLANES_SMEM, n_planes - p0);
@@ -78,11 +98,13 @@ __global__ void __launch_bounds__(SIM_BLOCK)
     __syncthreads();
     for (int p = 0; p < np; p++) {
       const double *q = sp + p * SIM_PLANE_STRIDE;
-      const double A = q[0], B = q[1], C = q[2], num = snum[p];
+      const double A = q[0], B = q[1], C = q[2];
 #pragma unroll
       for (int r = 0; r < RF_TILE / SIM_BLOCK; r++) {
+        const double ox = SWEEP ? og[r][0] : pose.o[0], oy = SWEEP ? og[r][1] : pose.o[1], oz = SWEEP ? og[r][2] : pose.o[2];
+        const double num = SWEEP ? -(A * ox + B * oy + C * oz + q[3]) : snum[p];
         const double t = num / (A * dg[r][0] + B * dg[r][1] + C * dg[r][2]);
-        const double px = pose.o[0] + t * dg[r][0], py = pose.o[1] + t * dg[r][1], pz = pose.o[2] + t * dg[r][2];
+        const double px = ox + t * dg[r][0], py = oy + t * dg[r][1], pz = oz + t * dg[r][2];
         const double u1x = px - q[4], u1y = py - q[5], u1z = pz - q[6];
         const double u2x = px - q[7], u2y = py - q[8], u2z = pz - q[9];
         const bool hit = t > 0.0 && (u1x * q[10] + u1y * q[11] + u1z * q[12]) > 0.0 && (u1x * q[13] + u1y * q[14] + u1z * q[15]) > 0.0 &&

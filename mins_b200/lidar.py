@@ -307,6 +307,15 @@ class LidarMap:
                                          out.ctypes.data if download else None, self._sim_rays if download else 0, C.byref(n)))
         return out[:n.value] if download else n.value
 
+    def sim_raycast_sweep(self, pose_knots, min_range, max_range, noise=0.0, seed=0):
+        """Motion-distorted scan (Simulator.cpp:761-771). pose_knots: (n_knots, 12) [R_LtoG row-major | p_LinG]."""
+        k = _f64(pose_knots).reshape(-1, 12)
+        n = C.c_int()
+        out = np.zeros((self._sim_rays, 4), np.float32)
+        self._ck(self.lib.ml_sim_raycast_sweep(self.h, k.ctypes.data, len(k), min_range, max_range, noise, int(seed), out.ctypes.data,
+                                               self._sim_rays, C.byref(n)))
+        return out[:n.value]
+
     def sim_scan_device(self):
         """(device pointer, n) of the last ray-cast scan, to pass as `xyz` of ml_scan_update (stride 4)."""
         ptr, n = C.c_void_p(), C.c_int()

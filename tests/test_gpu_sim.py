@@ -124,3 +124,48 @@ def test_raycast_with_more_planes_than_one_shared_memory_pass(sim_map, po):
     # a range gate nothing passes
     none = sim_map.sim_raycast(p, R, 1000.0, 2000.0)
     assert none.shape == (0, 4)
+
+
+def test_motion_distorted_scan_is_undone_by_deskew(sim_map):
+    """§8f N4 with the simulator's distortion model (Simulator.cpp:761-771): a scan ray-cast from a moving sensor
+    (ml_sim_raycast_sweep) and de-skewed with the same pose track (ml_scan_deskew, the loop body of LidarHelper.cpp:71-85)
+    lands on the world points expressed in the end-of-sweep frame."""
+    from mins_b200.lidar import OptionsLidar
+    from mins_b200.sim.se3 import exp_so3
+    from mins_b200.sim.world import PlaneWorld, lidar_ray_dirs, synthetic_floorplan
+    world = PlaneWorld(synthetic_floorplan(0))
+    dirs = lidar_ray_dirs(np.arange(-80, 81, 10), -180, 180, 2.0)
+    n, K = len(dirs), 33
+    R0, p0 = exp_so3(np.array([0.02, -0.01, 0.3])), np.array([0.5, -1.0, 1.0])
+    w, v = np.array([0.05, -0.1, 0.6]), np.array([1.0, 0.4, 0.05])           # rad and m over the sweep
+    Rk = [R0 @ exp_so3(w * s) for s in np.linspace(0, 1, K)]
+    pk = [p0 + v * s for s in np.linspace(0, 1, K)]
+    knots = np.array([np.r_[R.ravel(), p] for R, p in zip(Rk, pk)])
+    sim_map.sim_set_world(world.packed())
+    sim_map.sim_set_rays(dirs)
+    skewed = sim_map.sim_raycast_sweep(knots, 0.01, 200.0)
+    static = sim_map.sim_raycast(pk[-1], Rk[-1], 0.01, 200.0)
+    assert len(skewed) == len(static) == n                                    # closed hall: every ray returns
+    # ground truth on the host: the world point of ray i, expressed in the end frame
+    u = np.arange(n) / n * (K - 1)
+    k0 = np.minimum(u.astype(int), K - 2)
+    a = (u - k0)[:, None]
+    P = (1 - a) * knots[k0] + a * knots[k0 + 1]
+    Ri, oi = P[:, :9].reshape(n, 3, 3), P[:, 9:]
+    world_pts = np.einsum("nij,nj->ni", Ri, skewed[:, :3].astype(np.float64)) + oi
+    want = (world_pts - pk[-1]) @ Rk[-1]
+    # estimator side: T_LitoL = [R_end^T R_i | R_end^T (p_i - p_end)] (LidarHelper.cpp:73-79), fp32 knots
+    T = np.zeros((K, 3, 4), np.float32)
+    for j in range(K):
+        T[j, :, :3] = Rk[-1].T @ Rk[j]
+        T[j, :, 3] = Rk[-1].T @ (pk[j] - pk[-1])
+    op = OptionsLidar(min_range=0.01, max_range=200.0)
+    assert sim_map.feed_scan(skewed, 0.0, op) == n
+    sim_map.deskew(T.reshape(K, 12), n)
+    got = sim_map.scan(0)[:, :3]
+    assert np.abs(got - want).max() < 2e-4                                    # fp32 knots and transform at ~20 m range
+    assert np.abs(skewed[:, :3] - want).max() > 0.3                           # without de-skewing the error is decimetres
+    # every de-skewed point lies on a wall/floor/ceiling plane of the world
+    pw = got.astype(np.float64) @ Rk[-1].T + pk[-1]
+    A = world.abcd / np.linalg.norm(world.abcd[:, :3], axis=1, keepdims=True)
+    assert np.abs(pw @ A[:, :3].T + A[:, 3]).min(1).max() < 3e-4
