@@ -251,7 +251,8 @@ int ml_info_to_sqrt(const double *HtH, const double *Htr, int total_hx, double *
 
 /* device-time (ms, CUDA events on the handle's stream) of the stages of the last ml_linsys / ml_scan_update:
  * [0] upload+range filter (+ transform when not down-sampling), [1] downsample, [2] transform, [3] query binning, [4] knn,
- * [5] rows + reduction + finalize (one fused kernel), [6] D2H of the result block, [7] total */
+ * [5] rows + reduction + finalize (one fused kernel), [6] 0 (the kernel of [5] writes the result block straight into pinned
+ * host memory; there is no separate D2H copy), [7] total */
 int ml_last_timing(ml_handle *h, float ms[8]);
 /* CUDA-event timers: 0 = off, 1 = per-stage (default; diagnostic - the event records between kernels serialise the
  * programmatically dependent launches of the pipeline), 2 = total only ([7]; the other entries read 0) */

@@ -96,12 +96,10 @@ struct ml_handle {
   float *knn_d2 = nullptr;
   uint8_t *knn_ok = nullptr;
   DevConsts *d_consts = nullptr;
-  double *d_P = nullptr;
   PointRow *rows = nullptr;
   RRParts *parts = nullptr;
   unsigned int *ticket = nullptr;
   bool rows_exported = false;
-  LinsysOut *d_out = nullptr;
   // pinned host mirrors
   struct HostIn {
     ml_scan_consts c;
@@ -329,12 +327,10 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->knn_d2, sizeof(float) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->knn_ok, cs));
   CK(cudaMalloc(&h->d_consts, sizeof(DevConsts)));
-  CK(cudaMalloc(&h->d_P, sizeof(double) * ML_MAX_HX * ML_MAX_HX));
   CK(cudaMalloc(&h->rows, sizeof(PointRow) * cs));
   CK(cudaMalloc(&h->parts, sizeof(RRParts)));
   CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
   CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
-  CK(cudaMalloc(&h->d_out, sizeof(LinsysOut)));
   CK(cudaMallocHost(&h->h_in, sizeof(*h->h_in)));
   CK(cudaMallocHost(&h->h_out, sizeof(LinsysOut)));
   memset(&h->grid_host, 0, sizeof(GridDesc));
@@ -351,7 +347,7 @@ void ml_destroy(ml_handle *h) {
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
-                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->d_P, h->rows, h->parts, h->ticket, h->d_out,
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->rows, h->parts, h->ticket,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
                  h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot, h->sim_knots};
   for (void *p : dev)
