@@ -42,12 +42,11 @@ struct ml_handle {
   int map_n = 0;
   bool map_init = false;
   GridDesc *d_grid = nullptr;
-  GridDesc grid_host;
   uint32_t *d_bbox = nullptr;
   uint32_t *cell_cnt = nullptr, *cell_start = nullptr;
   float4 *cell_pts = nullptr;
   uint32_t *pt_cell = nullptr, *pt_rank = nullptr;
-  uint32_t *tile_sums = nullptr;
+  uint32_t *tile_sums = nullptr; // per-tile counts of the two-launch compactions (range filter fallback, simulator)
   VoxSlot *vox_tab = nullptr;
   int vox_slots = 0;
   uint32_t *add_slot = nullptr, *contender = nullptr, *keep = nullptr, *pos = nullptr;
@@ -58,9 +57,13 @@ struct ml_handle {
   float *h_raw = nullptr; // pinned staging
   float4 *scan_pts = nullptr, *scan_orig = nullptr, *scan_map = nullptr, *scan_tmp = nullptr;
   ScanState *d_st = nullptr;
-  unsigned long long *lb_state = nullptr; // decoupled look-back tile states of k_range_filter_bin
-  unsigned int *lb_ctr = nullptr;         // its tile ticket (monotonic; lb_tickets = tickets handed out so far)
-  unsigned int lb_tickets = 0, lb_epoch = 0;
+  // decoupled look-back (prims.cuh), shared by every single-pass scan/compaction on the handle's stream: tile states
+  // (epoch-tagged, never reset), tile ticket (back at 0 after each launch), epoch of the last launch
+  unsigned long long *lb_state = nullptr;
+  unsigned int *lb_ctr = nullptr;
+  unsigned int lb_epoch = 0;
+  unsigned int *mg_done = nullptr;  // k_map_merge: CTAs finished
+  MergeResult *h_merge = nullptr;   // pinned: result block of the last k_map_merge
   bool bin_done = false; // the queries of the resident scan are already in the hash table (fused front end)
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
@@ -181,11 +184,17 @@ static int check_launch(ml_handle *h) {
   return ML_OK;
 }
 
-// exclusive scan of `in` (n on device) into out[0..n]; total optionally to d_total. n_ub = host upper bound.
-static void excl_scan(ml_handle *h, const uint32_t *in, const int *d_n, int n_ub, uint32_t *out, int *d_total) {
+static uint32_t lb_next_epoch(ml_handle *h) {
+  h->lb_epoch = (h->lb_epoch + 1u) & 0x3fffffffu;
+  if (h->lb_epoch == 0u)
+    h->lb_epoch = 1u;
+  return h->lb_epoch;
+}
+
+// exclusive scan of `in` (n on device) into out[0..n], one pass; total optionally to d_total. n_ub = host upper bound.
+static void excl_scan(ml_handle *h, uint32_t *in, const int *d_n, int n_ub, uint32_t *out, int *d_total) {
   int tiles = std::max(1, cdiv(n_ub, SCAN_TILE));
-  LAUNCH(k_scan_reduce, tiles, SCAN_BLOCK, in, d_n, h->tile_sums);
-  LAUNCH(k_scan_apply, tiles, SCAN_BLOCK, in, d_n, h->tile_sums, out, d_total);
+  LAUNCH((k_scan_lb<SCAN_ITEMS, false>), tiles, SCAN_BLOCK, in, d_n, out, d_total, h->lb_state, h->lb_ctr, lb_next_epoch(h));
 }
 
 // stable sort of (keys, vals) by key; result ends in sort_keys[0]/sort_vals[0]. bits = number of key bits to sort.
@@ -204,6 +213,20 @@ static void radix_sort(ml_handle *h, const int *d_n, int n_ub, int bits) {
   }
 }
 
+// dense kNN grid over map_pts[cur] from the descriptor in d_grid: cell histogram -> one-pass scan over the cells -> scatter.
+// Nothing here waits for the device: launches are sized by host-side upper bounds (n_ub points, cap_cells cells), the device
+// descriptor is authoritative and surplus CTAs leave at once.
+static int grid_build_tail(ml_handle *h, int n_ub) {
+  if (n_ub <= 0)
+    return ML_OK;
+  LAUNCH(k_cell_count, cdiv(n_ub, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_cnt, h->pt_cell, h->pt_rank);
+  // cell_start = exclusive scan of the counters, which the same pass leaves all-zero for the next build
+  LAUNCH((k_scan_lb<SCAN_ITEMS_LONG, true>), std::max(1, cdiv(h->cap_cells, SCAN_TILE_LONG)), SCAN_BLOCK, h->cell_cnt, &h->d_grid->ncells,
+         h->cell_start, (int *)nullptr, h->lb_state, h->lb_ctr, lb_next_epoch(h));
+  LAUNCH(k_cell_scatter, cdiv(n_ub, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_start, h->pt_cell, h->pt_rank, h->cell_pts);
+  return check_launch(h);
+}
+
 // (re)build the dense kNN grid over map_pts[cur] (n = *d_map_n, host copy h->map_n)
 static int rebuild_grid(ml_handle *h) {
   const int n = h->map_n;
@@ -211,22 +234,31 @@ static int rebuild_grid(ml_handle *h) {
   if (n > 0)
     LAUNCH(k_bbox, std::min(148 * 8, cdiv(n, 256)), 256, h->map_pts[h->cur], h->d_map_n, h->d_bbox);
   LAUNCH(k_grid_setup, 1, 32, h->d_bbox, h->d_map_n, h->grid_cell, h->cap_cells, h->d_grid);
-  CK(cudaMemcpyAsync(&h->grid_host, h->d_grid, sizeof(GridDesc), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
   h->map_init = n > 0;
-  if (n <= 0)
-    return ML_OK;
-  const int nc = h->grid_host.ncells;
-  LAUNCH(k_zero_cells, std::min(148 * 8, cdiv(nc + 1, 256)), 256, h->cell_cnt, h->d_grid);
-  LAUNCH(k_cell_count, cdiv(n, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_cnt, h->pt_cell, h->pt_rank);
-  excl_scan(h, h->cell_cnt, &h->d_grid->ncells, nc, h->cell_start, nullptr);
-  LAUNCH(k_cell_scatter, cdiv(n, 256), 256, h->map_pts[h->cur], h->d_grid, h->cell_start, h->pt_cell, h->pt_rank, h->cell_pts);
-  return check_launch(h);
+  return grid_build_tail(h, n);
 }
 
-static int sync_map_n(ml_handle *h) {
-  CK(cudaMemcpyAsync(&h->map_n, h->d_map_n, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+// one-pass merge of the survivors of [a | b] into the other map buffer + bbox + grid descriptor (k_map_merge), then the grid
+// over it; ONE wait at the end for the result block. Flips the double buffer unless the capacity was exceeded.
+template <int MODE>
+static int merge_into_map(ml_handle *h, const float4 *a, const int *d_na, const float4 *b, const int *d_nb, int n_ub, const char *who) {
+  LAUNCH(k_bbox_init, 1, 32, h->d_bbox);
+  LAUNCH(k_map_merge<MODE>, std::max(1, cdiv(n_ub, MG_TILE)), MG_BLOCK, a, d_na, b, d_nb, h->vox_tab, h->contender, h->add_slot, h->keep,
+         h->map_pts[1 - h->cur], h->cap_map, h->lb_state, h->lb_ctr, lb_next_epoch(h), h->d_bbox, h->mg_done, h->d_ints + 3, h->grid_cell,
+         h->cap_cells, h->d_grid, h->d_map_n, h->h_merge);
+  h->cur = 1 - h->cur;
+  int rc = grid_build_tail(h, std::min(n_ub, h->cap_map));
   CK(cudaStreamSynchronize(h->stream));
+  if (rc)
+    return rc;
+  if (h->h_merge->overflow) { // the previous buffer and *d_map_n are untouched: put its grid back
+    h->cur = 1 - h->cur;
+    rc = rebuild_grid(h);
+    h->err = std::string(who) + ": map capacity (max_map_points) exceeded";
+    return rc ? rc : ML_ERR_CAPACITY;
+  }
+  h->map_n = h->h_merge->n_out;
+  h->map_init = h->map_n > 0;
   return ML_OK;
 }
 
@@ -280,8 +312,8 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->cell_pts, sizeof(float4) * ca));
   CK(cudaMalloc(&h->pt_cell, sizeof(uint32_t) * ca));
   CK(cudaMalloc(&h->pt_rank, sizeof(uint32_t) * ca));
-  const size_t max_scan_len = std::max((size_t)h->cap_cells + 2, ca + 2);
-  CK(cudaMalloc(&h->tile_sums, sizeof(uint32_t) * (max_scan_len / SCAN_TILE + 2)));
+  CK(cudaMemset(h->cell_cnt, 0, sizeof(uint32_t) * ((size_t)h->cap_cells + 2))); // all-zero between grid builds (k_scan_lb<.., true>)
+  CK(cudaMalloc(&h->tile_sums, sizeof(uint32_t) * (cs / RF_TILE + 4)));
   h->vox_slots = 1;
   while ((size_t)h->vox_slots < 2 * cs)
     h->vox_slots <<= 1;
@@ -301,10 +333,15 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->scan_tmp, sizeof(float4) * ca));
   CK(cudaMalloc(&h->d_st, sizeof(ScanState)));
   CK(cudaMemset(h->d_st, 0, sizeof(ScanState)));
-  CK(cudaMalloc(&h->lb_state, sizeof(unsigned long long) * (cs / RF_TILE + 2)));
-  CK(cudaMemset(h->lb_state, 0, sizeof(unsigned long long) * (cs / RF_TILE + 2)));
+  const size_t lb_tiles = std::max(std::max((size_t)h->cap_cells / SCAN_TILE, ca / SCAN_TILE), std::max(ca / MG_TILE, cs / RF_TILE)) + 4;
+  CK(cudaMalloc(&h->lb_state, sizeof(unsigned long long) * lb_tiles));
+  CK(cudaMemset(h->lb_state, 0, sizeof(unsigned long long) * lb_tiles));
   CK(cudaMalloc(&h->lb_ctr, sizeof(unsigned int)));
   CK(cudaMemset(h->lb_ctr, 0, sizeof(unsigned int)));
+  CK(cudaMalloc(&h->mg_done, sizeof(unsigned int)));
+  CK(cudaMemset(h->mg_done, 0, sizeof(unsigned int)));
+  CK(cudaMallocHost(&h->h_merge, sizeof(MergeResult)));
+  memset(h->h_merge, 0, sizeof(MergeResult));
   for (int b = 0; b < 2; b++) {
     CK(cudaMalloc(&h->sort_keys[b], sizeof(uint32_t) * ca));
     CK(cudaMalloc(&h->sort_vals[b], sizeof(uint32_t) * ca));
@@ -333,7 +370,6 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
   CK(cudaMallocHost(&h->h_in, sizeof(*h->h_in)));
   CK(cudaMallocHost(&h->h_out, sizeof(LinsysOut)));
-  memset(&h->grid_host, 0, sizeof(GridDesc));
   *out = h;
   return ML_OK;
 }
@@ -349,7 +385,7 @@ void ml_destroy(ml_handle *h) {
                  h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->rows, h->parts, h->ticket,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot, h->sim_knots};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot, h->sim_knots, h->mg_done};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -412,8 +448,9 @@ int ml_map_build_from_scan(ml_handle *h) {
   return rebuild_grid(h);
 }
 
-// shared tail of ml_map_add / ml_map_add_scan: add_pts[0..*d_ints[0]) (host upper bound n_ub) into the map
-static int map_add_device(ml_handle *h, int n_ub, int downsample, float ds, int *n_live) {
+// shared tail of ml_map_add / ml_map_add_scan: *d_nadd new points (host upper bound n_ub) into the map. xf_src != NULL: the new
+// points are xf_src[] in the sensor frame, transformed by T_LtoM into add_pts on the way (ml_map_add_scan); else add_pts holds them.
+static int map_add_device(ml_handle *h, const float4 *xf_src, const int *d_nadd, int n_ub, int downsample, float ds, int *n_live) {
   if (n_ub <= 0) {
     if (n_live)
       *n_live = h->map_n;
@@ -422,30 +459,22 @@ static int map_add_device(ml_handle *h, int n_ub, int downsample, float ds, int 
   if (downsample && !(ds > 0.f))
     return fail(h, ML_ERR_ARG, "ml_map_add: downsample size must be positive");
   const int M = h->map_n;
-  int *d_nadd = h->d_ints + 0, *d_total = h->d_ints + 1, *d_ovf = h->d_ints + 2;
-  const uint32_t mask = (uint32_t)h->vox_slots - 1u;
-  LAUNCH(k_set_int, 1, 1, d_ovf, 0);
+  int rc;
   if (downsample) {
+    const uint32_t mask = (uint32_t)h->vox_slots - 1u;
     LAUNCH(k_vox_clear, std::min(148 * 8, cdiv(h->vox_slots, 256)), 256, h->vox_tab, h->vox_slots);
-    LAUNCH(k_vox_insert_new, cdiv(n_ub, 256), 256, h->add_pts, d_nadd, h->d_map_n, ds, h->vox_tab, mask, h->add_slot);
+    if (xf_src)
+      LAUNCH(k_vox_insert_new<true>, cdiv(n_ub, 256), 256, xf_src, h->T_LtoM, h->add_pts, d_nadd, h->d_map_n, ds, h->vox_tab, mask, h->add_slot);
+    else
+      LAUNCH(k_vox_insert_new<false>, cdiv(n_ub, 256), 256, xf_src, h->T_LtoM, h->add_pts, d_nadd, h->d_map_n, ds, h->vox_tab, mask, h->add_slot);
     if (M > 0)
       LAUNCH(k_vox_compete_old, cdiv(M, 256), 256, h->map_pts[h->cur], h->d_map_n, ds, h->vox_tab, mask, h->contender);
+    rc = merge_into_map<MG_VOX>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add");
+  } else {
+    if (xf_src)
+      LAUNCH(k_transform, cdiv(n_ub, 256), 256, xf_src, d_nadd, h->T_LtoM, h->add_pts);
+    rc = merge_into_map<MG_ALL>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add");
   }
-  LAUNCH(k_vox_flags, cdiv(M + n_ub, 256), 256, h->d_map_n, d_nadd, h->vox_tab, h->contender, h->add_slot, downsample, h->keep, d_total);
-  excl_scan(h, h->keep, d_total, M + n_ub, h->pos, h->d_ints + 3);
-  LAUNCH(k_compact2, cdiv(M + n_ub, 256), 256, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, h->keep, h->pos, h->map_pts[1 - h->cur],
-         h->cap_map, d_ovf);
-  LAUNCH(k_copy_int, 1, 1, h->d_map_n, h->d_ints + 3);
-  int host_ints[4];
-  CK(cudaMemcpyAsync(host_ints, h->d_ints, sizeof(host_ints), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
-  if (host_ints[2] || host_ints[3] > h->cap_map) {
-    LAUNCH(k_set_int, 1, 1, h->d_map_n, h->map_n); // the map itself is untouched (double-buffered): restore its count
-    return fail(h, ML_ERR_CAPACITY, "ml_map_add: map capacity (max_map_points) exceeded");
-  }
-  h->cur = 1 - h->cur;
-  h->map_n = host_ints[3];
-  int rc = rebuild_grid(h);
   if (n_live)
     *n_live = h->map_n;
   return rc;
@@ -459,7 +488,7 @@ int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds,
   if (n > 0)
     CK(cudaMemcpyAsync(h->add_pts, xyzi, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, h->stream));
   LAUNCH(k_set_int, 1, 1, h->d_ints + 0, n);
-  return map_add_device(h, n, downsample, ds, n_live);
+  return map_add_device(h, nullptr, h->d_ints + 0, n, downsample, ds, n_live);
 }
 
 int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
@@ -467,10 +496,7 @@ int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
     return ML_ERR_ARG;
   if (!h->have_T)
     return fail(h, ML_ERR_ARG, "ml_map_add_scan: ml_scan_transform has not been called for this scan");
-  if (h->n_raw > 0)
-    LAUNCH(k_transform, cdiv(h->n_raw, 256), 256, h->scan_orig, ST(n_orig), h->T_LtoM, h->add_pts);
-  LAUNCH(k_copy_int, 1, 1, h->d_ints + 0, ST(n_orig));
-  return map_add_device(h, h->n_raw, downsample, ds, n_live);
+  return map_add_device(h, h->scan_orig, ST(n_orig), h->n_raw, downsample, ds, n_live);
 }
 
 // voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated. n_ub host bound. tmp buffers: sort_*, keep, pos.
@@ -512,18 +538,9 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
   ReanchorArgs a;
   memcpy(a.T, T, sizeof(a.T));
   a.now_minus_FT = now_minus_FT, a.decay_time = decay_time, a.decay_dist = decay_dist;
-  // transformed copy into cell_pts (free scratch: the grid is rebuilt below), keep flags, stable compaction
+  // transformed copy into cell_pts (free scratch: the grid is rebuilt below) + keep flags, then the one-pass merge
   LAUNCH(k_reanchor, cdiv(M, 256), 256, src, d_n, a, h->cell_pts, h->keep);
-  excl_scan(h, h->keep, d_n, M, h->pos, h->d_ints + 3);
-  LAUNCH(k_set_int, 1, 1, h->d_ints + 2, 0);
-  LAUNCH(k_compact2, cdiv(M, 256), 256, h->cell_pts, d_n, (const float4 *)nullptr, (const int *)nullptr, h->keep, h->pos,
-         h->map_pts[1 - h->cur], h->cap_map, h->d_ints + 2);
-  LAUNCH(k_copy_int, 1, 1, h->d_map_n, h->d_ints + 3);
-  h->cur = 1 - h->cur;
-  int rc = sync_map_n(h);
-  if (rc)
-    return rc;
-  rc = rebuild_grid(h);
+  int rc = merge_into_map<MG_FLAGS>(h, h->cell_pts, d_n, (const float4 *)nullptr, (const int *)nullptr, M, "ml_map_reanchor");
   if (n_live)
     *n_live = h->map_n;
   return rc;
@@ -598,18 +615,14 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   float4 *in_map = T_LtoM ? h->scan_map : nullptr;
   if (T_LtoM && h->map_init && h->use_fused_front) {
     // one launch: range filter (single-pass stable compaction) + transform + query binning
-    const unsigned int base = h->lb_tickets;
-    h->lb_tickets += (unsigned int)tiles;
-    h->lb_epoch = (h->lb_epoch + 1u) & 0x3fffffffu;
-    if (h->lb_epoch == 0u)
-      h->lb_epoch = 1u;
+    const uint32_t epoch = lb_next_epoch(h);
     const uint32_t mask = (uint32_t)h->q_slots - 1u;
     if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0)
       LAUNCHP(k_range_filter_bin<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
-              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, base, h->lb_epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
     else
       LAUNCHP(k_range_filter_bin<false>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
-              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, base, h->lb_epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
     h->bin_done = true;
     return check_launch(h);
   }

@@ -21,6 +21,20 @@ __device__ __forceinline__ float norm3_ref(float x, float y, float z) {
   return __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z))));
 }
 
+// ---- pcl::transformPointCloud(cloud, cloud_in_map, Matrix4f), LidarHelper.cpp:192,203 -----------------
+// row-major 3x4 fp32 rigid transform. PCL 1.10 SSE path: m0*x + (m1*y + (m2*z + m3)) per row, fp32, no FMA.
+struct Tf32 {
+  float m[12];
+};
+__device__ __forceinline__ float4 tf_apply(const Tf32 &T, float4 p) {
+  float4 q;
+  q.x = __fadd_rn(__fmul_rn(T.m[0], p.x), __fadd_rn(__fmul_rn(T.m[1], p.y), __fadd_rn(__fmul_rn(T.m[2], p.z), T.m[3])));
+  q.y = __fadd_rn(__fmul_rn(T.m[4], p.x), __fadd_rn(__fmul_rn(T.m[5], p.y), __fadd_rn(__fmul_rn(T.m[6], p.z), T.m[7])));
+  q.z = __fadd_rn(__fmul_rn(T.m[8], p.x), __fadd_rn(__fmul_rn(T.m[9], p.y), __fadd_rn(__fmul_rn(T.m[10], p.z), T.m[11])));
+  q.w = p.w;
+  return q;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Programmatic dependent launch (sm_90+): the kernels of the per-scan pipeline are launched with
 // cudaLaunchAttributeProgrammaticStreamSerialization, call pdl_launch() first thing (the next kernel's CTAs may become

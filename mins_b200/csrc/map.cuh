@@ -62,11 +62,7 @@ __global__ void __launch_bounds__(256) k_bbox(const float4 *__restrict__ pts, co
 }
 
 // one thread: choose origin/dims; the cell edge doubles until the grid fits max_cells.
-__global__ void k_grid_setup(const uint32_t *__restrict__ bbox, const int *__restrict__ d_n, double cell0, int max_cells,
-                             GridDesc *__restrict__ g) {
-  if (threadIdx.x != 0 || blockIdx.x != 0)
-    return;
-  const int n = *d_n;
+__device__ __forceinline__ void grid_setup_dev(const uint32_t *bbox, int n, double cell0, int max_cells, GridDesc *g) {
   g->n_pts = n;
   if (n <= 0) {
     g->valid = 0;
@@ -102,11 +98,10 @@ __global__ void k_grid_setup(const uint32_t *__restrict__ bbox, const int *__res
   g->inv_cell = 1.0 / cell;
   g->valid = 1;
 }
-
-__global__ void __launch_bounds__(256) k_zero_cells(uint32_t *__restrict__ cnt, const GridDesc *__restrict__ g) {
-  const int n = g->ncells + 1;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    cnt[i] = 0;
+__global__ void k_grid_setup(const uint32_t *__restrict__ bbox, const int *__restrict__ d_n, double cell0, int max_cells,
+                             GridDesc *__restrict__ g) {
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+    grid_setup_dev(bbox, *d_n, cell0, max_cells, g);
 }
 
 __device__ __forceinline__ int cell_of(const GridDesc &g, float x, float y, float z) {
@@ -187,15 +182,23 @@ __global__ void __launch_bounds__(256) k_vox_clear(VoxSlot *__restrict__ tab, in
   }
 }
 
-// new points claim their voxel slot and compete
-__global__ void __launch_bounds__(256) k_vox_insert_new(const float4 *__restrict__ add, const int *__restrict__ d_nadd,
-                                                       const int *__restrict__ d_M, float ds, VoxSlot *__restrict__ tab,
-                                                       uint32_t mask, uint32_t *__restrict__ add_slot) {
+// new points claim their voxel slot and compete. XF: the new points are pointcloud_original still in the sensor frame;
+// transform them (LidarHelper.cpp:203) on the way and leave the transformed copy in `add` for the merge.
+template <bool XF>
+__global__ void __launch_bounds__(256) k_vox_insert_new(const float4 *__restrict__ src, Tf32 T, float4 *__restrict__ add,
+                                                       const int *__restrict__ d_nadd, const int *__restrict__ d_M, float ds,
+                                                       VoxSlot *__restrict__ tab, uint32_t mask, uint32_t *__restrict__ add_slot) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= *d_nadd)
     return;
   const int M = *d_M;
-  float4 p = add[i];
+  float4 p;
+  if (XF) {
+    p = tf_apply(T, src[i]);
+    add[i] = p;
+  } else {
+    p = add[i];
+  }
   int kx, ky, kz;
   unsigned long long key = vox_key(p.x, p.y, p.z, ds, &kx, &ky, &kz);
   float bmin, bmax, mx, my, mz;
@@ -253,49 +256,159 @@ __global__ void __launch_bounds__(256) k_vox_compete_old(const float4 *__restric
   contender[m] = found;
 }
 
-// keep[] over the concatenation [existing (M) | new (nadd)]; d_total = M + nadd
-__global__ void __launch_bounds__(256) k_vox_flags(const int *__restrict__ d_M, const int *__restrict__ d_nadd,
-                                                  const VoxSlot *__restrict__ tab, const uint32_t *__restrict__ contender,
-                                                  const uint32_t *__restrict__ add_slot, int downsample, uint32_t *__restrict__ keep,
-                                                  int *__restrict__ d_total) {
-  const int M = *d_M, na = *d_nadd;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0)
-    *d_total = M + na;
-  if (i >= M + na)
-    return;
-  uint32_t k = 1;
-  if (downsample) {
-    if (i < M) {
-      uint32_t c = contender[i];
-      if (c) {
-        uint32_t seq = 0xffffffffu - (uint32_t)(tab[c - 1].best & 0xffffffffull);
-        k = (seq == (uint32_t)i) ? 1u : 0u;
+// ------------------------------------------------------------------------------------------------
+// One-pass map merge: survivors of [a (na) | b (nb)] stably compacted into `out`, the bounding box of the survivors, and -
+// by the CTA that finishes last - the new point count, the kNN grid descriptor and a result block in pinned host memory.
+// Replaces keep-flag, 2-kernel scan, compaction, count copy, bbox init, bbox and grid set-up launches (8 -> 1) and two of the
+// three passes over the map. Survivor rule by MODE:
+//   MG_ALL   every point (Add_Points without down-sampling)
+//   MG_VOX   the per-voxel contest of ikd_Tree.cpp:401-479 decided in `tab` (see above)
+//   MG_FLAGS keep[i] != 0 (re-anchor: decay filters)
+// Stable order = decoupled look-back over MG_TILE-point tiles (prims.cuh). `bbox` must hold the k_bbox_init values on entry.
+// ------------------------------------------------------------------------------------------------
+enum { MG_ALL = 0, MG_VOX = 1, MG_FLAGS = 2 };
+constexpr int MG_BLOCK = 256, MG_ROWS = 8, MG_TILE = MG_BLOCK * MG_ROWS; // 2048-point tiles (4 / 8 / 16 rows measured: 31 -> 21 / 21 / 24 us)
+struct MergeResult { // pinned host memory, written by the last CTA
+  int n_in, n_out, overflow, ncells;
+};
+template <int MODE>
+__global__ void __launch_bounds__(MG_BLOCK)
+    k_map_merge(const float4 *__restrict__ a, const int *d_na, const float4 *__restrict__ b, const int *__restrict__ d_nb,
+                const VoxSlot *__restrict__ tab, const uint32_t *__restrict__ contender, const uint32_t *__restrict__ add_slot,
+                const uint32_t *__restrict__ keep, float4 *__restrict__ out, int cap, unsigned long long *tile_state,
+                unsigned int *tile_ctr, uint32_t epoch, uint32_t *bbox, unsigned int *done_ctr,
+                int *d_total, double cell0, int max_cells, GridDesc *g, int *d_map_n, MergeResult *res) {
+  __shared__ uint32_t wsum[MG_BLOCK / 32];
+  __shared__ uint32_t s_tile, s_prefix, s_last;
+  __shared__ float smn[MG_BLOCK / 32][3], smx[MG_BLOCK / 32][3];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int na = *d_na, nb = d_nb ? *d_nb : 0, n = na + nb;
+  const uint32_t active = n > 0 ? (uint32_t)((n + MG_TILE - 1) / MG_TILE) : 1u;
+  if (blockIdx.x < active) { // CTA-uniform; the launch is sized by a host-side upper bound of n
+    if (threadIdx.x == 0)
+      s_tile = lb_ticket(tile_ctr, active);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const long long tbase = (long long)tile * MG_TILE;
+    const int wbase = (int)tbase + wid * (MG_TILE / (MG_BLOCK / 32));
+    // three unrolled phases so that the loads of all rows are in flight together (a ballot per row in the same loop would
+    // serialise them: 16 dependent round trips instead of 2)
+    float4 pt[MG_ROWS];
+    uint32_t sel[MG_ROWS]; // MG_VOX: voxel slot + 1 whose winner decides (0: not contested); MG_FLAGS: keep flag
+    uint32_t bal[MG_ROWS];
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int r = 0; r < MG_ROWS; r++) {
+      const int i = wbase + r * 32 + lane;
+      sel[r] = 0u;
+      if (i < n) {
+        pt[r] = i < na ? a[i] : b[i - na];
+        if (MODE == MG_VOX)
+          sel[r] = i < na ? contender[i] : add_slot[i - na] + 1u;
+        else if (MODE == MG_FLAGS)
+          sel[r] = keep[i];
       }
-    } else {
-      uint32_t seq = 0xffffffffu - (uint32_t)(tab[add_slot[i - M]].best & 0xffffffffull);
-      k = (seq == (uint32_t)i) ? 1u : 0u;
+    }
+    if (MODE == MG_VOX) {
+#pragma unroll
+      for (int r = 0; r < MG_ROWS; r++) {
+        const int i = wbase + r * 32 + lane;
+        // the voxel's winner is the sequence number in the low word of `best`; uncontested points win by default
+        const uint32_t win = sel[r] ? 0xffffffffu - (uint32_t)(tab[sel[r] - 1u].best & 0xffffffffull) : (uint32_t)i;
+        sel[r] = win == (uint32_t)i ? 1u : 0u;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < MG_ROWS; r++) {
+      const int i = wbase + r * 32 + lane;
+      const bool k = i < n && (MODE == MG_ALL || sel[r] != 0u);
+      bal[r] = __ballot_sync(0xffffffffu, k);
+      cnt += __popc(bal[r]);
+    }
+    if (lane == 0)
+      wsum[wid] = cnt;
+    __syncthreads();
+    if (wid == 0) {
+      uint32_t tot = lane < MG_BLOCK / 32 ? wsum[lane] : 0u;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        tot += __shfl_xor_sync(0xffffffffu, tot, o);
+      const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
+      if (lane == 0) {
+        s_prefix = excl;
+        if (tbase + MG_TILE >= (long long)n) // the tile that holds the end of the input knows the total
+          *d_total = (int)(excl + tot);
+      }
+    }
+    __syncthreads();
+    uint32_t pos = s_prefix;
+    for (int w = 0; w < wid; w++)
+      pos += wsum[w];
+    const uint32_t lt = (1u << lane) - 1u;
+    float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int r = 0; r < MG_ROWS; r++) {
+      if ((bal[r] >> lane) & 1u) {
+        const uint32_t o = pos + __popc(bal[r] & lt);
+        if ((int)o < cap)
+          out[o] = pt[r];
+        mn[0] = fminf(mn[0], pt[r].x), mx[0] = fmaxf(mx[0], pt[r].x);
+        mn[1] = fminf(mn[1], pt[r].y), mx[1] = fmaxf(mx[1], pt[r].y);
+        mn[2] = fminf(mn[2], pt[r].z), mx[2] = fmaxf(mx[2], pt[r].z);
+      }
+      pos += __popc(bal[r]);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+        mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int c = 0; c < 3; c++)
+        smn[wid][c] = mn[c], smx[wid][c] = mx[c];
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      const int c = threadIdx.x;
+      float lo = INFINITY, hi = -INFINITY;
+      for (int w = 0; w < MG_BLOCK / 32; w++)
+        lo = fminf(lo, smn[w][c]), hi = fmaxf(hi, smx[w][c]);
+      if (lo <= hi) {
+        atomicMin(&bbox[c], f2ord(lo));
+        atomicMax(&bbox[3 + c], f2ord(hi));
+      }
     }
   }
-  keep[i] = k;
-}
-
-// stable compaction of [map | add] into out using the exclusive scan of keep
-__global__ void __launch_bounds__(256) k_compact2(const float4 *__restrict__ a, const int *__restrict__ d_na,
-                                                 const float4 *__restrict__ b, const int *__restrict__ d_nb,
-                                                 const uint32_t *__restrict__ keep, const uint32_t *__restrict__ pos,
-                                                 float4 *__restrict__ out, int cap, int *__restrict__ d_overflow) {
-  const int na = *d_na, nb = d_nb ? *d_nb : 0;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= na + nb)
+  // last CTA out: new count, grid descriptor, result block
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0)
+    s_last = atomicAdd(done_ctr, 1u) == gridDim.x - 1u;
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0)
     return;
-  if (keep[i]) {
-    uint32_t p = pos[i];
-    if ((int)p < cap)
-      out[p] = i < na ? a[i] : b[i - na];
-    else
-      atomicExch(d_overflow, 1);
+  __threadfence();
+  *done_ctr = 0u;
+  const int total = *(volatile int *)d_total;
+  const bool ovf = total > cap;
+  if (!ovf) {
+    *d_map_n = total;
+    uint32_t bb[6];
+    for (int c = 0; c < 6; c++)
+      bb[c] = *(volatile uint32_t *)&bbox[c];
+    grid_setup_dev(bb, total, cell0, max_cells, g);
+  } else { // the map is double-buffered: the old one is intact; the grid is rebuilt for it by the host's error path
+    grid_setup_dev(bbox, 0, cell0, max_cells, g);
   }
+  res->n_in = n;
+  res->n_out = total;
+  res->overflow = ovf ? 1 : 0;
+  res->ncells = g->ncells;
+  __threadfence_system();
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -6,8 +6,8 @@
 namespace ml {
 
 constexpr int SCAN_BLOCK = 256;
-constexpr int SCAN_ITEMS = 8;
-constexpr int SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
+constexpr int SCAN_ITEMS = 8, SCAN_ITEMS_LONG = 32; // per thread: short inputs (points of a scan / of the map), long inputs (grid cells)
+constexpr int SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS, SCAN_TILE_LONG = SCAN_BLOCK * SCAN_ITEMS_LONG;
 
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
   const int lane = threadIdx.x & 31;
@@ -45,64 +45,259 @@ template <int BLOCK> __device__ __forceinline__ uint32_t block_excl_scan(uint32_
   return r;
 }
 
-// pass 1: per-tile sums. n is read from device memory so the launch can be sized by capacity.
-__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_reduce(const uint32_t *__restrict__ in, const int *__restrict__ d_n,
-                                                           uint32_t *__restrict__ tile_sums) {
-  const int n = *d_n;
-  const int base = blockIdx.x * SCAN_TILE;
-  if (base >= n)
-    return;
-  uint32_t s = 0;
-#pragma unroll
-  for (int k = 0; k < SCAN_ITEMS; k++) {
-    int i = base + k * SCAN_BLOCK + threadIdx.x;
-    if (i < n)
-      s += in[i];
+// ------------------------------------------------------------------------------------------------
+// Decoupled look-back (single-pass prefix over tiles). A tile publishes (epoch, AGG, its count), walks backwards over its
+// predecessors 32 at a time adding counts until it meets one that already knows its inclusive prefix, then publishes
+// (epoch, PREFIX, inclusive prefix). Tiles are handed out by an atomic ticket, so every tile a CTA waits for belongs to a CTA
+// that is already running: no deadlock whatever the grid size. States carry the launch's epoch: no reset pass between
+// launches (a state of another epoch reads as "not published yet"). Only CTAs that own a tile take a ticket. Integer sums: the result does not depend on timing.
+// ------------------------------------------------------------------------------------------------
+constexpr unsigned long long LB_AGG = 1ull, LB_PREFIX = 2ull;
+__device__ __forceinline__ unsigned long long lb_pack(uint32_t epoch, unsigned long long flag, uint32_t v) {
+  return ((unsigned long long)epoch << 34) | (flag << 32) | (unsigned long long)v;
+}
+// tile ticket for the `active` CTAs of a launch (exactly that many call it); the counter is back at 0 when all are handed out
+__device__ __forceinline__ uint32_t lb_ticket(unsigned int *tile_ctr, uint32_t active) {
+  const uint32_t t = atomicAdd(tile_ctr, 1u);
+  if (t == active - 1u)
+    atomicExch(tile_ctr, 0u);
+  return t;
+}
+// warp-collective (all 32 lanes of one warp of the CTA that owns `tile`); returns the exclusive prefix in every lane
+__device__ __forceinline__ uint32_t lb_exclusive_prefix(unsigned long long *tile_state, uint32_t tile, uint32_t epoch, uint32_t tot) {
+  const int lane = threadIdx.x & 31;
+  volatile unsigned long long *vs = tile_state;
+  if (lane == 0) {
+    vs[tile] = lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, tot);
+    __threadfence();
   }
-  uint32_t tot;
-  block_excl_scan<SCAN_BLOCK>(s, &tot);
-  if (threadIdx.x == 0)
-    tile_sums[blockIdx.x] = tot;
+  uint32_t excl = 0;
+  if (tile > 0) {
+    int base = (int)tile - 1;
+    for (;;) {
+      const int b = base - lane;
+      unsigned long long sv = lb_pack(epoch, LB_PREFIX, 0u); // tiles before the first: prefix 0
+      if (b >= 0) {
+        do {
+          sv = vs[b];
+        } while ((uint32_t)(sv >> 34) != epoch);
+      }
+      const bool is_prefix = ((sv >> 32) & 3ull) == LB_PREFIX;
+      const uint32_t val = (uint32_t)sv;
+      const unsigned pm = __ballot_sync(0xffffffffu, is_prefix);
+      // lanes up to (and including) the nearest tile that already knows its prefix contribute
+      const int first = pm ? __ffs(pm) - 1 : 31;
+      uint32_t part = lane <= first ? val : 0u;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        part += __shfl_xor_sync(0xffffffffu, part, o);
+      excl += part;
+      if (pm)
+        break;
+      base -= 32;
+    }
+    if (lane == 0) {
+      vs[tile] = lb_pack(epoch, LB_PREFIX, excl + tot);
+      __threadfence();
+    }
+  }
+  return excl;
 }
 
-// pass 2: out[i] = sum(in[0..i)); out[n] = total. Each tile sums the preceding tile sums itself (fixed order,
-// no inter-block dependency, deterministic).
-__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(const uint32_t *__restrict__ in, const int *__restrict__ d_n,
-                                                          const uint32_t *__restrict__ tile_sums, uint32_t *__restrict__ out,
-                                                          int *__restrict__ d_total) {
-  const int n = *d_n;
-  const int base = blockIdx.x * SCAN_TILE;
-  if (base >= n) {
-    if (n == 0 && blockIdx.x == 0 && threadIdx.x == 0) {
-      out[0] = 0;
-      if (d_total)
-        *d_total = 0;
+// ------------------------------------------------------------------------------------------------
+// Exclusive scan of uint32 with a device-side element count: out[i] = sum(in[0..i)), out[n] = total. n is read from device
+// memory so a launch can be sized by a host-side upper bound; CTAs whose tile starts past n leave at once.
+// A CTA tile is SCAN_BLOCK*ITEMS elements, warp-striped: warp w owns 32*ITEMS consecutive elements, a row is 128 of them,
+// a lane holds 4 consecutive ones (one 16-byte access; a warp instruction covers 512 contiguous bytes).
+// ZERO_IN: non-zero inputs are zeroed once read (the kNN grid's cell counters: all-zero again after the build, without a
+// clearing pass over the mostly empty dense grid).
+// Two drivers share the tile code: k_scan_lb (one pass, decoupled look-back) and k_scan_reduce + k_scan_apply (two passes,
+// no inter-CTA waiting). scripts/bench_scan.cu measures both; api.cu uses the faster one for each input size.
+// ------------------------------------------------------------------------------------------------
+template <int ITEMS, bool ZERO_IN> struct ScanTile {
+  static constexpr int ROWS = ITEMS / 4, TILE = SCAN_BLOCK * ITEMS;
+  uint4 q[ROWS];
+  uint32_t ex[ROWS]; // exclusive prefix, inside the CTA tile, of the lane's 4 items of row r
+
+  __device__ __forceinline__ void load(uint32_t *in, long long base, int n) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long wbase = base + (long long)wid * (32 * ITEMS);
+#pragma unroll
+    for (int r = 0; r < ROWS; r++) {
+      const long long i = wbase + r * 128 + lane * 4;
+      if (i + 4 <= (long long)n) {
+        q[r] = *reinterpret_cast<const uint4 *>(in + i);
+        if (ZERO_IN && (q[r].x | q[r].y | q[r].z | q[r].w))
+          *reinterpret_cast<uint4 *>(in + i) = make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        uint32_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          v[k] = i + k < (long long)n ? in[i + k] : 0u;
+          if (ZERO_IN && v[k])
+            in[i + k] = 0u;
+        }
+        q[r] = make_uint4(v[0], v[1], v[2], v[3]);
+      }
     }
+  }
+  // sum of the CTA tile (every thread)
+  __device__ __forceinline__ uint32_t reduce() {
+    __shared__ uint32_t wsum[SCAN_BLOCK / 32];
+    uint32_t s = 0;
+#pragma unroll
+    for (int r = 0; r < ROWS; r++)
+      s += q[r].x + q[r].y + q[r].z + q[r].w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0)
+      wsum[threadIdx.x >> 5] = s;
+    __syncthreads();
+    uint32_t tot = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_BLOCK / 32; w++)
+      tot += wsum[w];
+    return tot;
+  }
+  // fills ex[]; returns the sum of the CTA tile (every thread)
+  __device__ __forceinline__ uint32_t scan() {
+    __shared__ uint32_t wsum[SCAN_BLOCK / 32];
+    const int wid = threadIdx.x >> 5;
+    uint32_t off = 0;
+#pragma unroll
+    for (int r = 0; r < ROWS; r++) {
+      const uint32_t rs = q[r].x + q[r].y + q[r].z + q[r].w;
+      const uint32_t inc = warp_incl_scan(rs);
+      ex[r] = off + inc - rs;
+      off += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if ((threadIdx.x & 31) == 0)
+      wsum[wid] = off;
+    __syncthreads();
+    uint32_t wpre = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_BLOCK / 32; w++) {
+      wpre += w < wid ? wsum[w] : 0u;
+      tot += wsum[w];
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; r++)
+      ex[r] += wpre;
+    return tot;
+  }
+  __device__ __forceinline__ void store(uint32_t *out, long long base, int n, uint32_t prefix) const {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long wbase = base + (long long)wid * (32 * ITEMS);
+#pragma unroll
+    for (int r = 0; r < ROWS; r++) {
+      const long long i = wbase + r * 128 + lane * 4;
+      uint4 a;
+      a.x = prefix + ex[r], a.y = a.x + q[r].x, a.z = a.y + q[r].y, a.w = a.z + q[r].z;
+      if (i + 4 <= (long long)n) {
+        *reinterpret_cast<uint4 *>(out + i) = a;
+      } else {
+        const uint32_t v[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+          if (i + k < (long long)n)
+            out[i + k] = v[k];
+      }
+    }
+  }
+};
+
+template <int ITEMS, bool ZERO_IN>
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_lb(uint32_t *in, const int *__restrict__ d_n, uint32_t *__restrict__ out,
+                                                       int *__restrict__ d_total, unsigned long long *tile_state,
+                                                       unsigned int *tile_ctr, uint32_t epoch) {
+  constexpr int TILE = SCAN_BLOCK * ITEMS;
+  __shared__ uint32_t s_tile, s_prefix;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
     return;
+  if (threadIdx.x == 0)
+    s_tile = lb_ticket(tile_ctr, active);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const long long base = (long long)tile * TILE;
+  ScanTile<ITEMS, ZERO_IN> t;
+  t.load(in, base, n);
+  const uint32_t tot = t.scan();
+  if (threadIdx.x < 32) {
+    const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
+    if (threadIdx.x == 0)
+      s_prefix = excl;
   }
-  uint32_t p = 0;
-  for (int b = threadIdx.x; b < blockIdx.x; b += SCAN_BLOCK)
-    p += tile_sums[b];
-  uint32_t prefix;
-  block_excl_scan<SCAN_BLOCK>(p, &prefix);
-  // blocked arrangement: thread t owns items [t*ITEMS, t*ITEMS+ITEMS)
-  uint32_t v[SCAN_ITEMS], s = 0;
-#pragma unroll
-  for (int k = 0; k < SCAN_ITEMS; k++) {
-    int i = base + threadIdx.x * SCAN_ITEMS + k;
-    v[k] = i < n ? in[i] : 0;
-    s += v[k];
+  __syncthreads();
+  t.store(out, base, n, s_prefix);
+  if (base + TILE >= (long long)n && threadIdx.x == 0) {
+    out[n] = s_prefix + tot;
+    if (d_total)
+      *d_total = (int)(s_prefix + tot);
   }
-  uint32_t tot;
-  uint32_t ex = block_excl_scan<SCAN_BLOCK>(s, &tot) + prefix;
-#pragma unroll
-  for (int k = 0; k < SCAN_ITEMS; k++) {
-    int i = base + threadIdx.x * SCAN_ITEMS + k;
-    if (i < n)
-      out[i] = ex;
-    ex += v[k];
+}
+
+// pass 1 of the two-pass scan: tile sums; the CTA that finishes last turns them into exclusive tile prefixes in place
+// (tile_sums[active] = total). `done` must be 0 on entry and is 0 again on exit.
+template <int ITEMS>
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_reduce(uint32_t *in, const int *__restrict__ d_n, uint32_t *tile_sums,
+                                                           unsigned int *done) {
+  constexpr int TILE = SCAN_BLOCK * ITEMS;
+  __shared__ uint32_t s_last;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
+    return;
+  ScanTile<ITEMS, false> t;
+  t.load(in, (long long)blockIdx.x * TILE, n);
+  const uint32_t tot = t.reduce();
+  if (threadIdx.x == 0) {
+    *(volatile uint32_t *)&tile_sums[blockIdx.x] = tot;
+    __threadfence();
+    s_last = atomicAdd(done, 1u) == active - 1u;
   }
-  if (base + SCAN_TILE >= n && threadIdx.x == 0) {
+  __syncthreads();
+  if (!s_last)
+    return;
+  __threadfence();
+  // one CTA, thread t owns a contiguous chunk of the tile sums
+  const uint32_t per = (active + SCAN_BLOCK - 1) / SCAN_BLOCK;
+  const uint32_t lo = min(threadIdx.x * per, active), hi = min(lo + per, active);
+  volatile uint32_t *ts = tile_sums;
+  uint32_t s = 0;
+  for (uint32_t i = lo; i < hi; i++)
+    s += ts[i];
+  uint32_t total;
+  uint32_t e = block_excl_scan<SCAN_BLOCK>(s, &total);
+  for (uint32_t i = lo; i < hi; i++) {
+    const uint32_t v = ts[i];
+    ts[i] = e;
+    e += v;
+  }
+  if (threadIdx.x == 0) {
+    ts[active] = total;
+    *done = 0u;
+  }
+}
+
+// pass 2: scan inside the tile on top of the tile's exclusive prefix
+template <int ITEMS, bool ZERO_IN>
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(uint32_t *in, const int *__restrict__ d_n, const uint32_t *__restrict__ tile_sums,
+                                                          uint32_t *__restrict__ out, int *__restrict__ d_total) {
+  constexpr int TILE = SCAN_BLOCK * ITEMS;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
+    return;
+  const long long base = (long long)blockIdx.x * TILE;
+  const uint32_t prefix = tile_sums[blockIdx.x];
+  ScanTile<ITEMS, ZERO_IN> t;
+  t.load(in, base, n);
+  const uint32_t tot = t.scan();
+  t.store(out, base, n, prefix);
+  if (base + TILE >= (long long)n && threadIdx.x == 0) {
     out[n] = prefix + tot;
     if (d_total)
       *d_total = (int)(prefix + tot);

@@ -5,19 +5,6 @@
 
 namespace ml {
 
-// ---- pcl::transformPointCloud(cloud, cloud_in_map, Matrix4f), LidarHelper.cpp:192,203 -----------------
-// PCL 1.10 SSE path: m0*x + (m1*y + (m2*z + m3)) per row, fp32, no FMA.
-struct Tf32 {
-  float m[12];
-};
-__device__ __forceinline__ float4 tf_apply(const Tf32 &T, float4 p) {
-  float4 q;
-  q.x = __fadd_rn(__fmul_rn(T.m[0], p.x), __fadd_rn(__fmul_rn(T.m[1], p.y), __fadd_rn(__fmul_rn(T.m[2], p.z), T.m[3])));
-  q.y = __fadd_rn(__fmul_rn(T.m[4], p.x), __fadd_rn(__fmul_rn(T.m[5], p.y), __fadd_rn(__fmul_rn(T.m[6], p.z), T.m[7])));
-  q.z = __fadd_rn(__fmul_rn(T.m[8], p.x), __fadd_rn(__fmul_rn(T.m[9], p.y), __fadd_rn(__fmul_rn(T.m[10], p.z), T.m[11])));
-  q.w = p.w;
-  return q;
-}
 // ---- LiDARData::LiDARData, LidarTypes.cpp:36-55 ------------------------------------------------------
 // Stable compaction of the in-range points in two launches (no intermediate flag/prefix arrays in HBM):
 //   k_range_count   : per-tile (2048 points) count of kept points; CTA 0 initialises the scan state

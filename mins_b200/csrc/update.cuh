@@ -83,15 +83,11 @@ __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_
 // passes over the scan). Tiles are handed out by an atomic ticket, so every tile a CTA waits for belongs to a CTA that is
 // already running: the look-back cannot deadlock whatever the grid size. States carry a per-scan epoch: no reset pass.
 // ------------------------------------------------------------------------------------------------
-constexpr unsigned long long LB_AGG = 1ull, LB_PREFIX = 2ull;
-__device__ __forceinline__ unsigned long long lb_pack(uint32_t epoch, unsigned long long flag, uint32_t v) {
-  return ((unsigned long long)epoch << 34) | (flag << 32) | (unsigned long long)v;
-}
 template <bool VEC4>
 __global__ void __launch_bounds__(RF_BLOCK)
     k_range_filter_bin(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax, ScanState *__restrict__ st,
                        float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
-                       unsigned long long *tile_state, unsigned int *tile_ctr, unsigned int ticket_base, uint32_t epoch,
+                       unsigned long long *tile_state, unsigned int *tile_ctr, uint32_t epoch,
                        const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask, uint32_t *__restrict__ q_slot,
                        uint32_t *__restrict__ q_rank) {
   __shared__ uint32_t wsum[RF_BLOCK / 32];
@@ -99,7 +95,7 @@ __global__ void __launch_bounds__(RF_BLOCK)
   pdl_enter();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (threadIdx.x == 0)
-    s_tile = atomicAdd(tile_ctr, 1u) - ticket_base;
+    s_tile = lb_ticket(tile_ctr, gridDim.x);
   __syncthreads();
   const uint32_t tile = s_tile;
   const int wbase = (int)tile * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
@@ -122,41 +118,7 @@ __global__ void __launch_bounds__(RF_BLOCK)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
       tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    volatile unsigned long long *vs = tile_state;
-    if (lane == 0) {
-      vs[tile] = lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, tot);
-      __threadfence();
-    }
-    uint32_t excl = 0;
-    if (tile > 0) {
-      int base = (int)tile - 1;
-      for (;;) {
-        const int b = base - lane;
-        unsigned long long sv = lb_pack(epoch, LB_PREFIX, 0u); // tiles before the first: prefix 0
-        if (b >= 0) {
-          do {
-            sv = vs[b];
-          } while ((uint32_t)(sv >> 34) != epoch);
-        }
-        const bool is_prefix = ((sv >> 32) & 3ull) == LB_PREFIX;
-        const uint32_t val = (uint32_t)sv;
-        const unsigned pm = __ballot_sync(0xffffffffu, is_prefix);
-        // lanes up to (and including) the nearest tile that already knows its prefix contribute
-        const int first = pm ? __ffs(pm) - 1 : 31;
-        uint32_t part = lane <= first ? val : 0u;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-          part += __shfl_xor_sync(0xffffffffu, part, o);
-        excl += part;
-        if (pm)
-          break;
-        base -= 32;
-      }
-      if (lane == 0) {
-        vs[tile] = lb_pack(epoch, LB_PREFIX, excl + tot);
-        __threadfence();
-      }
-    }
+    const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
     if (lane == 0) {
       s_prefix = excl;
       if (tile == 0) {
