@@ -128,7 +128,10 @@ int ml_map_build(ml_handle *h, const float *xyzi, int n);
 /* init_map_local on the current (down-sampled) scan cloud, device-resident (UpdaterLidar.cpp:91-95) */
 int ml_map_build_from_scan(ml_handle *h);
 /* KD_TREE::Add_Points(PointVector&, bool) with set_downsample_param(ds) (ikd_Tree.cpp:401-479).
- * n_kept (may be NULL) = live map size afterwards. */
+ * n_live = live map size afterwards. n_live == NULL (the reference returns nothing): the merge and the kNN-grid rebuild are
+ * queued on the handle's stream and the call returns without waiting for the device; the map is current for every later call
+ * (stream order), and a capacity overflow - which leaves the map unchanged - is reported as ML_ERR_CAPACITY by the NEXT call on
+ * the handle that reads the map (ml_scan_update, ml_map_size, ...). Same rule for ml_map_add_scan and ml_map_reanchor. */
 int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds, int *n_live);
 /* LidarHelper::register_scan (LidarHelper.cpp:196-207): transform the ORIGINAL cloud of the current scan by
  * T_LtoM (set by ml_scan_transform) and Add_Points it. */

@@ -64,6 +64,8 @@ struct ml_handle {
   unsigned int lb_epoch = 0;
   unsigned int *mg_done = nullptr;  // k_map_merge: CTAs finished
   MergeResult *h_merge = nullptr;   // pinned: result block of the last k_map_merge
+  bool merge_pending = false;       // a k_map_merge is in flight: map_n / overflow not yet read back (resolve_merge)
+  const char *merge_who = "";
   bool bin_done = false; // the queries of the resident scan are already in the hash table (fused front end)
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
@@ -238,27 +240,49 @@ static int rebuild_grid(ml_handle *h) {
   return grid_build_tail(h, n);
 }
 
+// Waits for the merge in flight (if any) and takes over its result block: the new point count, or - when the capacity was
+// exceeded - the previous map (double-buffered, untouched) with its grid rebuilt and ML_ERR_CAPACITY. Every entry point
+// that reads the host-side map state calls this first; a caller that did not ask for the live count (n_live == NULL) thus
+// gets its map update queued behind the scan's kernels and overlapped with its own host work.
+static int resolve_merge(ml_handle *h) {
+  if (!h->merge_pending)
+    return ML_OK;
+  h->merge_pending = false;
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->h_merge->overflow) {
+    h->cur = 1 - h->cur;
+    int rc = rebuild_grid(h);
+    h->err = std::string(h->merge_who) + ": map capacity (max_map_points) exceeded; the map is unchanged";
+    return rc ? rc : ML_ERR_CAPACITY;
+  }
+  h->map_n = h->h_merge->n_out;
+  h->map_init = h->map_n > 0;
+  return ML_OK;
+}
+#define RESOLVE(h)                                                                                                      \
+  do {                                                                                                                 \
+    if (int rc_ = resolve_merge(h))                                                                                    \
+      return rc_;                                                                                                      \
+  } while (0)
+
 // one-pass merge of the survivors of [a | b] into the other map buffer + bbox + grid descriptor (k_map_merge), then the grid
-// over it; ONE wait at the end for the result block. Flips the double buffer unless the capacity was exceeded.
+// over it. Flips the double buffer at once (stream order makes every later launch see the new map); the host-side count and
+// the capacity verdict arrive with resolve_merge: now if `wait`, else at the next entry point that needs them.
 template <int MODE>
-static int merge_into_map(ml_handle *h, const float4 *a, const int *d_na, const float4 *b, const int *d_nb, int n_ub, const char *who) {
+static int merge_into_map(ml_handle *h, const float4 *a, const int *d_na, const float4 *b, const int *d_nb, int n_ub, const char *who,
+                          bool wait) {
   LAUNCH(k_bbox_init, 1, 32, h->d_bbox);
   LAUNCH(k_map_merge<MODE>, std::max(1, cdiv(n_ub, MG_TILE)), MG_BLOCK, a, d_na, b, d_nb, h->vox_tab, h->contender, h->add_slot, h->keep,
          h->map_pts[1 - h->cur], h->cap_map, h->lb_state, h->lb_ctr, lb_next_epoch(h), h->d_bbox, h->mg_done, h->d_ints + 3, h->grid_cell,
          h->cap_cells, h->d_grid, h->d_map_n, h->h_merge);
   h->cur = 1 - h->cur;
   int rc = grid_build_tail(h, std::min(n_ub, h->cap_map));
-  CK(cudaStreamSynchronize(h->stream));
-  if (rc)
-    return rc;
-  if (h->h_merge->overflow) { // the previous buffer and *d_map_n are untouched: put its grid back
-    h->cur = 1 - h->cur;
-    rc = rebuild_grid(h);
-    h->err = std::string(who) + ": map capacity (max_map_points) exceeded";
-    return rc ? rc : ML_ERR_CAPACITY;
+  h->merge_pending = true;
+  h->merge_who = who;
+  if (rc || wait) {
+    int rc2 = resolve_merge(h);
+    return rc ? rc : rc2;
   }
-  h->map_n = h->h_merge->n_out;
-  h->map_init = h->map_n > 0;
   return ML_OK;
 }
 
@@ -379,6 +403,8 @@ void ml_destroy(ml_handle *h) {
     return;
   cudaStreamSynchronize(h->stream);
   cudaStreamSynchronize(h->stream2);
+  if (h->h_merge)
+    cudaFreeHost(h->h_merge);
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
@@ -410,6 +436,7 @@ void ml_destroy(ml_handle *h) {
 int ml_map_reset(ml_handle *h) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   h->map_n = 0;
   h->map_init = false;
   CK(cudaMemsetAsync(h->d_map_n, 0, sizeof(int), h->stream));
@@ -417,11 +444,17 @@ int ml_map_reset(ml_handle *h) {
   CK(cudaStreamSynchronize(h->stream));
   return ML_OK;
 }
-int ml_map_initialized(const ml_handle *h) { return h && h->map_init ? 1 : 0; }
+int ml_map_initialized(const ml_handle *h) {
+  if (!h)
+    return 0;
+  resolve_merge(const_cast<ml_handle *>(h)); // a failed merge leaves the previous map in place: still the right answer
+  return h->map_init ? 1 : 0;
+}
 
 int ml_map_build(ml_handle *h, const float *xyzi, int n) {
   if (!h || n < 0 || (n > 0 && !xyzi))
     return fail(h, ML_ERR_ARG, "ml_map_build: bad argument");
+  RESOLVE(h);
   if (n > h->cap_map)
     return fail(h, ML_ERR_CAPACITY, "ml_map_build: more points than max_map_points");
   h->cur = 0;
@@ -435,6 +468,7 @@ int ml_map_build(ml_handle *h, const float *xyzi, int n) {
 int ml_map_build_from_scan(ml_handle *h) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   ScanState st;
   CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
@@ -469,11 +503,11 @@ static int map_add_device(ml_handle *h, const float4 *xf_src, const int *d_nadd,
       LAUNCH(k_vox_insert_new<false>, cdiv(n_ub, 256), 256, xf_src, h->T_LtoM, h->add_pts, d_nadd, h->d_map_n, ds, h->vox_tab, mask, h->add_slot);
     if (M > 0)
       LAUNCH(k_vox_compete_old, cdiv(M, 256), 256, h->map_pts[h->cur], h->d_map_n, ds, h->vox_tab, mask, h->contender);
-    rc = merge_into_map<MG_VOX>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add");
+    rc = merge_into_map<MG_VOX>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add", n_live != nullptr);
   } else {
     if (xf_src)
       LAUNCH(k_transform, cdiv(n_ub, 256), 256, xf_src, d_nadd, h->T_LtoM, h->add_pts);
-    rc = merge_into_map<MG_ALL>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add");
+    rc = merge_into_map<MG_ALL>(h, h->map_pts[h->cur], h->d_map_n, h->add_pts, d_nadd, M + n_ub, "ml_map_add", n_live != nullptr);
   }
   if (n_live)
     *n_live = h->map_n;
@@ -483,6 +517,7 @@ static int map_add_device(ml_handle *h, const float4 *xf_src, const int *d_nadd,
 int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds, int *n_live) {
   if (!h || n < 0 || (n > 0 && !xyzi))
     return fail(h, ML_ERR_ARG, "ml_map_add: bad argument");
+  RESOLVE(h);
   if (n > h->cap_scan)
     return fail(h, ML_ERR_CAPACITY, "ml_map_add: more points than max_scan_points in one call");
   if (n > 0)
@@ -494,6 +529,7 @@ int ml_map_add(ml_handle *h, const float *xyzi, int n, int downsample, float ds,
 int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   if (!h->have_T)
     return fail(h, ML_ERR_ARG, "ml_map_add_scan: ml_scan_transform has not been called for this scan");
   return map_add_device(h, h->scan_orig, ST(n_orig), h->n_raw, downsample, ds, n_live);
@@ -523,6 +559,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
                     float ds, int *n_live) {
   if (!h || !T)
     return fail(h, ML_ERR_ARG, "ml_map_reanchor: bad argument");
+  RESOLVE(h);
   if (!h->map_init)
     return fail(h, ML_SOFT_NO_MAP, "ml_map_reanchor: map not initialised");
   const int M = h->map_n;
@@ -540,7 +577,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
   a.now_minus_FT = now_minus_FT, a.decay_time = decay_time, a.decay_dist = decay_dist;
   // transformed copy into cell_pts (free scratch: the grid is rebuilt below) + keep flags, then the one-pass merge
   LAUNCH(k_reanchor, cdiv(M, 256), 256, src, d_n, a, h->cell_pts, h->keep);
-  int rc = merge_into_map<MG_FLAGS>(h, h->cell_pts, d_n, (const float4 *)nullptr, (const int *)nullptr, M, "ml_map_reanchor");
+  int rc = merge_into_map<MG_FLAGS>(h, h->cell_pts, d_n, (const float4 *)nullptr, (const int *)nullptr, M, "ml_map_reanchor", n_live != nullptr);
   if (n_live)
     *n_live = h->map_n;
   return rc;
@@ -549,6 +586,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
 int ml_map_flatten(ml_handle *h, float *xyzi_out, int cap, int *n) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   int m = std::min(cap, h->map_n);
   if (m > 0 && xyzi_out) {
     CK(cudaMemcpyAsync(xyzi_out, h->map_pts[h->cur], sizeof(float4) * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
@@ -561,6 +599,7 @@ int ml_map_flatten(ml_handle *h, float *xyzi_out, int cap, int *n) {
 int ml_map_size(ml_handle *h, int *n) {
   if (!h || !n)
     return ML_ERR_ARG;
+  RESOLVE(h);
   *n = h->map_n;
   return ML_OK;
 }
@@ -641,6 +680,7 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
 int ml_scan_upload(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, int *n_kept) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   int rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax, nullptr);
   if (rc)
     return rc;
@@ -938,6 +978,7 @@ extern "C" {
 int ml_knn(ml_handle *h, int k, float max_d2, int32_t *idx, float *d2, uint8_t *ok, int *n) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   int rc = knn_async(h, k, max_d2);
   if (rc)
     return rc;
@@ -1041,6 +1082,7 @@ static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *
 int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
   if (!h || !P)
     return fail(h, ML_ERR_ARG, "ml_linsys: bad argument");
+  RESOLVE(h);
   int rc = check_consts(h, c);
   if (rc)
     return rc;
@@ -1065,6 +1107,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
                    const float T_LtoM[16], const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
   if (!h || !P || !T_LtoM)
     return fail(h, ML_ERR_ARG, "ml_scan_update: bad argument");
+  RESOLVE(h);
   int rc = check_consts(h, c);
   if (rc)
     return rc;

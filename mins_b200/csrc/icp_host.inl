@@ -115,6 +115,7 @@ void ml_icp_default_options(ml_icp_options *o) {
 int ml_scan_icp(ml_handle *h, const float T_init[16], const ml_icp_options *o, ml_icp_result *res) {
   if (!h || !T_init || !o || !res)
     return fail(h, ML_ERR_ARG, "ml_scan_icp: bad argument");
+  RESOLVE(h);
   if (o->normal_knn != 7)
     return fail(h, ML_ERR_ARG, "ml_scan_icp: normal_knn must be 7 (the library default; the only instantiated kernel)");
   if (o->max_iter < 1 || o->smooth_len < 1 || !(o->max_match_dist > 0.0) || !(o->normal_radius > 0.0) || !(o->max_dist > 0.0))

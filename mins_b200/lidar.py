@@ -208,19 +208,20 @@ class LidarMap:
         T = _f32(T_LtoM).reshape(4, 4)
         self._ck(self.lib.ml_scan_transform(self.h, T.ctypes.data))
 
-    def register_scan(self, op):
-        """LidarHelper::register_scan (LidarHelper.cpp:196-207)."""
+    def register_scan(self, op, wait=True):
+        """LidarHelper::register_scan (LidarHelper.cpp:196-207). wait=False (the reference returns nothing): the merge and the
+        grid rebuild are queued and the call returns; the next call on the map picks up the count (and a capacity error)."""
         n = C.c_int()
-        self._ck(self.lib.ml_map_add_scan(self.h, int(op.map_do_downsample), op.map_downsample_size, C.byref(n)))
-        return n.value
+        self._ck(self.lib.ml_map_add_scan(self.h, int(op.map_do_downsample), op.map_downsample_size, C.byref(n) if wait else None))
+        return n.value if wait else None
 
-    def propagate_map_to_newest_clone(self, T_old_to_new, now_minus_FT, op):
+    def propagate_map_to_newest_clone(self, T_old_to_new, now_minus_FT, op, wait=True):
         """LidarHelper::propagate_map_to_newest_clone (LidarHelper.cpp:209-266), pose look-ups done by the caller."""
         T = _f64(T_old_to_new).reshape(4, 4)
         n = C.c_int()
         self._ck(self.lib.ml_map_reanchor(self.h, T.ctypes.data, now_minus_FT, op.map_decay_time, op.map_decay_dist,
-                                          int(op.map_do_downsample), op.map_downsample_size, C.byref(n)))
-        return n.value
+                                          int(op.map_do_downsample), op.map_downsample_size, C.byref(n) if wait else None))
+        return n.value if wait else None
 
     def scan(self, which=0):
         n = C.c_int()

@@ -384,6 +384,50 @@ def test_map_add_without_downsample_and_capacity(make_map, po):
     assert not m.initialized() and m.size() == 0
 
 
+def test_deferred_map_update_equals_the_waiting_one(make_map, po, workload):
+    """n_live == NULL (what the C++ shim passes: register_scan returns void): the merge and the grid rebuild are only queued;
+    the next calls see the same map as after the waiting variant, bit for bit, including a scan update issued right behind."""
+    import ctypes as C
+    from mins_b200.lidar import OptionsLidar
+    w = workload("G-small")
+    op = OptionsLidar(map_do_downsample=True, map_downsample_size=0.3)
+    T = np.eye(4)
+    T[:3, 3] = [0.05, -0.02, 0.01]
+    res = []
+    for wait in (True, False):
+        m = make_map()
+        m.Build(w["map"])
+        m.feed_scan(w["raw"], w["t_rel"], op)
+        m.transform_to_map(w["T_LtoM"])
+        n = m.register_scan(op, wait=wait)
+        assert (n is None) == (not wait)
+        # straight behind the (possibly still running) merge: a full scan update against the new map
+        rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
+        size_after_insert = m.size()
+        n2 = m.propagate_map_to_newest_clone(T, 1.0, op, wait=wait)
+        res.append((size_after_insert, HtH.copy(), Htr.copy(), cnt.as_dict(), m.flatten(), m.size()))
+    a, b = res
+    assert a[0] == b[0] and a[5] == b[5] and a[3] == b[3]
+    assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[4], b[4])
+
+
+def test_deferred_map_update_reports_capacity_on_the_next_call(make_map):
+    from mins_b200 import capi
+    from mins_b200.lidar import MLError
+    import ctypes as C
+    rng = np.random.default_rng(8)
+    a, b = as_xyzi(rng.uniform(-5, 5, (500, 3)), 0.1), as_xyzi(rng.uniform(-5, 5, (300, 3)), 0.2)
+    m = make_map(max_scan_points=400, max_map_points=700)
+    m.Build(a)
+    bb = np.ascontiguousarray(b, np.float32)
+    assert m.lib.ml_map_add(m.h, bb.ctypes.data, 300, 0, 0.3, None) == capi.ML_OK       # 800 > 700, not known yet
+    with pytest.raises(MLError) as e:
+        m.size()
+    assert e.value.code == capi.ML_ERR_CAPACITY
+    assert m.size() == 500 and np.array_equal(m.flatten(), a)                             # the map is unchanged and usable
+    assert m.Add_Points(b[:100], False, 0.3) == 600
+
+
 @pytest.mark.parametrize("do_ds", [False, True])
 def test_reanchor_equals_oracle(make_map, po, workload, do_ds):
     """LidarHelper::propagate_map_to_newest_clone (LidarHelper.cpp:209-266)"""
