@@ -170,14 +170,33 @@ def aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx, reps=10):
     aux["icp_ms"] = float(np.median(t_icp) * 1e3)
     aux["icp_iterations"] = int(np.median(iters))
     aux["icp_points"] = {"reading": int(res.n_reading), "reference": int(res.n_reference)}
-    # map insert (LidarHelper::register_scan) and re-anchor (propagate_map_to_newest_clone); both change the map: last
+    # map insert (LidarHelper::register_scan) and re-anchor (propagate_map_to_newest_clone); both change the map: last.
+    # The first insert adds the scan's voxels; the repetitions run the same contest again (same work, map unchanged).
     n0 = m.size()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    n1 = m.register_scan(op)
-    t_ins = time.perf_counter() - t0
-    aux["map_insert_points_per_s"] = float(w["n_rays"] / t_ins)
-    aux["map_insert_ms"] = float(t_ins * 1e3)
+    t_ins, t_defer, t_pair = [], [], []
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n1 = m.register_scan(op)
+        t_ins.append(time.perf_counter() - t0)
+    for _ in range(reps):                                   # n_live == NULL: queued, the call returns at once
+        m.size()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        m.register_scan(op, wait=False)
+        t_defer.append(time.perf_counter() - t0)
+    m.size()
+    for _ in range(reps):                                   # the estimator's per-scan pair, back to back (no host work between)
+        t0 = time.perf_counter()
+        step(host_ptr)
+        m.register_scan(op, wait=False)
+        t_pair.append(time.perf_counter() - t0)
+    m.size()
+    t_med = float(np.median(t_ins))
+    aux["map_insert_points_per_s"] = float(w["n_rays"] / t_med)
+    aux["map_insert_ms"] = t_med * 1e3
+    aux["map_insert_deferred_call_ms"] = float(np.median(t_defer) * 1e3)
+    aux["scan_update_plus_deferred_insert_ms"] = float(np.median(t_pair) * 1e3)
     aux["map_points_before_after_insert"] = [int(n0), int(n1)]
     T = np.eye(4)
     T[:3, 3] = [0.05, -0.02, 0.01]

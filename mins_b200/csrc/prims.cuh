@@ -66,11 +66,10 @@ __device__ __forceinline__ uint32_t lb_ticket(unsigned int *tile_ctr, uint32_t a
 // warp-collective (all 32 lanes of one warp of the CTA that owns `tile`); returns the exclusive prefix in every lane
 __device__ __forceinline__ uint32_t lb_exclusive_prefix(unsigned long long *tile_state, uint32_t tile, uint32_t epoch, uint32_t tot) {
   const int lane = threadIdx.x & 31;
-  volatile unsigned long long *vs = tile_state;
-  if (lane == 0) {
-    vs[tile] = lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, tot);
-    __threadfence();
-  }
+  // a state is ONE 64-bit word (epoch, flag, value) and readers consume nothing else the publisher wrote: no fence is
+  // needed for correctness; the atomic is there because it is performed at L2 at once (a plain store is visible later)
+  if (lane == 0)
+    atomicExch(&tile_state[tile], lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, tot));
   uint32_t excl = 0;
   if (tile > 0) {
     int base = (int)tile - 1;
@@ -79,7 +78,7 @@ __device__ __forceinline__ uint32_t lb_exclusive_prefix(unsigned long long *tile
       unsigned long long sv = lb_pack(epoch, LB_PREFIX, 0u); // tiles before the first: prefix 0
       if (b >= 0) {
         do {
-          sv = vs[b];
+          asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(sv) : "l"(tile_state + b) : "memory");
         } while ((uint32_t)(sv >> 34) != epoch);
       }
       const bool is_prefix = ((sv >> 32) & 3ull) == LB_PREFIX;
@@ -96,10 +95,8 @@ __device__ __forceinline__ uint32_t lb_exclusive_prefix(unsigned long long *tile
         break;
       base -= 32;
     }
-    if (lane == 0) {
-      vs[tile] = lb_pack(epoch, LB_PREFIX, excl + tot);
-      __threadfence();
-    }
+    if (lane == 0)
+      atomicExch(&tile_state[tile], lb_pack(epoch, LB_PREFIX, excl + tot));
   }
   return excl;
 }
