@@ -43,6 +43,7 @@ struct ml_handle {
   bool map_init = false;
   GridDesc *d_grid = nullptr;
   uint32_t *d_bbox = nullptr;
+  uint32_t *d_bbox_vg = nullptr; // the voxel filter's own box: in its initial (empty) state between uses
   uint32_t *cell_cnt = nullptr, *cell_start = nullptr;
   float4 *cell_pts = nullptr;
   uint32_t *pt_cell = nullptr, *pt_rank = nullptr;
@@ -70,7 +71,8 @@ struct ml_handle {
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
   Tf32 T_LtoM;
-  uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}, *radix_table = nullptr, *radix_dtot = nullptr;
+  uint32_t *sort_keys[2] = {nullptr, nullptr}, *sort_vals[2] = {nullptr, nullptr}, *radix_ghist = nullptr, *radix_dbase = nullptr;
+  unsigned long long *radix_state = nullptr; // per (tile, digit) look-back states of k_radix_pass, epoch-tagged
   int radix_tiles_cap = 0;
   VoxGridDesc *d_vg = nullptr;
   float *d_knots = nullptr;
@@ -204,17 +206,17 @@ static void excl_scan(ml_handle *h, uint32_t *in, const int *d_n, int n_ub, uint
 }
 
 // stable sort of (keys, vals) by key; result ends in sort_keys[0]/sort_vals[0]. bits = number of key bits to sort.
+// stable sort of (sort_keys[0], sort_vals[0]) by key, `bits` key bits; the result ends in buffer 0. The digit bases
+// (radix_dbase) must have been produced with the keys (k_vox_index_hist / k_radix_hist4).
 static void radix_sort(ml_handle *h, const int *d_n, int n_ub, int bits) {
-  int tiles = std::max(1, cdiv(n_ub, RS_TILE));
-  int passes = std::max(1, (bits + 7) / 8);
+  int passes = std::min(RS_PASSES, std::max(1, (bits + 7) / 8));
   if (passes & 1)
     passes++; // even number of passes so the result lands in buffer 0
+  const int tiles = std::max(1, cdiv(n_ub, RS_TILE));
   int src = 0;
   for (int p = 0; p < passes; p++) {
-    LAUNCH(k_radix_hist, tiles, RS_BLOCK, h->sort_keys[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap);
-    LAUNCH(k_radix_scan, 256, 256, h->radix_table, d_n, h->radix_tiles_cap, h->radix_dtot);
-    LAUNCH(k_radix_scatter, tiles, RS_BLOCK, h->sort_keys[src], h->sort_vals[src], d_n, p * 8, h->radix_table, h->radix_tiles_cap,
-           h->radix_dtot, h->sort_keys[1 - src], h->sort_vals[1 - src]);
+    LAUNCH(k_radix_pass<RS_ITEMS>, tiles, RS_BLOCK, h->sort_keys[src], h->sort_vals[src], d_n, p, h->radix_dbase, h->radix_state, h->lb_ctr,
+           lb_next_epoch(h), h->sort_keys[1 - src], h->sort_vals[1 - src]);
     src = 1 - src;
   }
 }
@@ -335,6 +337,8 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->d_grid, sizeof(GridDesc)));
   CK(cudaMemset(h->d_grid, 0, sizeof(GridDesc)));
   CK(cudaMalloc(&h->d_bbox, sizeof(uint32_t) * 8));
+  CK(cudaMalloc(&h->d_bbox_vg, sizeof(uint32_t) * 8));
+  k_bbox_init<<<1, 32, 0, h->stream>>>(h->d_bbox_vg);
   CK(cudaMalloc(&h->cell_cnt, sizeof(uint32_t) * ((size_t)h->cap_cells + 2)));
   CK(cudaMalloc(&h->cell_start, sizeof(uint32_t) * ((size_t)h->cap_cells + 2)));
   CK(cudaMalloc(&h->cell_pts, sizeof(float4) * ca));
@@ -375,8 +379,11 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     CK(cudaMalloc(&h->sort_vals[b], sizeof(uint32_t) * ca));
   }
   h->radix_tiles_cap = cdiv((long long)ca, RS_TILE) + 1;
-  CK(cudaMalloc(&h->radix_table, sizeof(uint32_t) * 256 * (size_t)h->radix_tiles_cap));
-  CK(cudaMalloc(&h->radix_dtot, sizeof(uint32_t) * 256));
+  CK(cudaMalloc(&h->radix_state, sizeof(unsigned long long) * 256 * (size_t)h->radix_tiles_cap));
+  CK(cudaMemset(h->radix_state, 0, sizeof(unsigned long long) * 256 * (size_t)h->radix_tiles_cap));
+  CK(cudaMalloc(&h->radix_ghist, sizeof(uint32_t) * 256 * RS_PASSES));
+  CK(cudaMemset(h->radix_ghist, 0, sizeof(uint32_t) * 256 * RS_PASSES));
+  CK(cudaMalloc(&h->radix_dbase, sizeof(uint32_t) * 256 * RS_PASSES));
   CK(cudaMalloc(&h->d_vg, sizeof(VoxGridDesc)));
   h->q_slots = 1;
   while ((size_t)h->q_slots < 2 * cs)
@@ -412,10 +419,10 @@ void ml_destroy(ml_handle *h) {
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
-                 h->sort_vals[1], h->radix_table, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
+                 h->sort_vals[1], h->radix_state, h->radix_ghist, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->rows, h->parts, h->ticket,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dtot, h->sim_knots, h->mg_done};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -539,23 +546,17 @@ int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
   return map_add_device(h, h->scan_orig, ST(n_orig), h->n_raw, downsample, ds, n_live);
 }
 
-// voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated. n_ub host bound. tmp buffers: sort_*, keep, pos.
-static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf) {
+// voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated (scan.cuh: 7 launches). n_ub host bound. tmp buffers: sort_*.
+// d_vox_n / d_vox_pass (may be NULL): occupied voxels and PCL's "leaf too small" verdict, for the scan state.
+static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf, int *d_vox_n, int *d_vox_pass) {
   if (n_ub <= 0)
     return ML_OK;
-  int *d_pass = h->d_ints + 4;
-  LAUNCH(k_bbox_init, 1, 32, h->d_bbox);
-  LAUNCH(k_bbox, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox);
-  LAUNCH(k_voxgrid_setup, 1, 32, h->d_bbox, d_n, leaf, h->d_vg);
-  LAUNCH(k_vox_index, cdiv(n_ub, 256), 256, src, d_n, h->d_vg, h->sort_keys[0], h->sort_vals[0]);
+  LAUNCH(k_bbox_voxgrid, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox_vg, h->mg_done, leaf, h->d_vg);
+  LAUNCH(k_vox_index_hist, cdiv(n_ub, RS_TILE), RS_BLOCK, src, d_n, h->d_vg, h->sort_keys[0], h->sort_vals[0], h->radix_ghist,
+         h->radix_dbase, h->mg_done);
   radix_sort(h, d_n, n_ub, 32);
-  LAUNCH(k_seg_heads, cdiv(n_ub, 256), 256, h->sort_keys[0], d_n, h->keep);
-  excl_scan(h, h->keep, d_n, n_ub, h->pos, nullptr);
-  LAUNCH(k_vox_centroid, cdiv(n_ub, 256), 256, src, h->sort_keys[0], h->sort_vals[0], h->keep, h->pos, d_n, dst);
-  // PCL refuses leaf sizes that overflow its int32 voxel index and returns the input unchanged
-  LAUNCH(k_copy_int, 1, 1, d_pass, &h->d_vg->passthrough);
-  LAUNCH(k_copy_if_flag, cdiv(n_ub, 256), 256, src, dst, d_n, d_pass, 1);
-  LAUNCH(k_vox_finish, 1, 32, h->d_vg, h->pos, d_n, d_pass);
+  LAUNCH(k_vox_reduce, cdiv(n_ub, VR_TILE), VR_BLOCK, src, h->sort_keys[0], h->sort_vals[0], d_n, h->d_vg, dst, h->lb_state, h->lb_ctr,
+         lb_next_epoch(h), h->mg_done, h->d_ints + 6, d_vox_n, d_vox_pass);
   return check_launch(h);
 }
 
@@ -571,7 +572,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
   int *d_n = h->d_ints + 5;
   LAUNCH(k_copy_int, 1, 1, d_n, h->d_map_n);
   if (do_downsample) {
-    int rc = voxel_filter(h, src, h->scan_tmp, d_n, M, ds);
+    int rc = voxel_filter(h, src, h->scan_tmp, d_n, M, ds, nullptr, nullptr);
     if (rc)
       return rc;
     src = h->scan_tmp;
@@ -738,7 +739,7 @@ int ml_scan_deskew(ml_handle *h, const float *T_LitoL_knots, int n_knots, int to
 static int scan_downsample_async(ml_handle *h, float leaf) {
   if (!(leaf > 0.f))
     return fail(h, ML_ERR_ARG, "ml_scan_downsample: leaf must be positive");
-  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf);
+  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf, ST(vox_n), ST(vox_passthrough));
   if (rc)
     return rc;
   std::swap(h->scan_pts, h->scan_tmp);

@@ -21,6 +21,15 @@ __device__ __forceinline__ float norm3_ref(float x, float y, float z) {
   return __fsqrt_rn(__fadd_rn(__fmul_rn(x, x), __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z))));
 }
 
+// order-preserving float <-> uint mapping for atomicMin/Max on floats
+__device__ __forceinline__ uint32_t f2ord(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) {
+  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
 // ---- pcl::transformPointCloud(cloud, cloud_in_map, Matrix4f), LidarHelper.cpp:192,203 -----------------
 // row-major 3x4 fp32 rigid transform. PCL 1.10 SSE path: m0*x + (m1*y + (m2*z + m3)) per row, fp32, no FMA.
 struct Tf32 {

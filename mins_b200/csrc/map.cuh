@@ -6,15 +6,6 @@
 
 namespace ml {
 
-// order-preserving float <-> uint mapping for atomicMin/Max on floats
-__device__ __forceinline__ uint32_t f2ord(float f) {
-  uint32_t u = __float_as_uint(f);
-  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-__device__ __forceinline__ float ord2f(uint32_t u) {
-  return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
-}
-
 // bbox[0..2] = min (ordered uint), bbox[3..5] = max
 __global__ void k_bbox_init(uint32_t *bbox) {
   if (threadIdx.x < 3)

@@ -303,85 +303,113 @@ __global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(uint32_t *in, const i
 
 // ------------------------------------------------------------------------------------------------
 // Stable LSD radix sort, 8 bits per pass, of (key uint32, value uint32) pairs; n on the device.
-// Per pass: k_radix_hist (tile histograms, digit-major table) -> k_radix_scan (one block scans the
-// table) -> k_radix_scatter (stable in-tile ranking with warp match_any, warps own consecutive chunks).
+// One histogram kernel for all passes (k_radix_hist4: the keys are read once, the CTA that finishes last turns the four
+// digit histograms into digit bases), then ONE kernel per pass (k_radix_pass): stable in-tile ranking with warp match_any
+// (warps own consecutive chunks), and the tile's offset inside every digit's output range by a decoupled look-back per digit
+// (thread d follows digit d through the preceding tiles). 5 launches for a 32-bit sort instead of 12.
 // ------------------------------------------------------------------------------------------------
 constexpr int RS_BLOCK = 256;
-constexpr int RS_ITEMS = 4;
+constexpr int RS_ITEMS = 4; // keys per thread (16 measured no faster on the 1 M-point map: the in-tile ranking dominates, not the look-back)
 constexpr int RS_TILE = RS_BLOCK * RS_ITEMS; // 1024: a 131 072-point scan sorts on 128 CTAs
 constexpr int RS_WARPS = RS_BLOCK / 32;
+constexpr int RS_PASSES = 4;
 
-__global__ void __launch_bounds__(RS_BLOCK) k_radix_hist(const uint32_t *__restrict__ keys, const int *__restrict__ d_n, int shift,
-                                                        uint32_t *__restrict__ table, int ntiles_cap) {
-  __shared__ uint32_t h[256];
-  const int n = *d_n;
-  const int ntiles = (n + RS_TILE - 1) / RS_TILE;
-  if ((int)blockIdx.x >= ntiles)
+// Digit histograms of all passes at once. h[p][d] (shared) = this CTA's counts. ghist[p][d] (global, all-zero on entry and on
+// exit) accumulates them; the CTA that finishes last writes dbase[p][d] = number of keys whose p-th byte is smaller than d.
+// `done` is 0 on entry and on exit. Called by every thread of the `active` CTAs after their shared histogram is complete.
+__device__ __forceinline__ void radix_hist4_publish(uint32_t (*h)[256], uint32_t *ghist, uint32_t *__restrict__ dbase,
+                                                    unsigned int *done, uint32_t active) {
+  __shared__ uint32_t s_last;
+  __syncthreads();
+#pragma unroll
+  for (int p = 0; p < RS_PASSES; p++)
+    if (h[p][threadIdx.x])
+      atomicAdd(&ghist[p * 256 + threadIdx.x], h[p][threadIdx.x]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0)
+    s_last = atomicAdd(done, 1u) == active - 1u;
+  __syncthreads();
+  if (!s_last)
     return;
-  h[threadIdx.x] = 0;
-  __syncthreads();
-  const int base = blockIdx.x * RS_TILE;
-  for (int k = 0; k < RS_ITEMS; k++) {
-    int i = base + k * RS_BLOCK + threadIdx.x;
-    if (i < n)
-      atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
-  }
-  __syncthreads();
-  table[threadIdx.x * ntiles_cap + blockIdx.x] = h[threadIdx.x];
-}
-
-// Row scan of the digit-major table: CTA d scans row d (the counts of digit d over the live tiles) in place to exclusive
-// prefixes and leaves the digit total in dtot[d]. 256 CTAs, all loads in flight at once; the scatter kernel turns the 256
-// digit totals into digit bases itself (one block scan), so there is no serial pass over the table.
-__global__ void __launch_bounds__(256) k_radix_scan(uint32_t *__restrict__ table, const int *__restrict__ d_n, int ntiles_cap,
-                                                   uint32_t *__restrict__ dtot) {
-  const int n = *d_n;
-  const int ntiles = (n + RS_TILE - 1) / RS_TILE;
-  uint32_t *row = table + (size_t)blockIdx.x * ntiles_cap;
-  uint32_t carry = 0;
-  for (int base = 0; base < ntiles; base += 256) {
-    const int t = base + threadIdx.x;
-    const uint32_t v = t < ntiles ? row[t] : 0u;
-    uint32_t tot;
-    const uint32_t ex = block_excl_scan<256>(v, &tot);
-    if (t < ntiles)
-      row[t] = carry + ex;
-    carry += tot;
+  __threadfence();
+#pragma unroll
+  for (int p = 0; p < RS_PASSES; p++) {
+    const uint32_t v = *(volatile uint32_t *)&ghist[p * 256 + threadIdx.x];
+    ghist[p * 256 + threadIdx.x] = 0u;
+    dbase[p * 256 + threadIdx.x] = block_excl_scan<RS_BLOCK>(v, nullptr);
   }
   if (threadIdx.x == 0)
-    dtot[blockIdx.x] = carry;
+    *done = 0u;
+}
+// plain shared-memory atomics: warp-aggregating them with match_any (the high bytes of voxel keys take few values) was
+// measured slower (11.0 vs 9.6 us for 131 072 keys)
+__device__ __forceinline__ void radix_hist4_add(uint32_t (*h)[256], uint32_t key) {
+#pragma unroll
+  for (int p = 0; p < RS_PASSES; p++)
+    atomicAdd(&h[p][(key >> (8 * p)) & 255u], 1u);
 }
 
-__global__ void __launch_bounds__(RS_BLOCK) k_radix_scatter(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
-                                                           const int *__restrict__ d_n, int shift,
-                                                           const uint32_t *__restrict__ table, int ntiles_cap,
-                                                           const uint32_t *__restrict__ dtot, uint32_t *__restrict__ keys_out,
-                                                           uint32_t *__restrict__ vals_out) {
-  __shared__ uint32_t wcnt[RS_WARPS][256]; // per-warp digit counts -> per-warp bases
+__global__ void __launch_bounds__(RS_BLOCK) k_radix_hist4(const uint32_t *__restrict__ keys, const int *__restrict__ d_n,
+                                                         uint32_t *ghist, uint32_t *__restrict__ dbase, unsigned int *done) {
+  __shared__ uint32_t h[RS_PASSES][256];
   const int n = *d_n;
-  const int ntiles = (n + RS_TILE - 1) / RS_TILE;
-  if ((int)blockIdx.x >= ntiles)
+  const uint32_t active = n > 0 ? (uint32_t)((n + RS_TILE - 1) / RS_TILE) : 1u;
+  if (blockIdx.x >= active)
     return;
+#pragma unroll
+  for (int p = 0; p < RS_PASSES; p++)
+    h[p][threadIdx.x] = 0;
+  __syncthreads();
+  const int base = blockIdx.x * RS_TILE;
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const int i = base + k * RS_BLOCK + threadIdx.x;
+    if (i < n)
+      radix_hist4_add(h, keys[i]);
+  }
+  radix_hist4_publish(h, ghist, dbase, done, active);
+}
+
+template <int ITEMS>
+__global__ void __launch_bounds__(RS_BLOCK) k_radix_pass(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                                        const int *__restrict__ d_n, int pass, const uint32_t *__restrict__ dbase,
+                                                        unsigned long long *digit_state, unsigned int *tile_ctr, uint32_t epoch,
+                                                        uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out) {
+  __shared__ uint32_t wcnt[RS_WARPS][256]; // per-warp digit counts -> per-warp bases
+  __shared__ uint32_t s_tile;
+  constexpr int TILE = RS_BLOCK * ITEMS;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
+    return;
+  const int shift = 8 * pass;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0)
+    s_tile = lb_ticket(tile_ctr, active);
   for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_BLOCK)
     (&wcnt[0][0])[i] = 0;
   __syncthreads();
+  const uint32_t tile = s_tile;
   // warp w owns the contiguous chunk [base + w*CH, base + (w+1)*CH), processed 32 at a time in order
-  constexpr int CH = RS_TILE / RS_WARPS; // 512
-  const int wbase = blockIdx.x * RS_TILE + wid * CH;
+  constexpr int CH = TILE / RS_WARPS;
+  const int wbase = (int)tile * TILE + wid * CH;
   uint32_t myk[CH / 32], myv[CH / 32], myrank[CH / 32];
 #pragma unroll
   for (int r = 0; r < CH / 32; r++) {
-    int i = wbase + r * 32 + lane;
-    bool ok = i < n;
-    uint32_t k = ok ? keys[i] : 0xffffffffu;
-    myk[r] = k;
-    myv[r] = ok ? vals[i] : 0;
-    uint32_t d = (k >> shift) & 255u;
-    unsigned act = __ballot_sync(0xffffffffu, ok);
+    const int i = wbase + r * 32 + lane;
+    myk[r] = i < n ? keys[i] : 0xffffffffu;
+    myv[r] = i < n ? vals[i] : 0u;
+  }
+#pragma unroll
+  for (int r = 0; r < CH / 32; r++) {
+    const int i = wbase + r * 32 + lane;
+    const bool ok = i < n;
+    const uint32_t d = (myk[r] >> shift) & 255u;
+    const unsigned act = __ballot_sync(0xffffffffu, ok);
     uint32_t rank = 0;
     if (ok) {
-      unsigned peers = __match_any_sync(act, d);
+      const unsigned peers = __match_any_sync(act, d);
       rank = wcnt[wid][d] + __popc(peers & ((1u << lane) - 1u));
       __syncwarp(act);
       if ((peers & ((1u << lane) - 1u)) == 0)
@@ -391,14 +419,31 @@ __global__ void __launch_bounds__(RS_BLOCK) k_radix_scatter(const uint32_t *__re
     myrank[r] = rank;
   }
   __syncthreads();
-  // per digit: exclusive prefix over warps + global base of this tile
   {
+    // thread d: this tile's count of digit d, its offset inside digit d's output range by look-back over the preceding
+    // tiles (state word = {epoch, flag, value}, published with an L2 atomic: see lb_exclusive_prefix), per-warp bases
     const int d = threadIdx.x; // 256 threads == 256 digits
-    const uint32_t dbase = block_excl_scan<RS_BLOCK>(dtot[d], nullptr); // elements with a smaller digit
-    uint32_t run = dbase + table[d * ntiles_cap + blockIdx.x];
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++)
+      cnt += wcnt[w][d];
+    atomicExch(&digit_state[(size_t)tile * 256 + d], lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, cnt));
+    uint32_t excl = 0;
+    for (int b = (int)tile - 1; b >= 0; b--) {
+      unsigned long long sv;
+      do {
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(sv) : "l"(digit_state + (size_t)b * 256 + d) : "memory");
+      } while ((uint32_t)(sv >> 34) != epoch);
+      excl += (uint32_t)sv;
+      if (((sv >> 32) & 3ull) == LB_PREFIX)
+        break;
+    }
+    if (tile > 0)
+      atomicExch(&digit_state[(size_t)tile * 256 + d], lb_pack(epoch, LB_PREFIX, excl + cnt));
+    uint32_t run = dbase[pass * 256 + d] + excl;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; w++) {
-      uint32_t c = wcnt[w][d];
+      const uint32_t c = wcnt[w][d];
       wcnt[w][d] = run;
       run += c;
     }
@@ -406,10 +451,10 @@ __global__ void __launch_bounds__(RS_BLOCK) k_radix_scatter(const uint32_t *__re
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < CH / 32; r++) {
-    int i = wbase + r * 32 + lane;
+    const int i = wbase + r * 32 + lane;
     if (i < n) {
-      uint32_t d = (myk[r] >> shift) & 255u;
-      uint32_t pos = wcnt[wid][d] + myrank[r];
+      const uint32_t d = (myk[r] >> shift) & 255u;
+      const uint32_t pos = wcnt[wid][d] + myrank[r];
       keys_out[pos] = myk[r];
       vals_out[pos] = myv[r];
     }

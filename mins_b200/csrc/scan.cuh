@@ -170,12 +170,10 @@ struct VoxGridDesc {
   int passthrough; // PCL: "Leaf size is too small" -> output = input
   float inv_leaf;
 };
-__global__ void k_voxgrid_setup(const uint32_t *__restrict__ bbox, const int *__restrict__ d_n, float leaf, VoxGridDesc *__restrict__ vg) {
-  if (threadIdx.x != 0 || blockIdx.x != 0)
-    return;
+__device__ __forceinline__ void voxgrid_setup_dev(const uint32_t *bbox, int n, float leaf, VoxGridDesc *__restrict__ vg) {
   const float inv = __fdiv_rn(1.0f, leaf);
   vg->inv_leaf = inv;
-  if (*d_n <= 0) {
+  if (n <= 0) {
     vg->passthrough = 0;
     for (int a = 0; a < 3; a++)
       vg->minb[a] = 0, vg->divb[a] = 1;
@@ -183,10 +181,7 @@ __global__ void k_voxgrid_setup(const uint32_t *__restrict__ bbox, const int *__
   }
   long long d[3];
   for (int a = 0; a < 3; a++) {
-    float mn = __uint_as_float(0), mx = 0;
-    uint32_t u0 = bbox[a], u1 = bbox[3 + a];
-    mn = __uint_as_float((u0 & 0x80000000u) ? (u0 & 0x7fffffffu) : ~u0);
-    mx = __uint_as_float((u1 & 0x80000000u) ? (u1 & 0x7fffffffu) : ~u1);
+    const float mn = ord2f(bbox[a]), mx = ord2f(bbox[3 + a]);
     d[a] = (long long)(__fmul_rn(__fsub_rn(mx, mn), inv)) + 1;
     vg->minb[a] = (int)floorf(__fmul_rn(mn, inv));
     int maxb = (int)floorf(__fmul_rn(mx, inv));
@@ -194,61 +189,230 @@ __global__ void k_voxgrid_setup(const uint32_t *__restrict__ bbox, const int *__
   }
   vg->passthrough = (d[0] * d[1] * d[2] > 2147483647ll) ? 1 : 0;
 }
-__global__ void __launch_bounds__(256) k_vox_index(const float4 *__restrict__ cloud, const int *__restrict__ d_n,
-                                                  const VoxGridDesc *__restrict__ vgd, uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= *d_n)
-    return;
-  const VoxGridDesc vg = *vgd;
-  float4 p = cloud[i];
-  int i0 = (int)floorf(__fmul_rn(p.x, vg.inv_leaf)) - vg.minb[0];
-  int i1 = (int)floorf(__fmul_rn(p.y, vg.inv_leaf)) - vg.minb[1];
-  int i2 = (int)floorf(__fmul_rn(p.z, vg.inv_leaf)) - vg.minb[2];
-  keys[i] = (uint32_t)(i0 + i1 * vg.divb[0] + i2 * vg.divb[0] * vg.divb[1]);
-  vals[i] = (uint32_t)i;
-}
-// head flag of each run of equal keys in the sorted order
-__global__ void __launch_bounds__(256) k_seg_heads(const uint32_t *__restrict__ keys, const int *__restrict__ d_n, uint32_t *__restrict__ head) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= *d_n)
-    return;
-  head[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
-}
-// one thread per sorted element that is a head: sum the run sequentially (fp32, input order inside the voxel)
-__global__ void __launch_bounds__(256) k_vox_centroid(const float4 *__restrict__ cloud, const uint32_t *__restrict__ keys,
-                                                     const uint32_t *__restrict__ vals, const uint32_t *__restrict__ head,
-                                                     const uint32_t *__restrict__ pos, const int *__restrict__ d_n,
-                                                     float4 *__restrict__ out) {
+
+// The voxel filter in 7 launches (was 15 with a 2-kernel scan, 22 with the 3-kernel radix passes):
+//   k_bbox_voxgrid     min/max of the cloud; the CTA that finishes last derives the voxel grid (PCL's getMinMax3D + leaf
+//                      arithmetic) and puts `bbox` back into its initial state (invariant: initial between uses)
+//   k_vox_index_hist   voxel index per point (sort key) + the digit histograms of all four radix passes
+//   4 x k_radix_pass   stable sort by voxel index (prims.cuh)
+//   k_vox_reduce       run heads of the sorted keys, their stable single-pass ranking (look-back), one centroid per run
+//                      summed in input order, the new count; or the unchanged copy when PCL would refuse the leaf size
+__global__ void __launch_bounds__(256) k_bbox_voxgrid(const float4 *__restrict__ pts, const int *__restrict__ d_n, uint32_t *bbox,
+                                                     unsigned int *done, float leaf, VoxGridDesc *__restrict__ vg) {
+  __shared__ float smn[8][3], smx[8][3];
+  __shared__ uint32_t s_last;
   const int n = *d_n;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n || !head[i])
-    return;
-  const uint32_t key = keys[i];
-  float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f;
-  int j = i;
-  for (; j < n && keys[j] == key; j++) {
-    float4 p = cloud[vals[j]];
-    sx = __fadd_rn(sx, p.x), sy = __fadd_rn(sy, p.y), sz = __fadd_rn(sz, p.z), sw = __fadd_rn(sw, p.w);
+  float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float4 p = pts[i];
+    mn[0] = fminf(mn[0], p.x), mx[0] = fmaxf(mx[0], p.x);
+    mn[1] = fminf(mn[1], p.y), mx[1] = fmaxf(mx[1], p.y);
+    mn[2] = fminf(mn[2], p.z), mx[2] = fmaxf(mx[2], p.z);
   }
-  float c = (float)(j - i);
-  out[pos[i]] = make_float4(__fdiv_rn(sx, c), __fdiv_rn(sy, c), __fdiv_rn(sz, c), __fdiv_rn(sw, c));
-}
-// publish the down-sampled count (or copy through when PCL would refuse the leaf size)
-__global__ void k_vox_finish(const VoxGridDesc *__restrict__ vg, const uint32_t *__restrict__ pos, int *__restrict__ d_n_inout,
-                             int *__restrict__ d_passthrough) {
-  if (threadIdx.x != 0 || blockIdx.x != 0)
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+      smn[wid][a] = mn[a], smx[wid][a] = mx[a];
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    float lo = INFINITY, hi = -INFINITY;
+    for (int w = 0; w < 8; w++)
+      lo = fminf(lo, smn[w][a]), hi = fmaxf(hi, smx[w][a]);
+    if (lo <= hi) {
+      atomicMin(&bbox[a], f2ord(lo));
+      atomicMax(&bbox[3 + a], f2ord(hi));
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    s_last = atomicAdd(done, 1u) == gridDim.x - 1u;
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0)
     return;
-  *d_passthrough = vg->passthrough;
-  if (!vg->passthrough)
-    *d_n_inout = (int)pos[*d_n_inout];
+  __threadfence();
+  uint32_t bb[6];
+  for (int c = 0; c < 6; c++) {
+    bb[c] = *(volatile uint32_t *)&bbox[c];
+    bbox[c] = c < 3 ? 0xffffffffu : 0u;
+  }
+  voxgrid_setup_dev(bb, n, leaf, vg);
+  *done = 0u;
 }
-__global__ void __launch_bounds__(256) k_copy_if_flag(const float4 *__restrict__ src, float4 *__restrict__ dst, const int *__restrict__ d_n,
-                                                     const int *__restrict__ d_flag, int want) {
-  if ((*d_flag != 0) != (want != 0))
+
+__global__ void __launch_bounds__(RS_BLOCK) k_vox_index_hist(const float4 *__restrict__ cloud, const int *__restrict__ d_n,
+                                                            const VoxGridDesc *__restrict__ vgd, uint32_t *__restrict__ keys,
+                                                            uint32_t *__restrict__ vals, uint32_t *ghist, uint32_t *__restrict__ dbase,
+                                                            unsigned int *done) {
+  __shared__ uint32_t h[RS_PASSES][256];
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + RS_TILE - 1) / RS_TILE) : 1u;
+  if (blockIdx.x >= active)
     return;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < *d_n)
-    dst[i] = src[i];
+#pragma unroll
+  for (int p = 0; p < RS_PASSES; p++)
+    h[p][threadIdx.x] = 0;
+  __syncthreads();
+  const VoxGridDesc vg = *vgd;
+  const int base = blockIdx.x * RS_TILE;
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const int i = base + k * RS_BLOCK + threadIdx.x;
+    if (i < n) {
+      const float4 p = cloud[i];
+      const int i0 = (int)floorf(__fmul_rn(p.x, vg.inv_leaf)) - vg.minb[0];
+      const int i1 = (int)floorf(__fmul_rn(p.y, vg.inv_leaf)) - vg.minb[1];
+      const int i2 = (int)floorf(__fmul_rn(p.z, vg.inv_leaf)) - vg.minb[2];
+      const uint32_t key = (uint32_t)(i0 + i1 * vg.divb[0] + i2 * vg.divb[0] * vg.divb[1]);
+      keys[i] = key;
+      vals[i] = (uint32_t)i;
+      radix_hist4_add(h, key);
+    }
+  }
+  radix_hist4_publish(h, ghist, dbase, done, active);
+}
+
+constexpr int VR_BLOCK = 256, VR_ROWS = 8, VR_TILE = VR_BLOCK * VR_ROWS;
+__global__ void __launch_bounds__(VR_BLOCK)
+    k_vox_reduce(const float4 *__restrict__ cloud, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, int *d_n,
+                 const VoxGridDesc *__restrict__ vgd, float4 *__restrict__ out, unsigned long long *tile_state, unsigned int *tile_ctr,
+                 uint32_t epoch, unsigned int *done, int *d_total, int *d_vox_n, int *d_vox_passthrough) {
+  __shared__ uint32_t wsum[VR_BLOCK / 32];
+  __shared__ uint32_t s_tile, s_prefix, s_tot, s_last;
+  __shared__ uint16_t head_off[VR_TILE];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int n = *d_n;
+  const int pass = vgd->passthrough;
+  const uint32_t active = n > 0 ? (uint32_t)((n + VR_TILE - 1) / VR_TILE) : 1u;
+  if (blockIdx.x < active) { // CTA-uniform
+    if (pass) {
+      // PCL refuses leaf sizes that overflow its int32 voxel index and returns the input unchanged
+      for (int k = 0; k < VR_ROWS; k++) {
+        const int i = blockIdx.x * VR_TILE + k * VR_BLOCK + threadIdx.x;
+        if (i < n)
+          out[i] = cloud[i];
+      }
+      if (blockIdx.x == 0 && threadIdx.x == 0)
+        *d_total = n;
+    } else {
+      if (threadIdx.x == 0)
+        s_tile = lb_ticket(tile_ctr, active);
+      __syncthreads();
+      const uint32_t tile = s_tile;
+      const int wbase = (int)tile * VR_TILE + wid * (VR_TILE / (VR_BLOCK / 32));
+      uint32_t key[VR_ROWS], bal[VR_ROWS], cnt = 0;
+#pragma unroll
+      for (int r = 0; r < VR_ROWS; r++) {
+        const int i = wbase + r * 32 + lane;
+        key[r] = i < n ? keys[i] : 0u;
+      }
+#pragma unroll
+      for (int r = 0; r < VR_ROWS; r++) {
+        const int i = wbase + r * 32 + lane;
+        // previous key: the neighbouring lane's, or (lane 0) the last key of the previous row / of the preceding chunk
+        uint32_t prev = __shfl_up_sync(0xffffffffu, key[r], 1);
+        const uint32_t prev_row_last = r > 0 ? __shfl_sync(0xffffffffu, key[r > 0 ? r - 1 : 0], 31) : 0u;
+        if (lane == 0)
+          prev = r > 0 ? prev_row_last : (i > 0 && i < n ? keys[i - 1] : 0u);
+        const bool head = i < n && (i == 0 || key[r] != prev);
+        bal[r] = __ballot_sync(0xffffffffu, head);
+        cnt += __popc(bal[r]);
+      }
+      if (lane == 0)
+        wsum[wid] = cnt;
+      __syncthreads();
+      if (wid == 0) {
+        uint32_t tot = lane < VR_BLOCK / 32 ? wsum[lane] : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+          tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
+        if (lane == 0) {
+          s_prefix = excl;
+          s_tot = tot;
+          if ((long long)tile * VR_TILE + VR_TILE >= (long long)n)
+            *d_total = (int)(excl + tot);
+        }
+      }
+      __syncthreads();
+      // the tile's run heads, in order, into shared memory; then one thread per head (strided over the CTA, so a thread
+      // that owns several heads in the load layout does not serialise their runs): the run is summed sequentially
+      // (fp32, input order inside the voxel: the sort is stable)
+      uint32_t lpos = 0;
+      for (int w = 0; w < wid; w++)
+        lpos += wsum[w];
+      const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+      for (int r = 0; r < VR_ROWS; r++) {
+        if ((bal[r] >> lane) & 1u)
+          head_off[lpos + __popc(bal[r] & lt)] = (uint16_t)(wid * (VR_TILE / (VR_BLOCK / 32)) + r * 32 + lane);
+        lpos += __popc(bal[r]);
+      }
+      __syncthreads();
+      const uint32_t tile_heads = s_tot, prefix = s_prefix;
+      for (uint32_t k = threadIdx.x; k < tile_heads; k += VR_BLOCK) {
+        const int i = (int)tile * VR_TILE + (int)head_off[k];
+        const uint32_t kk = keys[i];
+        float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f;
+        int j = i;
+        // 16 (then 4) gathers in flight at a time: the keys are sorted, so if the last of a batch still belongs to the run
+        // all of it does; the additions stay in order (runs of several hundred points exist next to the sensor)
+        while (j + 16 <= n && keys[j + 15] == kk) {
+          float4 p[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++)
+            p[u] = cloud[vals[j + u]];
+#pragma unroll
+          for (int u = 0; u < 16; u++)
+            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
+          j += 16;
+        }
+        while (j + 4 <= n && keys[j + 3] == kk) {
+          float4 p[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++)
+            p[u] = cloud[vals[j + u]];
+#pragma unroll
+          for (int u = 0; u < 4; u++)
+            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
+          j += 4;
+        }
+        for (; j < n && keys[j] == kk; j++) {
+          const float4 p = cloud[vals[j]];
+          sx = __fadd_rn(sx, p.x), sy = __fadd_rn(sy, p.y), sz = __fadd_rn(sz, p.z), sw = __fadd_rn(sw, p.w);
+        }
+        const float c = (float)(j - i);
+        out[prefix + k] = make_float4(__fdiv_rn(sx, c), __fdiv_rn(sy, c), __fdiv_rn(sz, c), __fdiv_rn(sw, c));
+      }
+    }
+  }
+  // last CTA out publishes the new count (every CTA has read the old one by then)
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0)
+    s_last = atomicAdd(done, 1u) == gridDim.x - 1u;
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0)
+    return;
+  __threadfence();
+  *done = 0u;
+  const int total = *(volatile int *)d_total;
+  if (d_vox_n)
+    *d_vox_n = pass ? 0 : total;
+  if (d_vox_passthrough)
+    *d_vox_passthrough = pass;
+  *d_n = total;
 }
 
 } // namespace ml
