@@ -642,7 +642,7 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
     if (on_device) {
       // scan already resident in HBM (e.g. produced by a device-side driver): used in place, no copy
       raw_src = xyz;
-    } else if (pinned && h->zero_copy && at.devicePointer && T_LtoM && h->map_init && h->use_fused_front) {
+    } else if (pinned && h->zero_copy && at.devicePointer && h->use_fused_front) {
       // pinned, device-mapped host memory and the one-pass front end: the kernel reads the scan straight over PCIe (each
       // point is read exactly once), so there is no separate DMA copy to wait for
       raw_src = (const float *)at.devicePointer;
@@ -657,17 +657,25 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   }
   const int tiles = cdiv(n, RF_TILE);
   float4 *in_map = T_LtoM ? h->scan_map : nullptr;
-  if (T_LtoM && h->map_init && h->use_fused_front) {
-    // one launch: range filter (single-pass stable compaction) + transform + query binning
+  if (h->use_fused_front) {
+    // one launch: range filter (single-pass stable compaction) [+ transform + query binning when the map transform is known]
     const uint32_t epoch = lb_next_epoch(h);
     const uint32_t mask = (uint32_t)h->q_slots - 1u;
-    if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0)
-      LAUNCHP(k_range_filter_bin<true>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
-              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
+    const bool vec4 = stride == 4 && (((uintptr_t)raw_src) & 15u) == 0;
+    const bool bin = T_LtoM && h->map_init;
+#define FRONT(V, B)                                                                                                    \
+  LAUNCHP((k_range_filter_bin<V, B>), tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,  \
+          h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank)
+    if (vec4 && bin)
+      FRONT(true, true);
+    else if (vec4)
+      FRONT(true, false);
+    else if (bin)
+      FRONT(false, true);
     else
-      LAUNCHP(k_range_filter_bin<false>, tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
-              h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank);
-    h->bin_done = true;
+      FRONT(false, false);
+#undef FRONT
+    h->bin_done = bin;
     return check_launch(h);
   }
   if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0) {

@@ -80,10 +80,10 @@ __global__ void __launch_bounds__(256) k_query_bin(const float4 *__restrict__ q_
 // with decoupled look-back (tile b publishes its count, then the running prefix; a later tile adds counts backwards until
 // it meets a prefix), the fp32 transform into the map frame (LidarHelper.cpp:192) and the query binning, all on the
 // registers that hold the freshly loaded points. Replaces k_range_count + k_range_compact + k_query_bin (3 launches, 2 extra
-// passes over the scan). Tiles are handed out by an atomic ticket, so every tile a CTA waits for belongs to a CTA that is
+// passes over the scan). BIN = false stops after the compaction (a down-sampling pass follows, or there is no map yet). Tiles are handed out by an atomic ticket, so every tile a CTA waits for belongs to a CTA that is
 // already running: the look-back cannot deadlock whatever the grid size. States carry a per-scan epoch: no reset pass.
 // ------------------------------------------------------------------------------------------------
-template <bool VEC4>
+template <bool VEC4, bool BIN>
 __global__ void __launch_bounds__(RF_BLOCK)
     k_range_filter_bin(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax, ScanState *__restrict__ st,
                        float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
@@ -144,12 +144,16 @@ __global__ void __launch_bounds__(RF_BLOCK)
       const float4 q = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
       cloud[o] = q;
       orig[o] = q;
-      const float4 qm = tf_apply(T, q);
-      in_map[o] = qm;
-      uint32_t s, rk;
-      bin_query(qm, bal[r], gd, tab, mask, &s, &rk);
-      q_slot[o] = s;
-      q_rank[o] = rk;
+      if (BIN) {
+        const float4 qm = tf_apply(T, q);
+        in_map[o] = qm;
+        uint32_t s, rk;
+        bin_query(qm, bal[r], gd, tab, mask, &s, &rk);
+        q_slot[o] = s;
+        q_rank[o] = rk;
+      } else if (in_map) { // transform known but no binning yet (no map, or a down-sampling pass follows)
+        in_map[o] = tf_apply(T, q);
+      }
     }
     pos += __popc(bal[r]);
   }
