@@ -106,7 +106,7 @@ struct DevConsts {
   double Qu[ML_G * (ML_G + 1) / 2]; // packed upper triangle of Q by rows, off-diagonal entries doubled
 };
 
-// Per-point result of k_rows, consumed by the fixed-order reduction.
+// Per-point result of point_row (k_rows_reduce), consumed by the fixed-order reduction.
 struct PointRow {
   double g[ML_G]; // whitened: g / raw_noise
   double w;       // ||v||^2

@@ -108,8 +108,8 @@ __device__ __forceinline__ uint32_t lb_exclusive_prefix(unsigned long long *tile
 // a lane holds 4 consecutive ones (one 16-byte access; a warp instruction covers 512 contiguous bytes).
 // ZERO_IN: non-zero inputs are zeroed once read (the kNN grid's cell counters: all-zero again after the build, without a
 // clearing pass over the mostly empty dense grid).
-// Two drivers share the tile code: k_scan_lb (one pass, decoupled look-back) and k_scan_reduce + k_scan_apply (two passes,
-// no inter-CTA waiting). scripts/bench_scan.cu measures both; api.cu uses the faster one for each input size.
+// Driver: k_scan_lb (one pass, decoupled look-back). scripts/bench_scan.cu holds the two-pass alternative (reduce + apply on the
+// same tile code) it was measured against: 37 us vs 30 us on the 13.5 M cell counters.
 // ------------------------------------------------------------------------------------------------
 template <int ITEMS, bool ZERO_IN> struct ScanTile {
   static constexpr int ROWS = ITEMS / 4, TILE = SCAN_BLOCK * ITEMS;
@@ -236,75 +236,10 @@ __global__ void __launch_bounds__(SCAN_BLOCK) k_scan_lb(uint32_t *in, const int 
   }
 }
 
-// pass 1 of the two-pass scan: tile sums; the CTA that finishes last turns them into exclusive tile prefixes in place
-// (tile_sums[active] = total). `done` must be 0 on entry and is 0 again on exit.
-template <int ITEMS>
-__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_reduce(uint32_t *in, const int *__restrict__ d_n, uint32_t *tile_sums,
-                                                           unsigned int *done) {
-  constexpr int TILE = SCAN_BLOCK * ITEMS;
-  __shared__ uint32_t s_last;
-  const int n = *d_n;
-  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
-  if (blockIdx.x >= active)
-    return;
-  ScanTile<ITEMS, false> t;
-  t.load(in, (long long)blockIdx.x * TILE, n);
-  const uint32_t tot = t.reduce();
-  if (threadIdx.x == 0) {
-    *(volatile uint32_t *)&tile_sums[blockIdx.x] = tot;
-    __threadfence();
-    s_last = atomicAdd(done, 1u) == active - 1u;
-  }
-  __syncthreads();
-  if (!s_last)
-    return;
-  __threadfence();
-  // one CTA, thread t owns a contiguous chunk of the tile sums
-  const uint32_t per = (active + SCAN_BLOCK - 1) / SCAN_BLOCK;
-  const uint32_t lo = min(threadIdx.x * per, active), hi = min(lo + per, active);
-  volatile uint32_t *ts = tile_sums;
-  uint32_t s = 0;
-  for (uint32_t i = lo; i < hi; i++)
-    s += ts[i];
-  uint32_t total;
-  uint32_t e = block_excl_scan<SCAN_BLOCK>(s, &total);
-  for (uint32_t i = lo; i < hi; i++) {
-    const uint32_t v = ts[i];
-    ts[i] = e;
-    e += v;
-  }
-  if (threadIdx.x == 0) {
-    ts[active] = total;
-    *done = 0u;
-  }
-}
-
-// pass 2: scan inside the tile on top of the tile's exclusive prefix
-template <int ITEMS, bool ZERO_IN>
-__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(uint32_t *in, const int *__restrict__ d_n, const uint32_t *__restrict__ tile_sums,
-                                                          uint32_t *__restrict__ out, int *__restrict__ d_total) {
-  constexpr int TILE = SCAN_BLOCK * ITEMS;
-  const int n = *d_n;
-  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
-  if (blockIdx.x >= active)
-    return;
-  const long long base = (long long)blockIdx.x * TILE;
-  const uint32_t prefix = tile_sums[blockIdx.x];
-  ScanTile<ITEMS, ZERO_IN> t;
-  t.load(in, base, n);
-  const uint32_t tot = t.scan();
-  t.store(out, base, n, prefix);
-  if (base + TILE >= (long long)n && threadIdx.x == 0) {
-    out[n] = prefix + tot;
-    if (d_total)
-      *d_total = (int)(prefix + tot);
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // Stable LSD radix sort, 8 bits per pass, of (key uint32, value uint32) pairs; n on the device.
-// One histogram kernel for all passes (k_radix_hist4: the keys are read once, the CTA that finishes last turns the four
-// digit histograms into digit bases), then ONE kernel per pass (k_radix_pass): stable in-tile ranking with warp match_any
+// One histogram for all passes, built by the kernel that produces the keys (radix_hist4_add / radix_hist4_publish, used by
+// k_vox_index_hist: the CTA that finishes last turns the four digit histograms into digit bases), then ONE kernel per pass (k_radix_pass): stable in-tile ranking with warp match_any
 // (warps own consecutive chunks), and the tile's offset inside every digit's output range by a decoupled look-back per digit
 // (thread d follows digit d through the preceding tiles). 5 launches for a 32-bit sort instead of 12.
 // ------------------------------------------------------------------------------------------------
@@ -348,27 +283,6 @@ __device__ __forceinline__ void radix_hist4_add(uint32_t (*h)[256], uint32_t key
 #pragma unroll
   for (int p = 0; p < RS_PASSES; p++)
     atomicAdd(&h[p][(key >> (8 * p)) & 255u], 1u);
-}
-
-__global__ void __launch_bounds__(RS_BLOCK) k_radix_hist4(const uint32_t *__restrict__ keys, const int *__restrict__ d_n,
-                                                         uint32_t *ghist, uint32_t *__restrict__ dbase, unsigned int *done) {
-  __shared__ uint32_t h[RS_PASSES][256];
-  const int n = *d_n;
-  const uint32_t active = n > 0 ? (uint32_t)((n + RS_TILE - 1) / RS_TILE) : 1u;
-  if (blockIdx.x >= active)
-    return;
-#pragma unroll
-  for (int p = 0; p < RS_PASSES; p++)
-    h[p][threadIdx.x] = 0;
-  __syncthreads();
-  const int base = blockIdx.x * RS_TILE;
-#pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    const int i = base + k * RS_BLOCK + threadIdx.x;
-    if (i < n)
-      radix_hist4_add(h, keys[i]);
-  }
-  radix_hist4_publish(h, ghist, dbase, done, active);
 }
 
 template <int ITEMS>

@@ -162,8 +162,8 @@ __global__ void __launch_bounds__(256) k_deskew(float4 *__restrict__ cloud, cons
 
 // ---- pcl::VoxelGrid<PointXYZI>, LidarHelper.cpp:89-101,214 -------------------------------------------
 // PCL 1.10 filters/impl/voxel_grid.hpp: bounds -> min_b/div_b -> linear voxel index -> sort -> centroids in
-// ascending index. Here: bbox reduce, k_vox_index, stable radix sort by index (ties in input order), segment
-// heads, one thread per voxel sums its points sequentially in fp32 and divides by the count.
+// ascending index. Here: bbox reduce, voxel index, stable radix sort by index (ties in input order), run heads, one thread
+// per voxel sums its points sequentially in fp32 and divides by the count (kernel list below).
 struct VoxGridDesc {
   int minb[3];
   int divb[3];

@@ -5,6 +5,73 @@
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
+namespace ml {
+// pass 1 of the two-pass scan: tile sums; the CTA that finishes last turns them into exclusive tile prefixes in place
+// (tile_sums[active] = total). `done` must be 0 on entry and is 0 again on exit.
+template <int ITEMS>
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_reduce(uint32_t *in, const int *__restrict__ d_n, uint32_t *tile_sums,
+                                                           unsigned int *done) {
+  constexpr int TILE = SCAN_BLOCK * ITEMS;
+  __shared__ uint32_t s_last;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
+    return;
+  ScanTile<ITEMS, false> t;
+  t.load(in, (long long)blockIdx.x * TILE, n);
+  const uint32_t tot = t.reduce();
+  if (threadIdx.x == 0) {
+    *(volatile uint32_t *)&tile_sums[blockIdx.x] = tot;
+    __threadfence();
+    s_last = atomicAdd(done, 1u) == active - 1u;
+  }
+  __syncthreads();
+  if (!s_last)
+    return;
+  __threadfence();
+  // one CTA, thread t owns a contiguous chunk of the tile sums
+  const uint32_t per = (active + SCAN_BLOCK - 1) / SCAN_BLOCK;
+  const uint32_t lo = min(threadIdx.x * per, active), hi = min(lo + per, active);
+  volatile uint32_t *ts = tile_sums;
+  uint32_t s = 0;
+  for (uint32_t i = lo; i < hi; i++)
+    s += ts[i];
+  uint32_t total;
+  uint32_t e = block_excl_scan<SCAN_BLOCK>(s, &total);
+  for (uint32_t i = lo; i < hi; i++) {
+    const uint32_t v = ts[i];
+    ts[i] = e;
+    e += v;
+  }
+  if (threadIdx.x == 0) {
+    ts[active] = total;
+    *done = 0u;
+  }
+}
+
+// pass 2: scan inside the tile on top of the tile's exclusive prefix
+template <int ITEMS, bool ZERO_IN>
+__global__ void __launch_bounds__(SCAN_BLOCK) k_scan_apply(uint32_t *in, const int *__restrict__ d_n, const uint32_t *__restrict__ tile_sums,
+                                                          uint32_t *__restrict__ out, int *__restrict__ d_total) {
+  constexpr int TILE = SCAN_BLOCK * ITEMS;
+  const int n = *d_n;
+  const uint32_t active = n > 0 ? (uint32_t)((n + TILE - 1) / TILE) : 1u;
+  if (blockIdx.x >= active)
+    return;
+  const long long base = (long long)blockIdx.x * TILE;
+  const uint32_t prefix = tile_sums[blockIdx.x];
+  ScanTile<ITEMS, ZERO_IN> t;
+  t.load(in, base, n);
+  const uint32_t tot = t.scan();
+  t.store(out, base, n, prefix);
+  if (base + TILE >= (long long)n && threadIdx.x == 0) {
+    out[n] = prefix + tot;
+    if (d_total)
+      *d_total = (int)(prefix + tot);
+  }
+}
+
+} // namespace ml
 using namespace ml;
 
 #define CK(x)                                                                                                          \
