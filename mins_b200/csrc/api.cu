@@ -548,15 +548,23 @@ int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
 
 // voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated (scan.cuh: 7 launches). n_ub host bound. tmp buffers: sort_*.
 // d_vox_n / d_vox_pass (may be NULL): occupied voxels and PCL's "leaf too small" verdict, for the scan state.
-static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf, int *d_vox_n, int *d_vox_pass) {
+// bin: the output is the scan's query cloud - also transform it by h->T_LtoM into scan_map and bin it for the kNN.
+static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf, int *d_vox_n, int *d_vox_pass, bool bin) {
   if (n_ub <= 0)
     return ML_OK;
   LAUNCH(k_bbox_voxgrid, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox_vg, h->mg_done, leaf, h->d_vg);
   LAUNCH(k_vox_index_hist, cdiv(n_ub, RS_TILE), RS_BLOCK, src, d_n, h->d_vg, h->sort_keys[0], h->sort_vals[0], h->radix_ghist,
          h->radix_dbase, h->mg_done);
   radix_sort(h, d_n, n_ub, 32);
-  LAUNCH(k_vox_reduce, cdiv(n_ub, VR_TILE), VR_BLOCK, src, h->sort_keys[0], h->sort_vals[0], d_n, h->d_vg, dst, h->lb_state, h->lb_ctr,
-         lb_next_epoch(h), h->mg_done, h->d_ints + 6, d_vox_n, d_vox_pass);
+  const uint32_t mask = (uint32_t)h->q_slots - 1u;
+  if (bin)
+    LAUNCH(k_vox_reduce<true>, cdiv(n_ub, VR_TILE), VR_BLOCK, src, h->sort_keys[0], h->sort_vals[0], d_n, h->d_vg, dst, h->lb_state,
+           h->lb_ctr, lb_next_epoch(h), h->mg_done, h->d_ints + 6, d_vox_n, d_vox_pass, h->T_LtoM, h->scan_map, h->d_grid, h->qtab, mask,
+           h->q_slot, h->q_rank);
+  else
+    LAUNCH(k_vox_reduce<false>, cdiv(n_ub, VR_TILE), VR_BLOCK, src, h->sort_keys[0], h->sort_vals[0], d_n, h->d_vg, dst, h->lb_state,
+           h->lb_ctr, lb_next_epoch(h), h->mg_done, h->d_ints + 6, d_vox_n, d_vox_pass, h->T_LtoM, (float4 *)nullptr,
+           (const GridDesc *)nullptr, (QSlot *)nullptr, mask, (uint32_t *)nullptr, (uint32_t *)nullptr);
   return check_launch(h);
 }
 
@@ -572,7 +580,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
   int *d_n = h->d_ints + 5;
   LAUNCH(k_copy_int, 1, 1, d_n, h->d_map_n);
   if (do_downsample) {
-    int rc = voxel_filter(h, src, h->scan_tmp, d_n, M, ds, nullptr, nullptr);
+    int rc = voxel_filter(h, src, h->scan_tmp, d_n, M, ds, nullptr, nullptr, false);
     if (rc)
       return rc;
     src = h->scan_tmp;
@@ -744,20 +752,34 @@ int ml_scan_deskew(ml_handle *h, const float *T_LitoL_knots, int n_knots, int to
   return check_launch(h);
 }
 
-static int scan_downsample_async(ml_handle *h, float leaf) {
+// T_LtoM != NULL (one-call path): the map transform is already known, so the filter's last kernel also produces
+// pointcloud_in_map and bins the queries (what ml_scan_transform and the binning launch would do next)
+static int scan_downsample_async(ml_handle *h, float leaf, const float *T_LtoM) {
   if (!(leaf > 0.f))
     return fail(h, ML_ERR_ARG, "ml_scan_downsample: leaf must be positive");
-  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf, ST(vox_n), ST(vox_passthrough));
+  const bool bin = T_LtoM && h->map_init && h->use_fused_front && h->n_raw > 0;
+  drop_stale_bins(h);
+  if (bin) {
+    for (int r = 0; r < 3; r++)
+      for (int c = 0; c < 4; c++)
+        h->T_LtoM.m[4 * r + c] = T_LtoM[4 * r + c];
+  }
+  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf, ST(vox_n), ST(vox_passthrough), bin);
   if (rc)
     return rc;
   std::swap(h->scan_pts, h->scan_tmp);
+  h->rows_valid = false;
+  if (bin) {
+    h->have_T = true;
+    h->bin_done = true;
+  }
   return ML_OK;
 }
 
 int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds) {
   if (!h)
     return ML_ERR_ARG;
-  int rc = scan_downsample_async(h, leaf);
+  int rc = scan_downsample_async(h, leaf, nullptr);
   if (rc)
     return rc;
   if (n_ds) {
@@ -1140,7 +1162,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
   if (h->timing == 1)
     cudaEventRecord(h->ev[1], h->stream);
   if (ds) {
-    rc = scan_downsample_async(h, leaf);
+    rc = scan_downsample_async(h, leaf, T_LtoM);
     if (rc) {
       cudaStreamSynchronize(h->stream2);
       return rc;
@@ -1148,7 +1170,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
   }
   if (h->timing == 1)
     cudaEventRecord(h->ev[2], h->stream);
-  if (ds) {
+  if (ds && !h->bin_done) { // not fused (MINS_NO_FUSED_FRONT=1): separate transform, binning inside the kNN stage
     rc = scan_transform_async(h, T_LtoM);
     if (rc) {
       cudaStreamSynchronize(h->stream2);

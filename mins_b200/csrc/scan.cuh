@@ -195,7 +195,7 @@ __device__ __forceinline__ void voxgrid_setup_dev(const uint32_t *bbox, int n, f
 //                      arithmetic) and puts `bbox` back into its initial state (invariant: initial between uses)
 //   k_vox_index_hist   voxel index per point (sort key) + the digit histograms of all four radix passes
 //   4 x k_radix_pass   stable sort by voxel index (prims.cuh)
-//   k_vox_reduce       run heads of the sorted keys, their stable single-pass ranking (look-back), one centroid per run
+//   k_vox_reduce       (update.cuh) run heads of the sorted keys, their stable single-pass ranking (look-back), one centroid per run
 //                      summed in input order, the new count; or the unchanged copy when PCL would refuse the leaf size
 __global__ void __launch_bounds__(256) k_bbox_voxgrid(const float4 *__restrict__ pts, const int *__restrict__ d_n, uint32_t *bbox,
                                                      unsigned int *done, float leaf, VoxGridDesc *__restrict__ vg) {
@@ -281,138 +281,6 @@ __global__ void __launch_bounds__(RS_BLOCK) k_vox_index_hist(const float4 *__res
     }
   }
   radix_hist4_publish(h, ghist, dbase, done, active);
-}
-
-constexpr int VR_BLOCK = 256, VR_ROWS = 8, VR_TILE = VR_BLOCK * VR_ROWS;
-__global__ void __launch_bounds__(VR_BLOCK)
-    k_vox_reduce(const float4 *__restrict__ cloud, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, int *d_n,
-                 const VoxGridDesc *__restrict__ vgd, float4 *__restrict__ out, unsigned long long *tile_state, unsigned int *tile_ctr,
-                 uint32_t epoch, unsigned int *done, int *d_total, int *d_vox_n, int *d_vox_passthrough) {
-  __shared__ uint32_t wsum[VR_BLOCK / 32];
-  __shared__ uint32_t s_tile, s_prefix, s_tot, s_last;
-  __shared__ uint16_t head_off[VR_TILE];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int n = *d_n;
-  const int pass = vgd->passthrough;
-  const uint32_t active = n > 0 ? (uint32_t)((n + VR_TILE - 1) / VR_TILE) : 1u;
-  if (blockIdx.x < active) { // CTA-uniform
-    if (pass) {
-      // PCL refuses leaf sizes that overflow its int32 voxel index and returns the input unchanged
-      for (int k = 0; k < VR_ROWS; k++) {
-        const int i = blockIdx.x * VR_TILE + k * VR_BLOCK + threadIdx.x;
-        if (i < n)
-          out[i] = cloud[i];
-      }
-      if (blockIdx.x == 0 && threadIdx.x == 0)
-        *d_total = n;
-    } else {
-      if (threadIdx.x == 0)
-        s_tile = lb_ticket(tile_ctr, active);
-      __syncthreads();
-      const uint32_t tile = s_tile;
-      const int wbase = (int)tile * VR_TILE + wid * (VR_TILE / (VR_BLOCK / 32));
-      uint32_t key[VR_ROWS], bal[VR_ROWS], cnt = 0;
-#pragma unroll
-      for (int r = 0; r < VR_ROWS; r++) {
-        const int i = wbase + r * 32 + lane;
-        key[r] = i < n ? keys[i] : 0u;
-      }
-#pragma unroll
-      for (int r = 0; r < VR_ROWS; r++) {
-        const int i = wbase + r * 32 + lane;
-        // previous key: the neighbouring lane's, or (lane 0) the last key of the previous row / of the preceding chunk
-        uint32_t prev = __shfl_up_sync(0xffffffffu, key[r], 1);
-        const uint32_t prev_row_last = r > 0 ? __shfl_sync(0xffffffffu, key[r > 0 ? r - 1 : 0], 31) : 0u;
-        if (lane == 0)
-          prev = r > 0 ? prev_row_last : (i > 0 && i < n ? keys[i - 1] : 0u);
-        const bool head = i < n && (i == 0 || key[r] != prev);
-        bal[r] = __ballot_sync(0xffffffffu, head);
-        cnt += __popc(bal[r]);
-      }
-      if (lane == 0)
-        wsum[wid] = cnt;
-      __syncthreads();
-      if (wid == 0) {
-        uint32_t tot = lane < VR_BLOCK / 32 ? wsum[lane] : 0u;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-          tot += __shfl_xor_sync(0xffffffffu, tot, o);
-        const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
-        if (lane == 0) {
-          s_prefix = excl;
-          s_tot = tot;
-          if ((long long)tile * VR_TILE + VR_TILE >= (long long)n)
-            *d_total = (int)(excl + tot);
-        }
-      }
-      __syncthreads();
-      // the tile's run heads, in order, into shared memory; then one thread per head (strided over the CTA, so a thread
-      // that owns several heads in the load layout does not serialise their runs): the run is summed sequentially
-      // (fp32, input order inside the voxel: the sort is stable)
-      uint32_t lpos = 0;
-      for (int w = 0; w < wid; w++)
-        lpos += wsum[w];
-      const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll
-      for (int r = 0; r < VR_ROWS; r++) {
-        if ((bal[r] >> lane) & 1u)
-          head_off[lpos + __popc(bal[r] & lt)] = (uint16_t)(wid * (VR_TILE / (VR_BLOCK / 32)) + r * 32 + lane);
-        lpos += __popc(bal[r]);
-      }
-      __syncthreads();
-      const uint32_t tile_heads = s_tot, prefix = s_prefix;
-      for (uint32_t k = threadIdx.x; k < tile_heads; k += VR_BLOCK) {
-        const int i = (int)tile * VR_TILE + (int)head_off[k];
-        const uint32_t kk = keys[i];
-        float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f;
-        int j = i;
-        // 16 (then 4) gathers in flight at a time: the keys are sorted, so if the last of a batch still belongs to the run
-        // all of it does; the additions stay in order (runs of several hundred points exist next to the sensor)
-        while (j + 16 <= n && keys[j + 15] == kk) {
-          float4 p[16];
-#pragma unroll
-          for (int u = 0; u < 16; u++)
-            p[u] = cloud[vals[j + u]];
-#pragma unroll
-          for (int u = 0; u < 16; u++)
-            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
-          j += 16;
-        }
-        while (j + 4 <= n && keys[j + 3] == kk) {
-          float4 p[4];
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            p[u] = cloud[vals[j + u]];
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
-          j += 4;
-        }
-        for (; j < n && keys[j] == kk; j++) {
-          const float4 p = cloud[vals[j]];
-          sx = __fadd_rn(sx, p.x), sy = __fadd_rn(sy, p.y), sz = __fadd_rn(sz, p.z), sw = __fadd_rn(sw, p.w);
-        }
-        const float c = (float)(j - i);
-        out[prefix + k] = make_float4(__fdiv_rn(sx, c), __fdiv_rn(sy, c), __fdiv_rn(sz, c), __fdiv_rn(sw, c));
-      }
-    }
-  }
-  // last CTA out publishes the new count (every CTA has read the old one by then)
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0)
-    s_last = atomicAdd(done, 1u) == gridDim.x - 1u;
-  __syncthreads();
-  if (!s_last || threadIdx.x != 0)
-    return;
-  __threadfence();
-  *done = 0u;
-  const int total = *(volatile int *)d_total;
-  if (d_vox_n)
-    *d_vox_n = pass ? 0 : total;
-  if (d_vox_passthrough)
-    *d_vox_passthrough = pass;
-  *d_n = total;
 }
 
 } // namespace ml
