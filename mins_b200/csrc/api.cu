@@ -68,6 +68,7 @@ struct ml_handle {
   bool merge_pending = false;       // a k_map_merge is in flight: map_n / overflow not yet read back (resolve_merge)
   const char *merge_who = "";
   bool bin_done = false; // the queries of the resident scan are already in the hash table (fused front end)
+  bool vg_ready = false; // d_vg already holds the voxel grid of the resident scan for the leaf of this call (fused front end)
   int n_raw = 0;     // host-known upper bound of the scan size
   bool have_T = false;
   Tf32 T_LtoM;
@@ -549,10 +550,12 @@ int ml_map_add_scan(ml_handle *h, int downsample, float ds, int *n_live) {
 // voxel-grid centroid filter of src[0..*d_n) -> dst, *d_n updated (scan.cuh: 7 launches). n_ub host bound. tmp buffers: sort_*.
 // d_vox_n / d_vox_pass (may be NULL): occupied voxels and PCL's "leaf too small" verdict, for the scan state.
 // bin: the output is the scan's query cloud - also transform it by h->T_LtoM into scan_map and bin it for the kNN.
-static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf, int *d_vox_n, int *d_vox_pass, bool bin) {
+static int voxel_filter(ml_handle *h, const float4 *src, float4 *dst, int *d_n, int n_ub, float leaf, int *d_vox_n, int *d_vox_pass, bool bin,
+                        bool have_vg = false) {
   if (n_ub <= 0)
     return ML_OK;
-  LAUNCH(k_bbox_voxgrid, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox_vg, h->mg_done, leaf, h->d_vg);
+  if (!have_vg)
+    LAUNCH(k_bbox_voxgrid, std::min(148 * 8, cdiv(n_ub, 256)), 256, src, d_n, h->d_bbox_vg, h->mg_done, leaf, h->d_vg);
   LAUNCH(k_vox_index_hist, cdiv(n_ub, RS_TILE), RS_BLOCK, src, d_n, h->d_vg, h->sort_keys[0], h->sort_vals[0], h->radix_ghist,
          h->radix_dbase, h->mg_done);
   radix_sort(h, d_n, n_ub, 32);
@@ -620,7 +623,9 @@ int ml_map_size(ml_handle *h, int *n) {
 // ---------------------------------------------------------------------------------------------- scan
 // LiDARData ctor on the device. T_LtoM (may be NULL): when the map transform is already known the compaction pass writes
 // pointcloud_in_map as well (LidarHelper.cpp:192), saving one pass over the scan.
-static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM) {
+// vg_leaf > 0: a voxel filter with this leaf follows at once (one-call path): the front end also prepares its grid (h->vg_ready)
+static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM,
+                             float vg_leaf = 0.f) {
   if (n < 0 || (n > 0 && !xyz) || (stride != 3 && stride != 4))
     return fail(h, ML_ERR_ARG, "ml_scan_upload: bad argument (stride must be 3 or 4)");
   if (n > h->cap_scan)
@@ -629,6 +634,7 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
   h->n_raw = n;
   h->have_T = false;
   h->rows_valid = false;
+  h->vg_ready = false;
   if (T_LtoM) {
     for (int r = 0; r < 3; r++)
       for (int c = 0; c < 4; c++)
@@ -673,7 +679,8 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
     const bool bin = T_LtoM && h->map_init;
 #define FRONT(V, B)                                                                                                    \
   LAUNCHP((k_range_filter_bin<V, B>), tiles, RF_BLOCK, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,  \
-          h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank)
+          h->scan_orig, h->T_LtoM, in_map, h->lb_state, h->lb_ctr, epoch, h->d_grid, h->qtab, mask, h->q_slot, h->q_rank, bin ? 0.f : vg_leaf,        \
+          h->d_bbox_vg, h->mg_done, h->d_vg)
     if (vec4 && bin)
       FRONT(true, true);
     else if (vec4)
@@ -684,6 +691,7 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
       FRONT(false, false);
 #undef FRONT
     h->bin_done = bin;
+    h->vg_ready = !bin && vg_leaf > 0.f;
     return check_launch(h);
   }
   if (stride == 4 && (((uintptr_t)raw_src) & 15u) == 0) {
@@ -723,6 +731,7 @@ int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
   h->n_raw = n;
   h->have_T = false;
   h->rows_valid = false;
+  h->vg_ready = false;
   ScanState st;
   memset(&st, 0, sizeof(st));
   st.n_raw = st.n_orig = st.n_scan = n;
@@ -764,7 +773,8 @@ static int scan_downsample_async(ml_handle *h, float leaf, const float *T_LtoM) 
       for (int c = 0; c < 4; c++)
         h->T_LtoM.m[4 * r + c] = T_LtoM[4 * r + c];
   }
-  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf, ST(vox_n), ST(vox_passthrough), bin);
+  int rc = voxel_filter(h, h->scan_pts, h->scan_tmp, ST(n_scan), h->n_raw, leaf, ST(vox_n), ST(vox_passthrough), bin, h->vg_ready);
+  h->vg_ready = false;
   if (rc)
     return rc;
   std::swap(h->scan_pts, h->scan_tmp);
@@ -1152,7 +1162,7 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     cudaEventRecord(h->ev[0], h->stream);
   const bool ds = leaf > 0.f;
   // without down-sampling the compaction pass also writes pointcloud_in_map
-  rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax, ds ? nullptr : T_LtoM);
+  rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax, ds ? nullptr : T_LtoM, ds ? leaf : 0.f);
   if (rc)
     return rc;
   // the constants are enqueued after the scan so that the GPU already works while the host stages them

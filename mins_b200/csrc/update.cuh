@@ -253,7 +253,8 @@ __global__ void __launch_bounds__(RF_BLOCK)
                        float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
                        unsigned long long *tile_state, unsigned int *tile_ctr, uint32_t epoch,
                        const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask, uint32_t *__restrict__ q_slot,
-                       uint32_t *__restrict__ q_rank) {
+                       uint32_t *__restrict__ q_rank, float vg_leaf, uint32_t *vg_bbox, unsigned int *vg_done,
+                       VoxGridDesc *__restrict__ vg) {
   __shared__ uint32_t wsum[RF_BLOCK / 32];
   __shared__ uint32_t s_tile, s_prefix;
   pdl_enter();
@@ -320,6 +321,60 @@ __global__ void __launch_bounds__(RF_BLOCK)
       }
     }
     pos += __popc(bal[r]);
+  }
+  if (!BIN && vg_leaf > 0.f) {
+    // a voxel filter follows (one-call path with down-sampling): its first kernel (k_bbox_voxgrid: bounds of the kept points,
+    // voxel grid by the CTA that finishes last) is done here on the registers that hold the points
+    __shared__ float smn[RF_BLOCK / 32][3], smx[RF_BLOCK / 32][3];
+    __shared__ uint32_t s_last;
+    float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+      if ((bal[r] >> lane) & 1u) {
+        mn[0] = fminf(mn[0], pt[r].x), mx[0] = fmaxf(mx[0], pt[r].x);
+        mn[1] = fminf(mn[1], pt[r].y), mx[1] = fmaxf(mx[1], pt[r].y);
+        mn[2] = fminf(mn[2], pt[r].z), mx[2] = fmaxf(mx[2], pt[r].z);
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+        mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+        smn[wid][a] = mn[a], smx[wid][a] = mx[a];
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      const int a = threadIdx.x;
+      float lo = INFINITY, hi = -INFINITY;
+      for (int w = 0; w < RF_BLOCK / 32; w++)
+        lo = fminf(lo, smn[w][a]), hi = fmaxf(hi, smx[w][a]);
+      if (lo <= hi) {
+        atomicMin(&vg_bbox[a], f2ord(lo));
+        atomicMax(&vg_bbox[3 + a], f2ord(hi));
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0)
+      s_last = atomicAdd(vg_done, 1u) == gridDim.x - 1u;
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+      __threadfence();
+      uint32_t bb[6];
+      for (int c = 0; c < 6; c++) {
+        bb[c] = *(volatile uint32_t *)&vg_bbox[c];
+        vg_bbox[c] = c < 3 ? 0xffffffffu : 0u;
+      }
+      voxgrid_setup_dev(bb, *(volatile int *)&st->n_scan, vg_leaf, vg);
+      *vg_done = 0u;
+    }
   }
 }
 
