@@ -66,10 +66,10 @@ class GpuBackend:
             self.m.feed_scan(scan["xyz"], scan["t_rel"], op)
             self.m.transform_to_map(T_LtoM)
             self.resident = scan["key"]
-        return self.m.register_scan(op)
+        return self.m.register_scan(op, wait=False)  # like the C++ shim: queued behind the scan's kernels, not waited for
 
     def reanchor(self, T_old_to_new, now_minus_FT, op):
-        return self.m.propagate_map_to_newest_clone(T_old_to_new, now_minus_FT, op)
+        return self.m.propagate_map_to_newest_clone(T_old_to_new, now_minus_FT, op, wait=False)
 
     def map_size(self):
         return self.m.size()

@@ -492,6 +492,51 @@ def test_full_size_g64_properties(make_map, po, workload):
     assert n_before < n_after <= n_before + c["n_points"]
 
 
+def test_one_call_downsampling_path_equals_the_separate_calls(make_map, po, workload):
+    """ml_scan_update with leaf > 0 (front end that also derives the voxel grid, voxel filter whose last kernel transforms and
+    bins the centroids) against ml_scan_upload -> ml_scan_downsample -> ml_scan_transform -> ml_linsys: same clouds, same
+    reduced system, for pageable / pinned / device input, ragged and tiny sizes, a scan the range gate rejects entirely,
+    and a leaf PCL would refuse."""
+    import ctypes as C
+    import torch
+    from mins_b200 import capi
+    w = workload("G-vlp")
+    op = w["op"]
+    m = make_map(max_map_points=1 << 19)
+    m.Build(w["map"])
+    hx = w["total_hx"]
+    T = np.ascontiguousarray(w["T_LtoM"], np.float32)
+    P = np.ascontiguousarray(w["P"], np.float64)
+    raw = np.ascontiguousarray(w["raw"], np.float32).copy()
+    raw[::3, :3] *= 1000.0
+    far = raw.copy()
+    far[:, :3] = 5000.0
+    for leaf in (0.3, 1.0, 1e-6):
+        for sub in (raw, raw[:2048 * 3 + 17], raw[:33], raw[:1], far[:4096]):
+            sub = np.ascontiguousarray(sub)
+            n = len(sub)
+            kept = m.feed_scan(sub, w["t_rel"], op)
+            n_ds = C.c_int()
+            assert m.lib.ml_scan_downsample(m.h, leaf, C.byref(n_ds)) == 0
+            m.transform_to_map(T)
+            rc0, HtH0, Htr0, cnt0 = m.linsys(w["consts"], P)
+            s0 = (m.scan(0), m.scan(1), m.scan(2))
+            assert len(s0[0]) == n_ds.value <= kept
+            # (centroid values against the oracle: test_voxel_downsample_membership_order_and_centroids; here only the count)
+            in_range = po.range_filter(sub, w["t_rel"], op.max_range, op.min_range)
+            assert len(s0[0]) == (len(po.voxel_downsample(in_range, leaf)[0]) if len(in_range) else 0)
+            pinned = torch.from_numpy(sub).pin_memory()
+            dev = torch.from_numpy(sub).cuda()
+            for ptr in (sub.ctypes.data, pinned.data_ptr(), dev.data_ptr()):
+                for _ in range(2):
+                    HtH, Htr, cnt = np.zeros((hx, hx)), np.zeros(hx), capi.ml_counters()
+                    rc = m.lib.ml_scan_update(m.h, ptr, 4, n, w["t_rel"], op.min_range, op.max_range, leaf, T.ctypes.data,
+                                              C.byref(w["consts"]), P.ctypes.data, HtH.ctypes.data, Htr.ctypes.data, C.byref(cnt))
+                    assert rc == rc0
+                    assert np.array_equal(m.scan(0), s0[0]) and np.array_equal(m.scan(1), s0[1]) and np.array_equal(m.scan(2), s0[2])
+                    assert cnt.as_dict() == cnt0.as_dict() and np.array_equal(HtH, HtH0) and np.array_equal(Htr, Htr0)
+
+
 def test_one_launch_front_end_equals_the_multi_call_path(make_map, po, workload):
     """ml_scan_update's fused front end (single-pass compaction + transform + binning, zero-copy pinned input) must leave
     exactly the state the separate calls leave: same clouds, same kNN, same reduced system - for packed xyz (stride 3),
