@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(VR_BLOCK)
                  float4 *__restrict__ in_map, const GridDesc *__restrict__ gd, QSlot *__restrict__ tab, uint32_t mask,
                  uint32_t *__restrict__ q_slot, uint32_t *__restrict__ q_rank) {
   __shared__ uint32_t wsum[VR_BLOCK / 32];
-  __shared__ uint32_t s_tile, s_prefix, s_tot, s_last;
+  __shared__ uint32_t s_tile, s_prefix, s_tot, s_last, s_last_len;
   __shared__ uint16_t head_off[VR_TILE];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int n = *d_n;
@@ -170,43 +170,70 @@ __global__ void __launch_bounds__(VR_BLOCK)
       }
       __syncthreads();
       const uint32_t tile_heads = s_tot, prefix = s_prefix;
+      const int tile_base = (int)tile * VR_TILE;
+      // length of the tile's last run (it may continue into the following tiles): found by one warp, 32 keys per round trip
+      if (wid == VR_BLOCK / 32 - 1 && tile_heads > 0) {
+        const int i = tile_base + (int)head_off[tile_heads - 1];
+        const uint32_t kk = keys[i];
+        int len = 0;
+        for (int j = i;; j += 32) {
+          const unsigned m = __ballot_sync(0xffffffffu, j + lane < n && keys[j + lane] == kk);
+          len += (m == 0xffffffffu) ? 32 : __ffs(~m) - 1;
+          if (m != 0xffffffffu)
+            break;
+        }
+        if (lane == 0)
+          s_last_len = len;
+      }
+      __syncthreads();
+      // one thread per run head (strided over the CTA, so a thread that owns several heads in the load layout does not
+      // serialise their runs); the run is added sequentially in fp32 in input order (the sort is stable). Its length is known
+      // (next head), so there is no data-dependent branch between the loads: 16 gathers per batch, the indices of the next
+      // batch fetched while this one is added (a key comparison per batch put three dependent round trips on every 16 points)
       for (uint32_t kb = 0; kb < tile_heads; kb += VR_BLOCK) {
         const uint32_t k = kb + threadIdx.x;
         const bool live = k < tile_heads;
         const unsigned act = __ballot_sync(0xffffffffu, live);
         if (!live)
           continue;
-        const int i = (int)tile * VR_TILE + (int)head_off[k];
-        const uint32_t kk = keys[i];
+        const int i = tile_base + (int)head_off[k];
+        const int len = k + 1 < tile_heads ? (int)head_off[k + 1] - (int)head_off[k] : (int)s_last_len;
         float sx = 0.f, sy = 0.f, sz = 0.f, sw = 0.f;
-        int j = i;
-        // 16 (then 4) gathers in flight at a time: the keys are sorted, so if the last of a batch still belongs to the run
-        // all of it does; the additions stay in order (runs of several hundred points exist next to the sensor)
-        while (j + 16 <= n && keys[j + 15] == kk) {
-          float4 p[16];
-#pragma unroll
-          for (int u = 0; u < 16; u++)
-            p[u] = cloud[vals[j + u]];
-#pragma unroll
-          for (int u = 0; u < 16; u++)
-            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
-          j += 16;
-        }
-        while (j + 4 <= n && keys[j + 3] == kk) {
+        if (len <= 4) { // most voxels of a fine grid (and of an already down-sampled map): 4 gathers instead of 16
           float4 p[4];
 #pragma unroll
           for (int u = 0; u < 4; u++)
-            p[u] = cloud[vals[j + u]];
+            p[u] = cloud[vals[i + min(u, len - 1)]]; // clamped: always a valid load
 #pragma unroll
-          for (int u = 0; u < 4; u++)
-            sx = __fadd_rn(sx, p[u].x), sy = __fadd_rn(sy, p[u].y), sz = __fadd_rn(sz, p[u].z), sw = __fadd_rn(sw, p[u].w);
-          j += 4;
+          for (int u = 0; u < 4; u++) {
+            const bool use = u < len;
+            const float ax = __fadd_rn(sx, p[u].x), ay = __fadd_rn(sy, p[u].y), az = __fadd_rn(sz, p[u].z), aw = __fadd_rn(sw, p[u].w);
+            sx = use ? ax : sx, sy = use ? ay : sy, sz = use ? az : sz, sw = use ? aw : sw;
+          }
+        } else {
+          uint32_t v[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++)
+            v[u] = vals[i + min(u, len - 1)];
+          for (int j0 = 0; j0 < len; j0 += 16) {
+            float4 p[16];
+#pragma unroll
+            for (int u = 0; u < 16; u++)
+              p[u] = cloud[v[u]];
+            if (j0 + 16 < len) {
+#pragma unroll
+              for (int u = 0; u < 16; u++)
+                v[u] = vals[i + min(j0 + 16 + u, len - 1)];
+            }
+#pragma unroll
+            for (int u = 0; u < 16; u++) {
+              const bool use = j0 + u < len;
+              const float ax = __fadd_rn(sx, p[u].x), ay = __fadd_rn(sy, p[u].y), az = __fadd_rn(sz, p[u].z), aw = __fadd_rn(sw, p[u].w);
+              sx = use ? ax : sx, sy = use ? ay : sy, sz = use ? az : sz, sw = use ? aw : sw;
+            }
+          }
         }
-        for (; j < n && keys[j] == kk; j++) {
-          const float4 p = cloud[vals[j]];
-          sx = __fadd_rn(sx, p.x), sy = __fadd_rn(sy, p.y), sz = __fadd_rn(sz, p.z), sw = __fadd_rn(sw, p.w);
-        }
-        const float c = (float)(j - i);
+        const float c = (float)len;
         const float4 ctr = make_float4(__fdiv_rn(sx, c), __fdiv_rn(sy, c), __fdiv_rn(sz, c), __fdiv_rn(sw, c));
         out[prefix + k] = ctr;
         if (BIN) {
