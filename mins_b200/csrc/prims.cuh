@@ -343,14 +343,25 @@ __global__ void __launch_bounds__(RS_BLOCK) k_radix_pass(const uint32_t *__restr
       cnt += wcnt[w][d];
     atomicExch(&digit_state[(size_t)tile * 256 + d], lb_pack(epoch, tile == 0 ? LB_PREFIX : LB_AGG, cnt));
     uint32_t excl = 0;
-    for (int b = (int)tile - 1; b >= 0; b--) {
-      unsigned long long sv;
-      do {
-        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(sv) : "l"(digit_state + (size_t)b * 256 + d) : "memory");
-      } while ((uint32_t)(sv >> 34) != epoch);
-      excl += (uint32_t)sv;
-      if (((sv >> 32) & 3ull) == LB_PREFIX)
-        break;
+    // LB_WALK predecessors per round trip (their loads are in flight together); consumed in order, a state that is not
+    // published yet is re-read until it is
+    constexpr int LB_WALK = 8;
+    bool done_walk = false;
+    for (int b = (int)tile - 1; b >= 0 && !done_walk; b -= LB_WALK) {
+      unsigned long long sv[LB_WALK];
+#pragma unroll
+      for (int q = 0; q < LB_WALK; q++)
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(sv[q]) : "l"(digit_state + (size_t)max(b - q, 0) * 256 + d) : "memory");
+#pragma unroll
+      for (int q = 0; q < LB_WALK; q++) {
+        if (done_walk || b - q < 0)
+          continue;
+        unsigned long long v = sv[q];
+        while ((uint32_t)(v >> 34) != epoch)
+          asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(digit_state + (size_t)(b - q) * 256 + d) : "memory");
+        excl += (uint32_t)v;
+        done_walk = ((v >> 32) & 3ull) == LB_PREFIX;
+      }
     }
     if (tile > 0)
       atomicExch(&digit_state[(size_t)tile * 256 + d], lb_pack(epoch, LB_PREFIX, excl + cnt));
