@@ -207,7 +207,21 @@ def aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx, reps=10):
     return aux
 
 
+def emit(line):
+    """the one JSON line, on the process's ORIGINAL stdout (see main: fd 1 is pointed at stderr while the run lasts)"""
+    os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+
+
+_STDOUT_FD = 1
+
+
 def main():
+    # stdout carries exactly one JSON line. Libraries write there too (NCCL prints "NCCL version ..." on stdout when the first
+    # communicator comes up): keep a private copy of fd 1 for the line and send everything else to stderr.
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -239,7 +253,7 @@ def main():
                 "config": workload_desc(w, {"points_per_step": CPU_SAMPLE_RAYS}),
                 "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "reference", "sample": sample},
                 "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import torch
@@ -400,7 +414,7 @@ def main():
                                         "ms_per_step": ms}
             except Exception as e:  # the baseline is reported, never required for the GPU number
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference", "sample": f"unavailable: {e}"}
-        print(json.dumps(line))
+        emit(line)
     m.close()
     if world > 1:
         dist.destroy_process_group()
