@@ -96,6 +96,36 @@ class ClockSampler:
         return out
 
 
+def bind_to_gpu_cpus(index):
+    """one process per GPU, kept on the host cores next to that GPU (NVML's cpu affinity = the GPU's NUMA node): the pinned
+    scan buffer and the pinned result block are then first-touched on that node, and the thread that waits for the result is
+    not migrated across sockets. Measured at 8 ranks on one box: see profiles/r1_multi_gpu.md. Returns a description."""
+    if os.environ.get("MINS_BENCH_NO_BIND"):
+        return "unchanged (MINS_BENCH_NO_BIND)"
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = index
+        if vis:
+            try:
+                idx = int(vis.split(",")[index])
+            except Exception:
+                pass
+        hdl = nv.nvmlDeviceGetHandleByIndex(idx)
+        n_cpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(hdl, (n_cpu + 63) // 64)
+        cpus = {64 * wi + b for wi, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        want = cpus & allowed
+        if not want or want == allowed:
+            return f"unchanged ({len(allowed)} cpus allowed; NVML lists {len(cpus)} for GPU {idx})"
+        os.sched_setaffinity(0, want)
+        return f"{len(want)} of {len(allowed)} cpus (NVML cpu affinity of GPU {idx})"
+    except Exception as e:  # pragma: no cover
+        return f"unchanged ({e!r})"
+
+
 def cpu_reference_run(w, steps, warmup, threads):
     """reference CPU path on a bounded sample of the workload; returns (points/s, ms/step, description)."""
     from oracle import pyoracle as po
@@ -256,6 +286,7 @@ def main():
         emit(line)
         return 0
 
+    affinity = bind_to_gpu_cpus(local_rank)
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
@@ -361,6 +392,12 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(pts, op=dist.ReduceOp.SUM)
     dev_ms_max, e2e_ms_max = float(tt[0]), float(tt[1])
+    by_rank = [e2e_s * 1e3 / args.steps]
+    if world > 1:
+        mine = torch.tensor([e2e_s * 1e3 / args.steps], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        by_rank = [float(x[0]) for x in allr]
     total_pts = float(pts[0])
     if rank == 0:
         value = total_pts / (dev_ms_max * 1e-3)
@@ -393,6 +430,7 @@ def main():
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(n * 16 + C.sizeof(capi.ml_scan_consts) + hx * hx * 8 + 32),
                     "d2h_bytes_per_step": int(8 * (hx * hx + hx) + C.sizeof(capi.ml_counters) + 40), "ms_per_step": e2e_ms_max / args.steps,
                     "step_ms_min_median_max": [float(np.min(e2e_steps) * 1e3), float(np.median(e2e_steps) * 1e3), float(np.max(e2e_steps) * 1e3)],
+                    "ms_per_step_by_rank": by_rank, "host_cpu_affinity_rank0": affinity,
                     "d2h": "none as a copy: the kernel's last CTA writes the result block into pinned host memory over PCIe"},
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k_: v / args.steps for k_, v in stage.items()},
