@@ -15,6 +15,7 @@ configuration the metric's target is quoted on; it fits one GPU.
   --impl reference : the reference CPU path on the host cores (reference ikd-Tree compiled unmodified + restated rows).
 """
 import argparse
+import gc
 import ctypes as C
 import json
 import os
@@ -99,7 +100,8 @@ class ClockSampler:
 def bind_to_gpu_cpus(index):
     """one process per GPU, kept on the host cores next to that GPU (NVML's cpu affinity = the GPU's NUMA node): the pinned
     scan buffer and the pinned result block are then first-touched on that node, and the thread that waits for the result is
-    not migrated across sockets. Measured at 8 ranks on one box: see profiles/r1_multi_gpu.md. Returns a description."""
+    not migrated across sockets. On this pool's boxes NVML lists every core for every GPU (one NUMA node): a no-op there,
+    see profiles/r1_multi_gpu.md. Returns a description."""
     if os.environ.get("MINS_BENCH_NO_BIND"):
         return "unchanged (MINS_BENCH_NO_BIND)"
     try:
@@ -375,6 +377,10 @@ def main():
         step(host_ptr)
     barrier()
     e2e_s, e2e_steps = 0.0, []
+    gc_off = not os.environ.get("MINS_BENCH_KEEP_GC")
+    if gc_off:
+        gc.collect()
+        gc.disable()  # a collection inside a ~160 us wall-clock region is a host artefact, not the call's cost
     for _ in range(args.steps):
         flush_l2()
         t0 = time.perf_counter()
@@ -383,6 +389,8 @@ def main():
         e2e_s += dt_
         e2e_steps.append(dt_)
         sampler.sample()
+    if gc_off:
+        gc.enable()
     barrier()
     clocks = sampler.finish()
 
@@ -392,12 +400,12 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(pts, op=dist.ReduceOp.SUM)
     dev_ms_max, e2e_ms_max = float(tt[0]), float(tt[1])
-    by_rank = [e2e_s * 1e3 / args.steps]
+    by_rank = [[e2e_s * 1e3 / args.steps, float(np.max(e2e_steps) * 1e3), float(np.argmax(e2e_steps))]]
     if world > 1:
-        mine = torch.tensor([e2e_s * 1e3 / args.steps], dtype=torch.float64, device="cuda")
+        mine = torch.tensor(by_rank[0], dtype=torch.float64, device="cuda")
         allr = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine)
-        by_rank = [float(x[0]) for x in allr]
+        by_rank = [[float(v) for v in x] for x in allr]
     total_pts = float(pts[0])
     if rank == 0:
         value = total_pts / (dev_ms_max * 1e-3)
@@ -430,7 +438,7 @@ def main():
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(n * 16 + C.sizeof(capi.ml_scan_consts) + hx * hx * 8 + 32),
                     "d2h_bytes_per_step": int(8 * (hx * hx + hx) + C.sizeof(capi.ml_counters) + 40), "ms_per_step": e2e_ms_max / args.steps,
                     "step_ms_min_median_max": [float(np.min(e2e_steps) * 1e3), float(np.median(e2e_steps) * 1e3), float(np.max(e2e_steps) * 1e3)],
-                    "ms_per_step_by_rank": by_rank, "host_cpu_affinity_rank0": affinity,
+                    "ms_mean_max_argmax_by_rank": by_rank, "host_cpu_affinity_rank0": affinity,
                     "d2h": "none as a copy: the kernel's last CTA writes the result block into pinned host memory over PCIe"},
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k_: v / args.steps for k_, v in stage.items()},
