@@ -372,15 +372,17 @@ def main():
             stage[k_] = stage.get(k_, 0.0) + v
     # ---- timed region 2: end to end from pinned host memory through the C ABI (wall clock of the blocking call) -------
     m.set_timing(0)
+    gc_off = not os.environ.get("MINS_BENCH_KEEP_GC")
+    if gc_off:
+        # a collection inside a ~160 us wall-clock region is a host artefact, not the call's cost; collect BEFORE the warm-up
+        # steps of this mode (a full collection leaves the host caches cold: the step right after it measured 35 us slower)
+        gc.collect()
+        gc.disable()
     for _ in range(3):  # warm-up of this mode (host input, no event timers)
         flush_l2()
         step(host_ptr)
     barrier()
     e2e_s, e2e_steps = 0.0, []
-    gc_off = not os.environ.get("MINS_BENCH_KEEP_GC")
-    if gc_off:
-        gc.collect()
-        gc.disable()  # a collection inside a ~160 us wall-clock region is a host artefact, not the call's cost
     for _ in range(args.steps):
         flush_l2()
         t0 = time.perf_counter()
