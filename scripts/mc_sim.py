@@ -80,6 +80,8 @@ def main():
                 "device_share_of_wall": sum(r["device_ms"] for r in recs) * 1e-3 / (wall * world),
                 "map_use_icp": bool(args.icp), "scan_source": "numpy" if args.host_raycast else "cuda (ml_sim_raycast)",
                 "summary": mc.summarize(recs, ["rmse_ori_deg", "rmse_pos_m", "nees_pos", "n_updates"]),
+                "per_run": [{k: (round(float(r[k]), 5) if isinstance(r[k], float) else r[k])
+                             for k in ("seed", "rank", "rmse_ori_deg", "rmse_pos_m", "n_updates", "n_acc", "icp_runs", "icp_ok")} for r in recs],
                 "host_cores": os.cpu_count()}
         print(json.dumps(line))
     if world > 1:
