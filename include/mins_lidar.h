@@ -82,7 +82,10 @@ typedef struct ml_scan_consts {
   double map_ngbr_max_d; /* compared against the SQUARED distance of the k-th neighbour (LidarHelper.cpp:284) */
   double plane_max_p2pd;
   double plane_max_condi;
-  double chi2_thr; /* chi2_mult * quantile(chi_squared(3), 0.95) = chi2_mult * 7.814727903251179 */
+  double chi2_mult; /* OptionsLidar::chi2_mult. The gate is chi2 < chi2_mult * quantile(chi_squared(res.rows()), 0.95) with
+                       res.rows() = map_ngbr_num + 1 - 3 after the nullspace projection (UpdaterLidar.cpp:301,362,
+                       UpdaterStatistics.cpp:31-33,110-111): 3 DoF (7.814727903251179) at the default k = 5. The library holds
+                       the quantile table for k = 3..ML_MAX_K itself. */
 } ml_scan_consts;
 
 /* What UpdaterStatistics would have accumulated (mins/src/update/UpdaterStatistics.cpp:47-83), as order-independent

@@ -42,7 +42,7 @@ class ml_scan_consts(C.Structure):
         ("ie_o", C.c_double), ("ie_p", C.c_double), ("total_hx", C.c_int),
         ("raw_noise", C.c_double), ("map_noise", C.c_double), ("map_ngbr_num", C.c_int),
         ("map_ngbr_max_d", C.c_double), ("plane_max_p2pd", C.c_double), ("plane_max_condi", C.c_double),
-        ("chi2_thr", C.c_double),
+        ("chi2_mult", C.c_double),
     ]
 
 

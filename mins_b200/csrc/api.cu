@@ -108,6 +108,9 @@ struct ml_handle {
   RRParts *parts = nullptr;
   unsigned int *ticket = nullptr;
   bool rows_exported = false;
+  bool rows_attr[ML_MAX_K + 1][2] = {}; // cudaFuncAttributeMaxDynamicSharedMemorySize set for k_rows_reduce<K, NB> on THIS handle's device
+  double *d_hrows = nullptr;            // parity export (ml_point_rows): n x total_hx, grown on demand, never on the per-scan path
+  size_t hrows_cap = 0;
   // pinned host mirrors
   struct HostIn {
     ml_scan_consts c;
@@ -266,8 +269,16 @@ static int resolve_merge(ml_handle *h) {
   h->map_init = h->map_n > 0;
   return ML_OK;
 }
+// the calling thread may have another device current (two LiDARs on two GPUs in one process): every entry point that
+// touches the device makes the handle's device current first
+static inline void use_device(const ml_handle *h) {
+  int d = -1;
+  if (cudaGetDevice(&d) != cudaSuccess || d != h->cfg.device)
+    cudaSetDevice(h->cfg.device);
+}
 #define RESOLVE(h)                                                                                                      \
   do {                                                                                                                 \
+    use_device(h);                                                                                                     \
     if (int rc_ = resolve_merge(h))                                                                                    \
       return rc_;                                                                                                      \
   } while (0)
@@ -413,6 +424,7 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
 void ml_destroy(ml_handle *h) {
   if (!h)
     return;
+  use_device(h);
   cudaStreamSynchronize(h->stream);
   cudaStreamSynchronize(h->stream2);
   if (h->h_merge)
@@ -423,7 +435,7 @@ void ml_destroy(ml_handle *h) {
                  h->sort_vals[1], h->radix_state, h->radix_ghist, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
                  h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->rows, h->parts, h->ticket,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->d_hrows, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -449,6 +461,7 @@ int ml_map_reset(ml_handle *h) {
   if (!h)
     return ML_ERR_ARG;
   RESOLVE(h);
+  h->rows_valid = false;
   h->map_n = 0;
   h->map_init = false;
   CK(cudaMemsetAsync(h->d_map_n, 0, sizeof(int), h->stream));
@@ -467,6 +480,7 @@ int ml_map_build(ml_handle *h, const float *xyzi, int n) {
   if (!h || n < 0 || (n > 0 && !xyzi))
     return fail(h, ML_ERR_ARG, "ml_map_build: bad argument");
   RESOLVE(h);
+  h->rows_valid = false;
   if (n > h->cap_map)
     return fail(h, ML_ERR_CAPACITY, "ml_map_build: more points than max_map_points");
   h->cur = 0;
@@ -481,6 +495,7 @@ int ml_map_build_from_scan(ml_handle *h) {
   if (!h)
     return ML_ERR_ARG;
   RESOLVE(h);
+  h->rows_valid = false;
   ScanState st;
   CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
@@ -497,6 +512,7 @@ int ml_map_build_from_scan(ml_handle *h) {
 // shared tail of ml_map_add / ml_map_add_scan: *d_nadd new points (host upper bound n_ub) into the map. xf_src != NULL: the new
 // points are xf_src[] in the sensor frame, transformed by T_LtoM into add_pts on the way (ml_map_add_scan); else add_pts holds them.
 static int map_add_device(ml_handle *h, const float4 *xf_src, const int *d_nadd, int n_ub, int downsample, float ds, int *n_live) {
+  h->rows_valid = false; // the map changes: a later ml_point_rows must not re-run the rows kernel against it
   if (n_ub <= 0) {
     if (n_live)
       *n_live = h->map_n;
@@ -576,6 +592,7 @@ int ml_map_reanchor(ml_handle *h, const double T[16], double now_minus_FT, doubl
   if (!h || !T)
     return fail(h, ML_ERR_ARG, "ml_map_reanchor: bad argument");
   RESOLVE(h);
+  h->rows_valid = false;
   if (!h->map_init)
     return fail(h, ML_SOFT_NO_MAP, "ml_map_reanchor: map not initialised");
   const int M = h->map_n;
@@ -725,6 +742,7 @@ int ml_scan_upload(ml_handle *h, const float *xyz, int stride, int n, float t_re
 int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
   if (!h || n < 0 || (n > 0 && !xyzi))
     return fail(h, ML_ERR_ARG, "ml_scan_set: bad argument");
+  use_device(h);
   if (n > h->cap_scan)
     return fail(h, ML_ERR_CAPACITY, "ml_scan_set: more points than max_scan_points");
   drop_stale_bins(h);
@@ -747,6 +765,8 @@ int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
 int ml_scan_deskew(ml_handle *h, const float *T_LitoL_knots, int n_knots, int total_points) {
   if (!h || !T_LitoL_knots || n_knots < 2 || total_points < 1)
     return fail(h, ML_ERR_ARG, "ml_scan_deskew: bad argument");
+  use_device(h);
+  h->rows_valid = false;
   const size_t need = (size_t)n_knots * 12;
   if (need > h->knots_cap) {
     if (h->d_knots)
@@ -789,6 +809,7 @@ static int scan_downsample_async(ml_handle *h, float leaf, const float *T_LtoM) 
 int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds) {
   if (!h)
     return ML_ERR_ARG;
+  use_device(h);
   int rc = scan_downsample_async(h, leaf, nullptr);
   if (rc)
     return rc;
@@ -816,12 +837,14 @@ static int scan_transform_async(ml_handle *h, const float T[16]) {
 int ml_scan_transform(ml_handle *h, const float T_LtoM[16]) {
   if (!h || !T_LtoM)
     return fail(h, ML_ERR_ARG, "ml_scan_transform: bad argument");
+  use_device(h);
   return scan_transform_async(h, T_LtoM);
 }
 
 int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n) {
   if (!h || which < 0 || which > 2)
     return fail(h, ML_ERR_ARG, "ml_scan_download: bad argument");
+  use_device(h);
   ScanState st;
   CK(cudaMemcpyAsync(&st, h->d_st, sizeof(st), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
@@ -841,6 +864,7 @@ int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n) 
 int ml_sim_set_world(ml_handle *h, const double *planes, int n_planes) {
   if (!h || !planes || n_planes < 1)
     return fail(h, ML_ERR_ARG, "ml_sim_set_world: bad argument");
+  use_device(h);
   CK(cudaStreamSynchronize(h->stream));
   if (h->sim_planes)
     cudaFree(h->sim_planes);
@@ -856,6 +880,7 @@ int ml_sim_set_world(ml_handle *h, const double *planes, int n_planes) {
 int ml_sim_set_rays(ml_handle *h, const double *dirs_L, int n_rays) {
   if (!h || !dirs_L || n_rays < 1)
     return fail(h, ML_ERR_ARG, "ml_sim_set_rays: bad argument");
+  use_device(h);
   if (n_rays > h->cap_scan)
     return fail(h, ML_ERR_CAPACITY, "ml_sim_set_rays: more rays than max_scan_points");
   CK(cudaStreamSynchronize(h->stream));
@@ -902,6 +927,7 @@ int ml_sim_raycast(ml_handle *h, const double p_LinG[3], const double R_LtoG[9],
                    uint64_t seed, float *xyz_out, int cap, int *n_out) {
   if (!h || !p_LinG || !R_LtoG)
     return fail(h, ML_ERR_ARG, "ml_sim_raycast: bad argument");
+  use_device(h);
   if (!h->sim_planes || !h->sim_dirs)
     return fail(h, ML_ERR_ARG, "ml_sim_raycast: ml_sim_set_world / ml_sim_set_rays have not been called");
   SimPose pose;
@@ -916,6 +942,7 @@ int ml_sim_raycast_sweep(ml_handle *h, const double *pose_knots, int n_knots, do
                          uint64_t seed, float *xyz_out, int cap, int *n_out) {
   if (!h || !pose_knots || n_knots < 2)
     return fail(h, ML_ERR_ARG, "ml_sim_raycast_sweep: bad argument (at least 2 pose knots)");
+  use_device(h);
   if (!h->sim_planes || !h->sim_dirs)
     return fail(h, ML_ERR_ARG, "ml_sim_raycast_sweep: ml_sim_set_world / ml_sim_set_rays have not been called");
   const size_t need = (size_t)n_knots * 12;
@@ -951,7 +978,8 @@ template <int K> static void launch_knn(ml_handle *h, float max_d2, int ph) {
 }
 // fused rows + reduction + finalize; rows_out != nullptr only for the parity export
 template <int K, int NB> static int launch_rows_nb(ml_handle *h, PointRow *rows_out) {
-  static bool attr_set = false;
+  // the attribute is per device (and per function): remembered per handle, a handle lives on one device
+  bool &attr_set = h->rows_attr[K][NB == 5 ? 1 : 0];
   if (!attr_set) {
     CK(cudaFuncSetAttribute(k_rows_reduce<K, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM));
     attr_set = true;
@@ -1024,6 +1052,7 @@ int ml_knn(ml_handle *h, int k, float max_d2, int32_t *idx, float *d2, uint8_t *
   if (!h)
     return ML_ERR_ARG;
   RESOLVE(h);
+  h->rows_valid = false; // the kNN buffers the rows kernel read are overwritten
   int rc = knn_async(h, k, max_d2);
   if (rc)
     return rc;
@@ -1215,8 +1244,10 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
 int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int *n) {
   if (!h)
     return ML_ERR_ARG;
+  RESOLVE(h);
   if (!h->rows_valid)
-    return fail(h, ML_ERR_ARG, "ml_point_rows: no ml_linsys result for the current scan");
+    return fail(h, ML_ERR_ARG, "ml_point_rows: no ml_linsys result for the current scan and map (the export must follow "
+                               "ml_linsys / ml_scan_update directly)");
   const int cnt = h->h_out->st.n_scan;
   const int hx = h->h_in->c.total_hx;
   const int m = std::min(cap, cnt);
@@ -1248,13 +1279,17 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
     }
   }
   if (h_rows) {
-    double *d_h = nullptr;
-    CK(cudaMalloc(&d_h, sizeof(double) * (size_t)cnt * hx));
-    LAUNCH(k_expand_h, std::min(148 * 8, cdiv((long long)cnt * hx, 256)), 256, h->d_st, h->rows, h->d_consts, d_h);
-    cudaError_t e = cudaMemcpyAsync(h_rows, d_h, sizeof(double) * (size_t)m * hx, cudaMemcpyDeviceToHost, h->stream);
-    cudaStreamSynchronize(h->stream);
-    cudaFree(d_h);
-    CK(e);
+    const size_t need = (size_t)cnt * hx;
+    if (need > h->hrows_cap) { // debug export only: grown on demand and kept
+      if (h->d_hrows)
+        cudaFree(h->d_hrows);
+      h->d_hrows = nullptr, h->hrows_cap = 0;
+      CK(cudaMalloc(&h->d_hrows, sizeof(double) * need));
+      h->hrows_cap = need;
+    }
+    LAUNCH(k_expand_h, std::min(148 * 8, cdiv((long long)cnt * hx, 256)), 256, h->d_st, h->rows, h->d_consts, h->d_hrows);
+    CK(cudaMemcpyAsync(h_rows, h->d_hrows, sizeof(double) * (size_t)m * hx, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
   }
   return ML_OK;
 }

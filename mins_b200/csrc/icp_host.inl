@@ -125,6 +125,7 @@ int ml_scan_icp(ml_handle *h, const float T_init[16], const ml_icp_options *o, m
   int rc = icp_alloc(h);
   if (rc)
     return rc;
+  h->rows_valid = false; // the matcher runs k_knn<1> into the kNN buffers the rows kernel read
   drop_stale_bins(h);
   memset(res, 0, sizeof(*res));
   for (int i = 0; i < 16; i++)

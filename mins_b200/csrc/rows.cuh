@@ -35,6 +35,13 @@ __device__ __forceinline__ void d_cross(const double *a, const double *b, double
   o[2] = a[0] * b[1] - a[1] * b[0];
 }
 
+// quantile(chi_squared(dof), 0.95), the entries of UpdaterStatistics' chi_squared_table (UpdaterStatistics.cpp:31-33) the path can
+// reach: the projected residual has map_ngbr_num + 1 - 3 rows (UpdaterLidar.cpp:301,362), map_ngbr_num in [3, ML_MAX_K]
+__host__ __device__ constexpr double chi2_q95(int dof) {
+  return dof == 1 ? 3.841458820694124 : dof == 2 ? 5.991464547107979 : dof == 3 ? 7.814727903251179 : dof == 4 ? 9.487729036781154
+       : dof == 5 ? 11.070497693516351 : dof == 6 ? 12.591587243743977 : dof == 7 ? 14.067140449340169 : 15.50731305586545;
+}
+
 // eigenvalues (min, max) of a symmetric 3x3 matrix [a00 a01 a02; . a11 a12; . . a22], trigonometric closed form
 __device__ __forceinline__ void sym3_eig_minmax(double a00, double a01, double a02, double a11, double a12, double a22, double *lmin,
                                                 double *lmax) {
@@ -393,7 +400,7 @@ __device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, 
   out.res = res5 / raw_n;
   out.raw_n = raw_n;
   out.rss = rss;
-  out.status = (chi2 < c.chi2_thr) ? 0 : 4; // NaN -> reject (UpdaterStatistics.cpp:117)
+  out.status = (chi2 < c.chi2_mult * chi2_q95(K - 2)) ? 0 : 4; // NaN -> reject (UpdaterStatistics.cpp:117)
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -75,7 +75,7 @@ static int m_update(ml_handle *h, const float *, int stride, int n, float t_rel,
   std::printf("|");
   for (int j = 0; j < c->nA; j++)
     std::printf(" %d", c->dTdxA[j].col);
-  std::printf("] at_clone=%d%d k=%d chi2=%.4f P00=%.3g\n", c->at_clone_m, c->at_clone_a, c->map_ngbr_num, c->chi2_thr, P[0]);
+  std::printf("] at_clone=%d%d k=%d chi2=%.4f P00=%.3g\n", c->at_clone_m, c->at_clone_a, c->map_ngbr_num, c->chi2_mult * 7.814727903251179, P[0]);
   for (int i = 0; i < c->total_hx * c->total_hx; i++)
     HtH[i] = 0;
   for (int i = 0; i < c->total_hx; i++) {

@@ -288,7 +288,7 @@ private:
     c.raw_noise = op.raw_noise, c.map_noise = op.map_noise;
     c.map_ngbr_num = op.map_ngbr_num, c.map_ngbr_max_d = op.map_ngbr_max_d;
     c.plane_max_p2pd = op.plane_max_p2pd, c.plane_max_condi = op.plane_max_condi;
-    c.chi2_thr = op.chi2_mult * 7.814727903251179; // quantile(chi_squared(3), 0.95), UpdaterStatistics.cpp:31-33
+    c.chi2_mult = op.chi2_mult; // the library applies quantile(chi_squared(k - 2), 0.95), UpdaterStatistics.cpp:31-33,110-111
 
     // ---- marginal covariance for the chi2 test (UpdaterLidar.cpp:257) ----
     std::vector<double> P((size_t)total_hx * total_hx);

@@ -40,6 +40,15 @@ class OptionsLidar:
     do_calib_dt: bool = False
 
 
+def kaist_options(**kw):
+    """mins/config/kaist/config_lidar.yaml:11-29 (KAIST Urban: 2 x VLP-16, coarse raw leaf, 0.5 m map, wide neighbour gate)."""
+    d = dict(max_range=30.0, min_range=1.0, chi2_mult=1.0, raw_do_downsample=True, raw_downsample_size=2.0, raw_noise=0.1,
+             map_do_downsample=True, map_downsample_size=0.5, map_noise=0.1, map_ngbr_num=5, map_ngbr_max_d=10.0, map_decay_time=30.0,
+             map_decay_dist=30.0, map_use_icp=False, map_icp_dist=30.0, plane_max_p2pd=0.1, plane_max_condi=200.0)
+    d.update(kw)
+    return OptionsLidar(**d)
+
+
 class MLError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"mins_lidar status {code}: {msg}")
@@ -110,7 +119,7 @@ def make_scan_consts(op, RGtoI_est, pIinG_est, RGtoA_est, pAinG_est, RGtoI_fej, 
     c.map_ngbr_num = op.map_ngbr_num
     c.map_ngbr_max_d = op.map_ngbr_max_d
     c.plane_max_p2pd, c.plane_max_condi = op.plane_max_p2pd, op.plane_max_condi
-    c.chi2_thr = op.chi2_mult * CHI2_95_3DOF
+    c.chi2_mult = op.chi2_mult  # the library applies quantile(chi_squared(k - 2), 0.95) itself (UpdaterStatistics.cpp:110-111)
     T = np.eye(4, dtype=np.float32)  # LidarHelper.cpp:149-151
     T[:3, :3] = RLtoM_est.astype(np.float32)
     T[:3, 3] = pLinM_est.astype(np.float32)

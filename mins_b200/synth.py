@@ -145,14 +145,15 @@ def lagrange_weights(ts, t):
     return w
 
 
-def make_workload(shape="G-64", seed=None, op=None, variant="plain", map_points=None, noise=0.02):
+def make_workload(shape="G-64", seed=None, op=None, variant="plain", map_points=None, noise=0.02, map_radius=None):
     """Returns a dict: raw scan (n,4 float32, PointXYZ layout with pad), map (M,4 float32 in the map frame),
     options, scan constants, T_LtoM, P, and the scan time stamp.
 
     variant: "plain" (total_hx 48), "overlap" (I and A share clones, 30), "calib" (54), "calib_dt" (55),
              "at_clone" (both times are clones: no interpolation-error inflation).
     """
-    v_angles, n_az, n_sensors, M_target, ext, n_boxes, map_radius = SHAPES[shape]
+    v_angles, n_az, n_sensors, M_target, ext, n_boxes, map_radius_ = SHAPES[shape]
+    map_radius = map_radius_ if map_radius is None else float(map_radius)  # e.g. map_decay_dist of the option set
     if map_points is not None:
         M_target = int(map_points)
     if seed is None:

@@ -330,6 +330,49 @@ void orc_knn_brute(const float *map_xyzi, int M, const float *q_xyzi, int N, int
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// boost::math::quantile(chi_squared(dof), 0.95) — UpdaterStatistics.cpp:31-33 fills chi_squared_table[i] with it and
+// get_chi2 (:110-111) reads chi_squared_table[res.rows()]. Computed here (not tabulated): regularised lower incomplete
+// gamma P(dof/2, x/2) by its power series, root by bisection to the last bit. tests/test_oracle_math.py pins it to
+// scipy.stats.chi2.ppf.
+// ---------------------------------------------------------------------------------------------------------
+static double reg_lower_gamma(double a, double x) {
+  if (x <= 0)
+    return 0.0;
+  double term = 1.0 / a, sum = term;
+  for (int n = 1; n < 2000; n++) {
+    term *= x / (a + n);
+    sum += term;
+    if (term < sum * 1e-18)
+      break;
+  }
+  return sum * std::exp(-x + a * std::log(x) - std::lgamma(a));
+}
+static double chi2_quantile95_solve(int dof) {
+  double lo = 0.0, hi = 10.0 * dof + 50.0;
+  for (int it = 0; it < 200; it++) {
+    const double mid = 0.5 * (lo + hi);
+    if (reg_lower_gamma(0.5 * dof, 0.5 * mid) < 0.95)
+      lo = mid;
+    else
+      hi = mid;
+  }
+  return 0.5 * (lo + hi);
+}
+// the table UpdaterStatistics' constructor builds (max_chi_size entries there; 64 cover every row count of this path)
+double orc_chi2_quantile95(int dof) {
+  struct Table {
+    double q[64];
+    Table() {
+      q[0] = 0.0;
+      for (int i = 1; i < 64; i++)
+        q[i] = chi2_quantile95_solve(i);
+    }
+  };
+  static const Table t; // thread-safe initialisation (C++11)
+  return dof < 64 ? t.q[dof < 0 ? 0 : dof] : chi2_quantile95_solve(dof);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // A5  LidarHelper::compute_plane — LidarHelper.cpp:291-328. nb: k x float[4] neighbour points (map frame).
 // returns 1 on success (plane = [abc, d], un-normalised), 0 on rejection. cond (may be NULL) = sigma_max/sigma_min.
 // ---------------------------------------------------------------------------------------------------------
@@ -576,7 +619,8 @@ int orc_point(const ml_scan_consts *c, const double *P, const float *pfinL_f, co
       row->vr = hh > 0 ? s / hh : 0;
     }
   }
-  int status = (std::isnan(chi) || !(chi < c->chi2_thr)) ? 4 : 0; // UpdaterStatistics.cpp:117,59
+  const double thr = c->chi2_mult * orc_chi2_quantile95(pr); // UpdaterStatistics.cpp:110-111: chi_squared_table[res.rows()]
+  int status = (std::isnan(chi) || !(chi < thr)) ? 4 : 0; // UpdaterStatistics.cpp:117,59
   if (row)
     row->status = status;
   if (Hp)
@@ -629,7 +673,9 @@ static int scan_linsys_core(const ml_scan_consts *c, const double *P, const floa
   std::vector<int> status(N, 1);
   std::vector<double> Hall((size_t)N * pr * hx), rall((size_t)N * pr);
   std::vector<ml_point_row> rows(N);
-  std::vector<double> hrows((size_t)N * hx, 0.0);
+  // the per-point Jacobian rows and the (w, vr) invariants are test exports: not formed on the timed baseline path
+  const bool want_rows = rows_out || h_rows_out;
+  std::vector<double> hrows(want_rows ? (size_t)N * hx : 0, 0.0);
   auto work = [&](int s, int e) {
     std::vector<float> nb(4 * (size_t)k);
     for (int i = s; i < e; i++) {
@@ -640,7 +686,7 @@ static int scan_linsys_core(const ml_scan_consts *c, const double *P, const floa
       for (int j = 0; j < k; j++)
         memcpy(&nb[4 * j], nb_in ? nb_in + 4 * ((size_t)i * k + j) : map_xyzi + 4 * (size_t)idx[(size_t)i * k + j], 4 * sizeof(float));
       status[i] = orc_point(c, P, scan_L + 4 * (size_t)i, nb.data(), &Hall[(size_t)i * pr * hx], &rall[(size_t)i * pr],
-                            &rows[i], &hrows[(size_t)i * hx]);
+                            &rows[i], want_rows ? &hrows[(size_t)i * hx] : nullptr);
     }
   };
   {

@@ -48,6 +48,10 @@ def lib():
         L.orc_reanchor.argtypes = [vp, C.c_int, vp, C.c_double, C.c_double, C.c_double, C.c_int, C.c_float, vp]
         L.orc_deskew.argtypes = [vp, C.c_int, vp]
         L.orc_deskew.restype = None
+        L.orc_chi2_quantile95.argtypes = [C.c_int]
+        L.orc_chi2_quantile95.restype = C.c_double
+        L.orc_scan_linsys_nb.argtypes = [C.POINTER(capi.ml_scan_consts), vp, vp, C.c_int, vp, vp, vp, vp, C.POINTER(capi.ml_counters),
+                                         vp, vp, vp, C.c_int]
         assert L.orc_sizeof_consts() == C.sizeof(capi.ml_scan_consts)
         assert L.orc_sizeof_row() == C.sizeof(capi.ml_point_row)
         assert L.orc_sizeof_counters() == C.sizeof(capi.ml_counters)
@@ -129,6 +133,31 @@ def scan_linsys(consts, P, map_xyzi, scan_L, scan_M, knn_idx=None, threads=8, wa
                                   hrows.ctypes.data, Hc.ctypes.data if want_compress else None,
                                   rc.ctypes.data if want_compress else None, C.byref(nc) if want_compress else None, threads)
     out = dict(HtH=HtH, Htr=Htr, cnt=cnt, rows=rows_to_numpy(rows, N), h=hrows, total_res=total)
+    if want_compress:
+        out["Hc"], out["rc"] = Hc[:nc.value], rc[:nc.value]
+    return out
+
+
+def chi2_quantile95(dof):
+    """quantile(chi_squared(dof), 0.95) as the oracle computes it (UpdaterStatistics.cpp:31-33)."""
+    return float(lib().orc_chi2_quantile95(int(dof)))
+
+
+def scan_linsys_nb(consts, P, scan_L, nb_xyzi, nb_ok, threads=8, want_compress=False):
+    """rows -> stacking [-> Givens compression] driven by neighbour COORDINATES (N x k x 4 float32), the form in which
+    KD_TREE::Nearest_Search returns them, with nb_ok = LidarHelper::get_neighbors' verdict per point."""
+    hx = consts.total_hx
+    sl = f32(scan_L).reshape(-1, 4)
+    nb = f32(nb_xyzi).reshape(len(sl), -1, 4)
+    ok = np.ascontiguousarray(nb_ok, np.uint8)
+    P = f64(P)
+    HtH, Htr = np.zeros((hx, hx)), np.zeros(hx)
+    cnt = capi.ml_counters()
+    Hc, rc, nc = np.zeros((hx, hx)), np.zeros(hx), C.c_int(0)
+    total = lib().orc_scan_linsys_nb(C.byref(consts), P.ctypes.data, sl.ctypes.data, len(sl), nb.ctypes.data, ok.ctypes.data,
+                                     HtH.ctypes.data, Htr.ctypes.data, C.byref(cnt), Hc.ctypes.data if want_compress else None,
+                                     rc.ctypes.data if want_compress else None, C.byref(nc) if want_compress else None, threads)
+    out = dict(HtH=HtH, Htr=Htr, cnt=cnt, total_res=total)
     if want_compress:
         out["Hc"], out["rc"] = Hc[:nc.value], rc[:nc.value]
     return out
@@ -286,9 +315,11 @@ class RefIkd:
         self.L.ref_ikd_knn(self.h, q.ctypes.data, len(q), k, nb.ctypes.data, d2.ctypes.data, found.ctypes.data, threads)
         return nb, d2, found
 
-    def lidar_update(self, raw, t_rel, op, T_LtoM, consts, P, threads=8):
+    def lidar_update(self, raw, t_rel, op, T_LtoM, consts, P, threads=8, want_info=True):
         """The reference CPU path for one scan: LiDARData ctor -> transform -> reference ikd-Tree kNN in
-        the static-chunk thread loop -> restated rows -> stacking -> Givens compression. Returns (Hc, rc, counters, HtH, Htr)."""
+        the static-chunk thread loop -> restated rows -> stacking -> Givens compression. Returns (Hc, rc, counters, HtH, Htr).
+        want_info=False (the timed baseline): HtH / Htr are NOT formed - the reference never forms them (UpdaterLidar.cpp:376-397
+        stacks and QR-compresses); they exist only so that tests can compare with the device's information form."""
         a = f32(raw)
         hx = consts.total_hx
         T, P = f32(T_LtoM).reshape(4, 4), f64(P)
@@ -297,5 +328,5 @@ class RefIkd:
         cnt = capi.ml_counters()
         self.L.ref_lidar_update(self.h, a.ctypes.data, a.shape[1], len(a), t_rel, op.max_range, op.min_range, T.ctypes.data,
                                 C.byref(consts), P.ctypes.data, Hc.ctypes.data, rc.ctypes.data, C.byref(nc), C.byref(cnt), threads,
-                                HtH.ctypes.data, Htr.ctypes.data)
+                                HtH.ctypes.data if want_info else None, Htr.ctypes.data if want_info else None)
         return Hc[:nc.value], rc[:nc.value], cnt, HtH, Htr

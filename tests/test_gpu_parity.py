@@ -9,7 +9,7 @@ insert point set, re-anchor, deskew); plane / residual / Jacobian rows and the r
 import numpy as np
 import pytest
 
-from conftest import load_golden, rel
+from conftest import check_voxel_contract, load_golden, rel
 
 pytestmark = pytest.mark.gpu
 
@@ -308,7 +308,7 @@ def test_chi2_gate_rejects_like_the_reference(make_map, po, workload):
     import copy
     w = workload("G-small")
     c2 = copy.copy(w["consts"])
-    c2.chi2_thr = 0.02
+    c2.chi2_mult = 0.02 / 7.814727903251179
     m = make_map()
     m.Build(w["map"])
     rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], w["op"], w["T_LtoM"], c2, w["P"])
@@ -446,8 +446,16 @@ def test_reanchor_equals_oracle(make_map, po, workload, do_ds):
     assert n == len(ref) and 0 < n < len(w["map"])
     if not do_ds:
         assert np.array_equal(out, ref)
-    else:  # centroids: fp32 accumulation order inside a voxel is not defined by PCL either
-        assert np.abs(out - ref).max() <= 1e-4
+    else:  # centroids: fp32 accumulation order inside a voxel is not defined by PCL either -> the stated voxel contract
+        # (identical membership and order, 4 ulp sqrt(n)), carried through the decay filters and the fp64 transform
+        def post(c):
+            keep = ~(c[:, 3].astype(np.float64) + op.map_decay_time < 5.5)
+            nrm = np.sqrt((c[:, 0] * c[:, 0] + (c[:, 1] * c[:, 1] + c[:, 2] * c[:, 2]).astype(np.float32)).astype(np.float32))
+            keep &= ~(nrm > op.map_decay_dist)
+            q = c[keep].copy()
+            q[:, :3] = (c[keep, :3].astype(np.float64) @ T[:3, :3].T + T[:3, 3]).astype(np.float32)
+            return q, keep
+        check_voxel_contract(w["map"], out, op.map_downsample_size, po, post=post, slack=2.0)
     assert m.initialized()
 
 

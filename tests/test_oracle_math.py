@@ -209,3 +209,43 @@ def test_reanchor_matches_numpy(po):
     assert abs(len(out) - keep.sum()) <= 1  # a point within fp32 rounding of the distance gate may flip
     if len(out) == keep.sum():
         assert np.abs(out[:, :3] - ref).max() <= 1e-5 and np.array_equal(out[:, 3], m[keep, 3])
+
+
+def test_chi2_quantile_table_matches_scipy(po):
+    """UpdaterStatistics.cpp:31-33: chi_squared_table[i] = quantile(chi_squared(i), 0.95); the oracle computes it itself."""
+    from scipy.stats import chi2
+    for dof in range(1, 40):
+        assert po.chi2_quantile95(dof) == pytest.approx(float(chi2.ppf(0.95, dof)), rel=1e-13)
+
+
+@pytest.mark.parametrize("k", [3, 4, 5, 8, 10])
+def test_oracle_chi2_gate_follows_the_projected_row_count(po, workload, k):
+    """get_chi2 reads chi_squared_table[res.rows()] with res.rows() = k - 2 after the projection (UpdaterStatistics.cpp:110-111)."""
+    import copy
+    from scipy.stats import chi2
+    w = workload("G-small", k=k)
+    op = w["op"]
+    sc = po.range_filter(w["raw"], w["t_rel"], op.max_range, op.min_range)
+    sm = po.transform_f32(sc, w["T_LtoM"])
+    r0 = po.scan_linsys(w["consts"], w["P"], w["map"], sc, sm)
+    tested = (r0["rows"]["status"] == 0) | (r0["rows"]["status"] == 4)
+    q = float(chi2.ppf(0.95, k - 2))
+    c2 = copy.copy(w["consts"])
+    v = np.sort(r0["rows"]["chi2"][tested])
+    c2.chi2_mult = float(0.5 * (v[len(v) // 2] + v[len(v) // 2 + 1])) / q      # between two points: nobody sits on the gate
+    r1 = po.scan_linsys(c2, w["P"], w["map"], sc, sm)
+    st = r1["rows"]["status"]
+    assert np.array_equal(st[tested] == 0, r1["rows"]["chi2"][tested] < c2.chi2_mult * q)
+    assert 0.3 * tested.sum() < (st == 4).sum() < 0.7 * tested.sum()
+    assert r1["total_res"] == (k - 2) * (st == 0).sum()
+
+
+def test_oracle_plane_gate_on_rank_deficient_neighbours(po):
+    """LidarHelper.cpp:305-312: collinear / coplanar-with-the-origin neighbours give sigma_max / sigma_min = huge or inf."""
+    t = np.arange(5, dtype=np.float32)[:, None]
+    for nbp in (t * np.float32([0.3, 0.3, 0.0]) + np.float32([0.3, 0.3, 0.0]), t * np.float32([0.25, 0.0, 0.0]) + np.float32([3.0, 2.0, 0.5]),
+                np.float32([[2, 0, 0], [2.3, 0, 0], [2, 0.3, 0], [2.3, 0.3, 0], [2.15, 0.15, 0]])):
+        mp = np.zeros((5, 4), np.float32)
+        mp[:, :3] = nbp
+        ok, plane, cond = po.compute_plane(mp)
+        assert not ok and cond > 1e12
