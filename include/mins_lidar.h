@@ -263,6 +263,10 @@ int ml_last_timing(ml_handle *h, float ms[8]);
 /* CUDA-event timers: 0 = off, 1 = per-stage (default; diagnostic - the event records between kernels serialise the
  * programmatically dependent launches of the pipeline), 2 = total only ([7]; the other entries read 0) */
 int ml_set_timing(ml_handle *h, int on);
+/* profiling aid, not part of the reference's surface: per-CTA %globaltimer stamps [ns] of the kNN and rows kernels of the scans
+ * that follow (on = 1 arms, 0 disarms); out (may be NULL) receives the stamps of the last scan as [kernel: 0 kNN, 1 rows][cta <
+ * 2048][slot < 8] and clears them. Returns the number of values written. Costs one predicated store per mark when disarmed. */
+int ml_debug_timeline(ml_handle *h, int on, unsigned long long *out, int cap);
 /* sizeof of {ml_scan_consts, ml_point_row, ml_counters, ml_config} as compiled, for FFI layout checks */
 void ml_abi_sizes(int out[4]);
 /* number of kernel launches issued by this handle so far */

@@ -23,6 +23,7 @@
 using namespace ml;
 
 static std::string g_global_error;
+#define ML_TL_MAX_CTAS 2048
 
 struct ml_handle {
   ml_config cfg;
@@ -103,12 +104,18 @@ struct ml_handle {
   int32_t *knn_idx = nullptr;
   float *knn_d2 = nullptr;
   uint8_t *knn_ok = nullptr;
+  float4 *nbr = nullptr; // k neighbour coordinates per query, scan order (written by k_knn, read by k_rows_reduce)
+  RowConsts rowc;        // per-scan constants of the rows kernel (kernel parameter), filled by consts_async
   DevConsts *d_consts = nullptr;
   PointRow *rows = nullptr;
   RRParts *parts = nullptr;
   unsigned int *ticket = nullptr;
   bool rows_exported = false;
-  bool rows_attr[ML_MAX_K + 1][2] = {}; // cudaFuncAttributeMaxDynamicSharedMemorySize set for k_rows_reduce<K, NB> on THIS handle's device
+  bool rows_attr[ML_MAX_K + 1][8] = {};
+  // debug timeline (ml_debug_timeline): per-CTA %globaltimer stamps of the kNN and rows kernels
+  bool tl_on = false;
+  unsigned long long *tl_rows = nullptr, *tl_knn = nullptr;
+  int rows_block = 0; // 0 = chosen per scan size; MINS_ROWS_BLOCK=512|1024 pins it (profiling) // cudaFuncAttributeMaxDynamicSharedMemorySize set for k_rows_reduce<K, NB> on THIS handle's device
   double *d_hrows = nullptr;            // parity export (ml_point_rows): n x total_hx, grown on demand, never on the per-scan path
   size_t hrows_cap = 0;
   // pinned host mirrors
@@ -330,6 +337,8 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     h->use_pdl = !(e[0] == '1');
   if (const char *e = getenv("MINS_ZERO_COPY"))
     h->zero_copy = !(e[0] == '0');
+  if (const char *e = getenv("MINS_ROWS_BLOCK"))
+    h->rows_block = atoi(e);
   if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
     h->use_fused_front = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -410,6 +419,7 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->knn_idx, sizeof(int32_t) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->knn_d2, sizeof(float) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->knn_ok, cs));
+  CK(cudaMalloc(&h->nbr, sizeof(float4) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->d_consts, sizeof(DevConsts)));
   CK(cudaMalloc(&h->rows, sizeof(PointRow) * cs));
   CK(cudaMalloc(&h->parts, sizeof(RRParts)));
@@ -433,9 +443,9 @@ void ml_destroy(ml_handle *h) {
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_state, h->radix_ghist, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
-                 h->knn_idx, h->knn_d2, h->knn_ok, h->d_consts, h->rows, h->parts, h->ticket,
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->nbr, h->d_consts, h->rows, h->parts, h->ticket,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
-                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->d_hrows, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
+                 h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->d_hrows, h->tl_rows, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
   for (void *p : dev)
     if (p)
       cudaFree(p);
@@ -974,21 +984,50 @@ int ml_sim_scan_device(ml_handle *h, const float **xyz_dev, int *n) {
 template <int K> static void launch_knn(ml_handle *h, float max_d2, int ph) {
   const int blocks = h->n_sm * 8;
   LAUNCHP(k_knn<K>, blocks, KNN_WARPS * 32, h->units, h->d_st, ph, h->q_sorted, h->d_grid, h->cell_start, h->cell_pts, max_d2,
-         h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots);
+         h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots, (const float4 *)h->map_pts[h->cur], h->nbr,
+         h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
 }
 // fused rows + reduction + finalize; rows_out != nullptr only for the parity export
-template <int K, int NB> static int launch_rows_nb(ml_handle *h, PointRow *rows_out) {
+template <int K, int NB, int BLOCK, bool EXPORT> static int launch_rows_cfg(ml_handle *h, PointRow *rows_out, int nb) {
+  constexpr int WARPS = BLOCK / 32;
+  const size_t smem = RRLayout<NB>::smem(WARPS);
   // the attribute is per device (and per function): remembered per handle, a handle lives on one device
-  bool &attr_set = h->rows_attr[K][NB == 5 ? 1 : 0];
+  bool &attr_set = h->rows_attr[K][(NB == 5 ? 1 : 0) + (BLOCK == RR_BLOCK_BIG ? 2 : BLOCK == RR_BLOCK_MID ? 4 : 0) + (EXPORT ? 6 : 0)];
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(k_rows_reduce<K, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RR_SMEM));
+    CK(cudaFuncSetAttribute(k_rows_reduce<K, NB, BLOCK, EXPORT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  const int nb = std::max(1, std::min(h->n_sm, cdiv(std::max(h->n_raw, 1), 256)));
-  launch_pdl(h, k_rows_reduce<K, NB>, nb, RR_BLOCK, RR_SMEM, (const ScanState *)h->d_st, (const float4 *)h->scan_pts,
-             (const float4 *)h->map_pts[h->cur], (const int32_t *)h->knn_idx, (const uint8_t *)h->knn_ok, (const DevConsts *)h->d_consts,
-             rows_out, h->parts, h->ticket, h->h_out /* pinned host memory, written by the last CTA */);
+  launch_pdl(h, k_rows_reduce<K, NB, BLOCK, EXPORT>, nb, BLOCK, smem, h->rowc, (const ScanState *)h->d_st, h->n_raw,
+             (const float4 *)h->scan_pts, (const float4 *)h->nbr, (const DevConsts *)h->d_consts, rows_out, h->parts, h->ticket,
+             h->h_out /* pinned host memory, written by the last CTA */, h->tl_on ? h->tl_rows : (unsigned long long *)nullptr);
   return ML_OK;
+}
+// Launch shape: one CTA per SM (fewer for small scans), and the block size whose warps walk the 32-point tiles in the most even
+// number of rounds - the kernel ends with a CTA barrier, so a round that only some warps run is paid by all of them. Fixed for a
+// given scan size: the reduction order (and the result, bit for bit) depends on nothing else.
+template <int K, int NB> static int launch_rows_nb(ml_handle *h, PointRow *rows_out) {
+  const int n = std::max(h->n_raw, 1);
+  const int ntiles = cdiv(n, 32);
+  const int nb = std::max(1, std::min(h->n_sm, cdiv(n, 256)));
+  if (rows_out) // parity export: same arithmetic, same launch-shape rule is not needed (the sums are not compared bit for bit
+    return launch_rows_cfg<K, NB, RR_BLOCK, true>(h, rows_out, nb); // with the timed run's; the export re-writes the result block)
+  if (NB == 3 && K == 5) {
+    // efficiency of a block size = tiles / (rounds * warps); more warps also hide more latency, so they win ties
+    auto eff = [&](int warps) { return (double)ntiles / ((double)cdiv(ntiles, nb * warps) * nb * warps); };
+    int best = RR_BLOCK;
+    double be = eff(RR_BLOCK / 32) * 0.92;
+    for (int b : {RR_BLOCK_MID, RR_BLOCK_BIG})
+      if (eff(b / 32) >= be)
+        best = b, be = eff(b / 32);
+    if (h->rows_block)
+      best = h->rows_block;
+    constexpr int MID = (NB == 3 && K == 5) ? RR_BLOCK_MID : RR_BLOCK, BIG = (NB == 3 && K == 5) ? RR_BLOCK_BIG : RR_BLOCK;
+    if (best == RR_BLOCK_BIG)
+      return launch_rows_cfg<K, NB, BIG, false>(h, rows_out, nb);
+    if (best == RR_BLOCK_MID)
+      return launch_rows_cfg<K, NB, MID, false>(h, rows_out, nb);
+  }
+  return launch_rows_cfg<K, NB, RR_BLOCK, false>(h, rows_out, nb);
 }
 // NB = 3-wide blocks of the folded Jacobian direction that can be non-zero: 3 without extrinsic calibration, 5 with
 template <int K> static int launch_rows(ml_handle *h, PointRow *rows_out) {
@@ -1007,7 +1046,12 @@ static int launch_rows_k(ml_handle *h, int k, PointRow *rows_out) {
   }
 }
 
-static int knn_async(ml_handle *h, int k, float max_d2) {
+// join_consts: the rows kernel follows (ml_linsys / ml_scan_update). The constants' stream (k_prep_consts) is joined HERE, in
+// front of the kNN kernel, not in front of the rows kernel: an event wait between two kernels makes the second one wait for
+// the full completion of the first and pay a launch gap (3.5 us measured between the last kNN CTA and the first rows CTA);
+// with kNN -> rows adjacent in the stream the rows CTAs are launched programmatically behind the kNN's and stage their
+// constants while it drains. k_prep_consts (~20 us, one CTA) has run beside the front end and the binning by then.
+static int knn_async(ml_handle *h, int k, float max_d2, bool join_consts = false) {
   if (k < 1 || k > ML_MAX_K)
     return fail(h, ML_ERR_ARG, "knn: k out of range [1, ML_MAX_K]");
   if (!h->map_init)
@@ -1015,8 +1059,11 @@ static int knn_async(ml_handle *h, int k, float max_d2) {
   if (!h->have_T)
     return fail(h, ML_ERR_ARG, "knn: ml_scan_transform has not been called for this scan");
   const int n = h->n_raw;
-  if (n <= 0)
+  if (n <= 0) {
+    if (join_consts)
+      CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
     return ML_OK;
+  }
   const uint32_t mask = (uint32_t)h->q_slots - 1u;
   const int ph = h->knn_calls & 1;
   h->knn_calls++;
@@ -1027,6 +1074,8 @@ static int knn_async(ml_handle *h, int k, float max_d2) {
   h->bin_done = false;
   LAUNCHP(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, ph, h->units, h->units_cap);
   LAUNCHP(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
+  if (join_consts)
+    CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   if (h->timing == 1)
     cudaEventRecord(h->ev[4], h->stream);
   switch (k) {
@@ -1091,11 +1140,54 @@ static int check_consts(ml_handle *h, const ml_scan_consts *c) {
   return ML_OK;
 }
 
+// 3x3 helpers (row-major) for the host-side constant folding
+static inline void m3_mul(const double *A, const double *B, double *C) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+static inline void m3_vec(const double *A, const double *v, double *o) {
+  for (int i = 0; i < 3; i++)
+    o[i] = A[3 * i] * v[0] + A[3 * i + 1] * v[1] + A[3 * i + 2] * v[2];
+}
+// ml_scan_consts (the reference's local variables, UpdaterLidar.cpp:223-254) -> the folded form the rows kernel takes as its
+// parameter (RowConsts, rows.cuh)
+static void make_row_consts(const ml_scan_consts &c, RowConsts *r) {
+  memcpy(r->RLtoM_est, c.RLtoM_est, sizeof r->RLtoM_est), memcpy(r->pLinM_est, c.pLinM_est, sizeof r->pLinM_est);
+  memcpy(r->RLtoM_fej, c.RLtoM_fej, sizeof r->RLtoM_fej), memcpy(r->pLinM_fej, c.pLinM_fej, sizeof r->pLinM_fej);
+  memcpy(r->RLtoI, c.RLtoI_fej, sizeof r->RLtoI);
+  double t[3], u[3];
+  m3_vec(c.RLtoI_fej, c.pIinL_fej, t); // w = RLtoI (pfinL - pIinL) = RLtoI pfinL - RLtoI pIinL
+  for (int a = 0; a < 3; a++)
+    r->pLinI[a] = -t[a];
+  m3_mul(c.RGtoM_fej, c.RItoG_fej, r->RItoM);
+  memcpy(r->RGtoM, c.RGtoM_fej, sizeof r->RGtoM);
+  memcpy(r->RItoL, c.RItoL_fej, sizeof r->RItoL);
+  m3_mul(c.RGtoA_fej, c.RLtoG_fej, r->U1);
+  m3_vec(c.RItoG_fej, c.pLinI_fej, t);
+  for (int a = 0; a < 3; a++)
+    u[a] = c.pIinG_fej[a] + t[a] - c.pAinG_fej[a];
+  m3_vec(c.RGtoA_fej, u, r->U0);
+  for (int a = 0; a < 3; a++)
+    u[a] = c.pIinG_fej[a] - c.pAinG_fej[a];
+  m3_vec(c.RGtoM_fej, u, r->c1);
+  memcpy(r->pIinL, c.pIinL_fej, sizeof r->pIinL);
+  r->raw_noise = c.raw_noise, r->map_noise = c.map_noise;
+  r->condi2 = c.plane_max_condi * c.plane_max_condi;
+  r->p2pd = c.plane_max_p2pd;
+  r->badmatch = c.plane_max_p2pd * 3.0;
+  r->ie_o = c.ie_o, r->ie_p = c.ie_p;
+  r->chi2_thr = c.chi2_mult * chi2_q95(c.map_ngbr_num - 2);
+  r->intr = (!c.at_clone_m || !c.at_clone_a) ? 1 : 0;
+  r->total_hx = c.total_hx;
+}
+
 // per-scan constants: H2D + k_prep_consts on the side stream, so they overlap the scan pipeline (filter, binning, kNN)
 static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) {
   const int hx = c->total_hx;
   h->h_in->c = *c;
   memcpy(h->h_in->P, P, sizeof(double) * (size_t)hx * hx);
+  make_row_consts(*c, &h->rowc);
   // no fork event: every entry point that launches the rows kernel (the only reader of d_consts) synchronises the main
   // stream before it returns, so d_consts is idle here; an event record here would also split the kernel chain
   // no copy nodes: k_prep_consts reads the pinned staging block over PCIe (24 KB) and leaves c, T, Q in device memory
@@ -1108,14 +1200,11 @@ static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) 
 // everything after the transform; one synchronisation at the end. consts_async must have been issued.
 static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *HtH, double *Htr, ml_counters *cnt) {
   const int hx = c->total_hx, k = c->map_ngbr_num;
-  int rc = knn_async(h, k, (float)c->map_ngbr_max_d);
+  int rc = knn_async(h, k, (float)c->map_ngbr_max_d, true);
   if (rc) {
     cudaStreamSynchronize(h->stream2);
     return rc;
   }
-  // join the constants' stream as late as possible: k_prep_consts (~20 us, one CTA) and its two small H2D copies run
-  // beside front end + binning + kNN; only the rows kernel reads d_consts
-  CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   rc = launch_rows_k(h, k, nullptr);
   if (rc)
     return rc;
@@ -1292,6 +1381,35 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
     CK(cudaStreamSynchronize(h->stream));
   }
   return ML_OK;
+}
+
+// Debug/profiling aid (not part of the reference's surface): arm (on = 1) or disarm per-CTA %globaltimer stamps in the kNN and
+// rows kernels; with out != NULL copy the stamps of the last scan: out[0 .. cap) receives 2 * ML_TL_MAX_CTAS * 8 values
+// ([kernel: 0 kNN, 1 rows][cta][slot], ns, 0 = not reached). Returns the number of values written or < 0.
+int ml_debug_timeline(ml_handle *h, int on, unsigned long long *out, int cap) {
+  if (!h)
+    return ML_ERR_ARG;
+  use_device(h);
+  const size_t per = (size_t)ML_TL_MAX_CTAS * ML_TL_SLOTS;
+  if (!h->tl_rows) {
+    CK(cudaMalloc(&h->tl_rows, sizeof(unsigned long long) * per * 2));
+    h->tl_knn = h->tl_rows + per;
+    CK(cudaMemset(h->tl_rows, 0, sizeof(unsigned long long) * per * 2));
+  }
+  int written = 0;
+  if (out && cap > 0) {
+    CK(cudaStreamSynchronize(h->stream));
+    const size_t m = std::min((size_t)cap, per * 2);
+    std::vector<unsigned long long> tmp(per * 2);
+    CK(cudaMemcpy(tmp.data(), h->tl_rows, sizeof(unsigned long long) * per * 2, cudaMemcpyDeviceToHost));
+    // device order is [rows | knn]; hand out [knn | rows]
+    for (size_t i = 0; i < m; i++)
+      out[i] = i < per ? tmp[per + i] : tmp[i - per];
+    written = (int)m;
+    CK(cudaMemset(h->tl_rows, 0, sizeof(unsigned long long) * per * 2));
+  }
+  h->tl_on = on != 0;
+  return written;
 }
 
 void ml_abi_sizes(int out[4]) {

@@ -58,6 +58,17 @@ __device__ __forceinline__ void pdl_enter() {
   pdl_wait();
 }
 
+// Debug timeline (ml_debug_timeline): thread 0 of every CTA stamps %globaltimer [ns] at up to ML_TL_SLOTS points of a kernel.
+// tl == NULL (always, unless the debug entry point armed it): one predicated-off store per mark.
+#define ML_TL_SLOTS 8
+__device__ __forceinline__ void tl_mark(unsigned long long *tl, int slot) {
+  if (tl && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    tl[(size_t)blockIdx.x * ML_TL_SLOTS + slot] = t;
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Dense kNN grid over the map's bounding box. Cell id = (z*dimy + y)*dimx + x (x fastest, so the cells
 // of one x-run are one contiguous range of cell_pts).
@@ -84,6 +95,7 @@ struct ScanState {
   // kNN work-list counters, double-buffered by the parity of the kNN call: call c fills [c & 1] and clears [(c + 1) & 1]
   int n_units[2];   // warp work units
   int n_qsorted[2]; // queries placed in cell order
+  int knn_next[2];  // kNN work ticket: units beyond the first one of every warp are handed out dynamically
 };
 
 // One warp work unit of the kNN kernel: up to 32 queries that fall into the same grid cell.

@@ -184,7 +184,8 @@ int ml_scan_icp(ml_handle *h, const float T_init[16], const ml_icp_options *o, m
     LAUNCH(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_ist, ph, h->units, h->units_cap);
     LAUNCH(k_query_scatter, cdiv(n_read, 256), 256, h->icp_q, h->d_ist, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
     LAUNCH(k_knn<1>, h->n_sm * 8, KNN_WARPS * 32, h->units, h->d_ist, ph, h->q_sorted, h->d_grid, h->cell_start, h->icp_cell_pts, mm2,
-           h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots);
+           h->knn_idx, h->knn_d2, h->knn_ok, h->qtab, h->q_slots, (const float4 *)nullptr, (float4 *)nullptr,
+           (unsigned long long *)nullptr);
     for (int pass = 3; pass >= 0; pass--)
       LAUNCH(k_icp_select_pass, Gs, 256, h->knn_d2, h->knn_ok, h->d_icp, pass, (float)o->trim_ratio);
     LAUNCH(k_icp_normal_eq, Gs, 256, h->icp_q, h->knn_idx, h->knn_d2, h->knn_ok, h->map_pts[h->cur], h->icp_normals, h->d_icp, h->icp_parts,

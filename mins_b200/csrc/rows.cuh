@@ -42,25 +42,50 @@ __host__ __device__ constexpr double chi2_q95(int dof) {
        : dof == 5 ? 11.070497693516351 : dof == 6 ? 12.591587243743977 : dof == 7 ? 14.067140449340169 : 15.50731305586545;
 }
 
-// eigenvalues (min, max) of a symmetric 3x3 matrix [a00 a01 a02; . a11 a12; . . a22], trigonometric closed form
+// sqrt(x) for x >= 0 as x * rsqrt(x): MUFU.RSQ64H + two Newton steps, no slow-path call (<= 2 ulp; 0 -> 0)
+__device__ __forceinline__ double fast_sqrt(double x) { return x > 0.0 ? x * rsqrt(x) : 0.0; }
+
+// eigenvalues (min, max) of a symmetric 3x3 matrix [a00 a01 a02; . a11 a12; . . a22]: the trigonometric closed form
+//   lambda = q + 2 p cos(phi + 2 pi k / 3),  phi = acos(r) / 3,  r = det((A - q I) / p) / 2,
+// evaluated WITHOUT acos / cos (double-precision acos + 2 cos cost ~570 instructions, a third of the whole point):
+// c = cos(phi) in [1/2, 1] is the largest root of 4 c^3 - 3 c = r. Start above it at c0 = 1/2 + sqrt((1 + r) / 6) (exact to
+// first order at the double root r = -1, 1.08 at r = 1), three Newton steps in fp32 and two in fp64 (monotone from above: the
+// cubic is convex and increasing there; error < 2e-12 at the ill-conditioned double root, where acos is no better, ~1e-16
+// elsewhere). Then cos(phi + 2 pi / 3) = -(c + sqrt(3) sqrt(1 - c^2)) / 2.
 __device__ __forceinline__ void sym3_eig_minmax(double a00, double a01, double a02, double a11, double a12, double a22, double *lmin,
                                                 double *lmax) {
-  const double p1 = a01 * a01 + a02 * a02 + a12 * a12;
-  const double q = (a00 + a11 + a22) / 3.0;
+  const double p1 = fma(a01, a01, fma(a02, a02, a12 * a12));
+  const double q = (a00 + a11 + a22) * (1.0 / 3.0);
   const double b00 = a00 - q, b11 = a11 - q, b22 = a22 - q;
-  const double p2 = b00 * b00 + b11 * b11 + b22 * b22 + 2.0 * p1;
-  if (p2 <= 0.0) {
+  const double p2 = fma(b00, b00, fma(b11, b11, fma(b22, b22, 2.0 * p1)));
+  if (!(p2 > 0.0)) {
     *lmin = *lmax = q;
     return;
   }
-  const double p = sqrt(p2 / 6.0);
-  const double ip = 1.0 / p;
-  const double c00 = b00 * ip, c11 = b11 * ip, c22 = b22 * ip, c01 = a01 * ip, c02 = a02 * ip, c12 = a12 * ip;
-  double r = 0.5 * (c00 * (c11 * c22 - c12 * c12) - c01 * (c01 * c22 - c12 * c02) + c02 * (c01 * c12 - c11 * c02));
+  const double ip = rsqrt(p2 * (1.0 / 6.0));
+  const double p = p2 * (1.0 / 6.0) * ip;
+  const double det = fma(b00, fma(b11, b22, -a12 * a12), fma(-a01, fma(a01, b22, -a12 * a02), a02 * fma(a01, a12, -b11 * a02)));
+  double r = 0.5 * det * ip * ip * ip;
   r = fmin(1.0, fmax(-1.0, r));
-  const double phi = acos(r) / 3.0;
-  *lmax = q + 2.0 * p * cos(phi);
-  *lmin = q + 2.0 * p * cos(phi + 2.0943951023931953);
+  float cf = 0.5f + sqrtf((1.0f + (float)r) * (1.0f / 6.0f));
+  const float rf = (float)r;
+#pragma unroll
+  for (int it = 0; it < 3; it++) {
+    const float c2 = cf * cf;
+    cf = cf - __fdividef(fmaf(fmaf(4.0f, c2, -3.0f), cf, -rf), fmaf(12.0f, c2, -3.0f) + 1e-30f);
+  }
+  double c = fmax(0.5, (double)cf);
+#pragma unroll
+  for (int it = 0; it < 2; it++) {
+    const double c2 = c * c;
+    const double fp = fma(12.0, c2, -3.0);
+    const double f = fma(fma(4.0, c2, -3.0), c, -r);
+    c = fp > 1e-300 ? c - f / fp : c;
+  }
+  c = fmin(1.0, fmax(0.5, c));
+  const double sn = fast_sqrt(fma(-c, c, 1.0));
+  *lmax = fma(2.0 * p, c, q);
+  *lmin = q - p * fma(1.7320508075688772, sn, c);
 }
 
 // T (18 x hx) and Q = T P T^T from the scan constants. One block of 1024; T and T P staged in shared memory, P read
@@ -151,373 +176,358 @@ __global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *dc, const ml_sc
   }
 }
 
-// One scan point: neighbours -> plane -> gates -> g, w, vr, chi2 (see the header of this file). `c` and `sQ` live in
-// shared memory; `out` arrives zeroed with status 1. out.status: 0 accepted, 1 kNN fail, 2 plane fail, 3 bad match,
-// 4 chi2 reject.
+// ------------------------------------------------------------------------------------------------
+// Per-scan constants of the point loop in the form the kernel consumes them, derived on the host from ml_scan_consts
+// (make_row_consts, api.cu) and passed BY VALUE as a __grid_constant__ kernel parameter: parameters live in the constant
+// bank, so every use is an instruction operand - no load, no register, no shared-memory staging.
+//   w  = RLtoI (pfinL - pIinL) = RLtoI pfinL + pLinI                (UpdaterLidar.cpp:320)
+//   nI = (RGtoM RItoG)^T n,  nG = RGtoM^T n                         (:320-321)
+//   u  = RGtoA (pIinG + RItoG pLinI - pAinG + RLtoG pfinL) = U0 + U1 pfinL   (:322)
+//   c1 = RGtoM (pIinG - pAinG)                                      (:325)
+// ------------------------------------------------------------------------------------------------
+struct RowConsts {
+  double RLtoM_est[9], pLinM_est[3], RLtoM_fej[9], pLinM_fej[3];
+  double RLtoI[9], pLinI[3];
+  double RItoM[9], RGtoM[9], RItoL[9];
+  double U1[9], U0[3];
+  double c1[3], pIinL[3];
+  double raw_noise, map_noise;
+  double condi2;       // plane_max_condi^2
+  double p2pd;         // plane_max_p2pd
+  double badmatch;     // 3 plane_max_p2pd (UpdaterLidar.cpp:296)
+  double ie_o, ie_p;
+  double chi2_thr;     // chi2_mult * quantile(chi_squared(K - 2), 0.95)
+  int intr;            // !at_clone_m || !at_clone_a (UpdaterLidar.cpp:332)
+  int total_hx;
+};
+
+// One scan point: k neighbour coordinates -> plane -> gates -> g (UN-whitened, 3 NB numbers), weights, chi2.
+//   Gram route: G = A^T A (3x3, uncentred, as the reference's A), condition gate from its extreme eigenvalues
+//   (cond(A)^2 = lmax / lmin, LidarHelper.cpp:305-312), plane abc = -d G^-1 A^T 1 by Cholesky G = L L^T (LidarHelper.cpp:315:
+//   the least-squares solution colPivHouseholderQr returns; the gate bounds cond(G) by plane_max_condi^2 = 4e4, so the normal
+//   equations lose < 5 of 16 digits: 1e-11 against the 1e-9 contract). The neighbour residuals e_j = abc p_j + d serve the
+//   sanity gate (:319-325), the residual rows (UpdaterLidar.cpp:305-310) and - being the least-squares residual of that very
+//   fit, orthogonal to the columns of A - the neighbour part of ||r'||^2 directly: RSS_nb = sum e_j^2 / map_n^2, and the
+//   deleted residual of the scan-point row is its plain whitened residual e5 = res5 / raw_n. Leverage of the scan-point row:
+//   t = (map_n / raw_n)^2 || L^-1 pfinM_fej ||^2. Then ||v||^2 = 1/(1+t), v^T r' = e5/(1+t), ||r'||^2 = RSS_nb + e5^2/(1+t),
+//   chi2 = ||r'||^2 - s (v^T r')^2 / (1 + s ||v||^2), s = h^T P h = g^T Q g / raw_n^2 (header of this file).
+// Returns the status (0 accepted, 2 plane fail, 3 bad match, 4 chi2 reject); the caller has checked knn_ok.
+// Outputs: g[3 NB] un-whitened; W = ||v||^2 / raw_n^2 (weight of g g^T), V = v^T r' / raw_n (weight of g in H^T r).
+struct RowOut {
+  double W, V, chi2, rss, raw_n, res5;
+  double n[3], d;
+};
 template <int K, int NB>
-__device__ __forceinline__ void point_row(const int i, const ml_scan_consts &c, const double *__restrict__ sQ,
-                                          const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
-                                          const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, PointRow &out) {
-  if (!knn_ok[i]) {
-    return;
-  }
-  // ---- neighbours, A = k x 3, d = mean range (LidarHelper.cpp:293-302) ----
-  double A[K][3];
-  double dmean = 0.0;
+__device__ __forceinline__ int point_row(const RowConsts &rc, const double *__restrict__ sQ, const float4 pl4,
+                                         const float4 (&nb)[K], double *__restrict__ g, RowOut &o) {
+  // ---- neighbours: Gram matrix, column sums, mean range (LidarHelper.cpp:293-302) ----
+  float px[K], py[K], pz[K];
+  double g00 = 0, g01 = 0, g02 = 0, g11 = 0, g12 = 0, g22 = 0, sx = 0, sy = 0, sz = 0, dsum = 0;
 #pragma unroll
   for (int j = 0; j < K; j++) {
-    const float4 p = __ldg(&map_pts[knn_idx[(size_t)i * K + j]]);
-    A[j][0] = (double)p.x, A[j][1] = (double)p.y, A[j][2] = (double)p.z;
-    dmean += sqrt(A[j][0] * A[j][0] + A[j][1] * A[j][1] + A[j][2] * A[j][2]);
+    const float4 p = nb[j];
+    px[j] = p.x, py[j] = p.y, pz[j] = p.z;
+    const double x = (double)p.x, y = (double)p.y, z = (double)p.z;
+    g00 = fma(x, x, g00), g01 = fma(x, y, g01), g02 = fma(x, z, g02);
+    g11 = fma(y, y, g11), g12 = fma(y, z, g12), g22 = fma(z, z, g22);
+    sx += x, sy += y, sz += z;
+    dsum += fast_sqrt(fma(x, x, fma(y, y, z * z)));
   }
-  dmean /= (double)K;
+  const double d = dsum * (1.0 / (double)K);
   // ---- condition number gate (LidarHelper.cpp:305-312): cond(A)^2 = lmax/lmin of A^T A ----
   {
-    double g00 = 0, g01 = 0, g02 = 0, g11 = 0, g12 = 0, g22 = 0;
-#pragma unroll
-    for (int j = 0; j < K; j++) {
-      g00 += A[j][0] * A[j][0], g01 += A[j][0] * A[j][1], g02 += A[j][0] * A[j][2];
-      g11 += A[j][1] * A[j][1], g12 += A[j][1] * A[j][2], g22 += A[j][2] * A[j][2];
-    }
     double lmin, lmax;
     sym3_eig_minmax(g00, g01, g02, g11, g12, g22, &lmin, &lmax);
-    // condA > max  <=>  lmax > max^2 * lmin  (lmin <= 0 after rounding means singular: reject, as inf/NaN > max
-    // would... NaN compares false in the reference, but a rank-deficient 5x3 A never passes the later gates)
-    if (!(lmin > 0.0) || lmax > c.plane_max_condi * c.plane_max_condi * lmin) {
-      out.status = 2;
-      return;
-    }
+    // condA > max  <=>  lmax > max^2 lmin. lmin <= 0 after rounding = singular: sigma_max / sigma_min is huge or inf in the
+    // reference (> max: rejected). Its 0/0 = NaN case needs every neighbour at the origin, which a voxel-thinned map cannot hold.
+    if (!(lmin > 0.0) || lmax > rc.condi2 * lmin)
+      return 2;
   }
-  // keep the raw neighbour coordinates for the residuals
-  double PN[K][3];
-#pragma unroll
-  for (int j = 0; j < K; j++) {
-    PN[j][0] = A[j][0], PN[j][1] = A[j][1], PN[j][2] = A[j][2];
-  }
-  // ---- Householder QR of A, applied to b = -d*1 (LidarHelper.cpp:302,315) ----
-  double b[K];
-#pragma unroll
-  for (int j = 0; j < K; j++)
-    b[j] = -dmean;
-  double Rd[3], vdiag[3], vn2[3];
-#pragma unroll
-  for (int cc = 0; cc < 3; cc++) {
-    double sigma = 0.0;
-#pragma unroll
-    for (int r = cc; r < K; r++)
-      sigma += A[r][cc] * A[r][cc];
-    const double nrm = sqrt(sigma);
-    const double alpha = A[cc][cc] > 0.0 ? -nrm : nrm;
-    const double v0 = A[cc][cc] - alpha;
-    const double vnorm2 = sigma - A[cc][cc] * A[cc][cc] + v0 * v0;
-    Rd[cc] = alpha;
-    vdiag[cc] = v0;
-    vn2[cc] = vnorm2;
-    const double inv2 = vnorm2 > 0.0 ? 2.0 / vnorm2 : 0.0;
-#pragma unroll
-    for (int jj = cc + 1; jj < 3; jj++) {
-      double dot = v0 * A[cc][jj];
-#pragma unroll
-      for (int r = cc + 1; r < K; r++)
-        dot += A[r][cc] * A[r][jj];
-      const double f = dot * inv2;
-      A[cc][jj] -= f * v0;
-#pragma unroll
-      for (int r = cc + 1; r < K; r++)
-        A[r][jj] -= f * A[r][cc];
-    }
-    {
-      double dot = v0 * b[cc];
-#pragma unroll
-      for (int r = cc + 1; r < K; r++)
-        dot += A[r][cc] * b[r];
-      const double f = dot * inv2;
-      b[cc] -= f * v0;
-#pragma unroll
-      for (int r = cc + 1; r < K; r++)
-        b[r] -= f * A[r][cc];
-    }
-  }
-  // R = [Rd0 A01 A02; 0 Rd1 A12; 0 0 Rd2]; abc = R^-1 (Q^T b)[0:3]
-  double n[3];
-  n[2] = b[2] / Rd[2];
-  n[1] = (b[1] - A[1][2] * n[2]) / Rd[1];
-  n[0] = (b[0] - A[0][1] * n[1] - A[0][2] * n[2]) / Rd[0];
-  out.plane[0] = n[0], out.plane[1] = n[1], out.plane[2] = n[2], out.plane[3] = dmean;
-  const double nn = sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
-  // ---- sanity check (LidarHelper.cpp:319-325) ----
+  // ---- Cholesky G = L L^T (inverse pivots i0, i1, i2), abc = -d G^-1 s ----
+  const double i0 = rsqrt(g00);
+  const double l10 = g01 * i0, l20 = g02 * i0;
+  const double i1 = rsqrt(fma(-l10, l10, g11));
+  const double l21 = fma(-l20, l10, g12) * i1;
+  const double i2 = rsqrt(fma(-l21, l21, fma(-l20, l20, g22)));
+  double n0, n1, n2;
   {
-    const double pl0 = n[0] / nn, pl1 = n[1] / nn, pl2 = n[2] / nn, pl3 = dmean / nn;
-    bool bad = false;
-#pragma unroll
-    for (int j = 0; j < K; j++)
-      bad = bad || (fabs(pl0 * PN[j][0] + pl1 * PN[j][1] + pl2 * PN[j][2] + pl3) > c.plane_max_p2pd);
-    if (bad || !(nn == nn)) {
-      out.status = 2;
-      return;
-    }
+    const double z0 = -d * sx * i0;
+    const double z1 = fma(-l10, z0, -d * sy) * i1;
+    const double z2 = fma(-l21, z1, fma(-l20, z0, -d * sz)) * i2;
+    n2 = z2 * i2;
+    n1 = fma(-l21, n2, z1) * i1;
+    n0 = fma(-l20, n2, fma(-l10, n1, z0)) * i0;
   }
-  // ---- scan point in the map frame, est and fej (UpdaterLidar.cpp:281-283) ----
-  const float4 pl4 = scan_L[i];
-  const double pfinL[3] = {(double)pl4.x, (double)pl4.y, (double)pl4.z};
-  double t3[3], pfinM_est[3], pfinM_fej[3];
-  d_mat3_vec(c.RLtoM_est, pfinL, t3);
-#pragma unroll
-  for (int a = 0; a < 3; a++)
-    pfinM_est[a] = c.pLinM_est[a] + t3[a];
-  d_mat3_vec(c.RLtoM_fej, pfinL, t3);
-#pragma unroll
-  for (int a = 0; a < 3; a++)
-    pfinM_fej[a] = c.pLinM_fej[a] + t3[a];
-  // ---- bad match gate + residual of the scan point (UpdaterLidar.cpp:296,313) ----
-  const double res5 = -(n[0] * pfinM_est[0] + n[1] * pfinM_est[1] + n[2] * pfinM_est[2]) - dmean;
-  if (res5 > c.plane_max_p2pd * 3.0) {
-    out.status = 3;
-    return;
-  }
-  // ---- g = n * [dpfinM_dI | dpfinM_dA | dpfinM_dcalib] (UpdaterLidar.cpp:320-329) ----
-  double g[ML_G];
+  const double nn = fast_sqrt(fma(n0, n0, fma(n1, n1, n2 * n2)));
+  // ---- sanity check (LidarHelper.cpp:319-325) and the neighbours' residuals (UpdaterLidar.cpp:305-310) in one pass ----
+  double rss_nb = 0.0;
   {
-    double nG[3], nI[3], w[3], v[3], cr[3];
-    d_mat3T_vec(c.RGtoM_fej, n, nG); // (n^T RGtoM)^T
-    d_mat3T_vec(c.RItoG_fej, nG, nI); // (n^T RGtoM RItoG)^T
+    const double lim = rc.p2pd * nn;
+    bool bad = !(nn == nn);
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+      const double e = fma(n0, (double)px[j], fma(n1, (double)py[j], fma(n2, (double)pz[j], d)));
+      bad = bad || (fabs(e) > lim);
+      rss_nb = fma(e, e, rss_nb);
+    }
+    if (bad)
+      return 2;
+  }
+  o.n[0] = n0, o.n[1] = n1, o.n[2] = n2, o.d = d;
+  // ---- scan point in the map frame, est and fej (UpdaterLidar.cpp:281-283); bad match gate + residual (:296,:313) ----
+  const double qx = (double)pl4.x, qy = (double)pl4.y, qz = (double)pl4.z;
+  double res5;
+  {
+    const double mx = fma(rc.RLtoM_est[0], qx, fma(rc.RLtoM_est[1], qy, fma(rc.RLtoM_est[2], qz, rc.pLinM_est[0])));
+    const double my = fma(rc.RLtoM_est[3], qx, fma(rc.RLtoM_est[4], qy, fma(rc.RLtoM_est[5], qz, rc.pLinM_est[1])));
+    const double mz = fma(rc.RLtoM_est[6], qx, fma(rc.RLtoM_est[7], qy, fma(rc.RLtoM_est[8], qz, rc.pLinM_est[2])));
+    res5 = -fma(n0, mx, fma(n1, my, n2 * mz)) - d;
+  }
+  if (res5 > rc.badmatch)
+    return 3;
+  // ---- leverage of the scan-point row: || L^-1 pfinM_fej ||^2 ----
+  double zz;
+  {
+    const double fx = fma(rc.RLtoM_fej[0], qx, fma(rc.RLtoM_fej[1], qy, fma(rc.RLtoM_fej[2], qz, rc.pLinM_fej[0])));
+    const double fy = fma(rc.RLtoM_fej[3], qx, fma(rc.RLtoM_fej[4], qy, fma(rc.RLtoM_fej[5], qz, rc.pLinM_fej[1])));
+    const double fz = fma(rc.RLtoM_fej[6], qx, fma(rc.RLtoM_fej[7], qy, fma(rc.RLtoM_fej[8], qz, rc.pLinM_fej[2])));
+    const double y0 = fx * i0;
+    const double y1 = fma(-l10, y0, fy) * i1;
+    const double y2 = fma(-l21, y1, fma(-l20, y0, fz)) * i2;
+    zz = fma(y0, y0, fma(y1, y1, y2 * y2));
+  }
+  // ---- g = n [dpfinM_dI | dpfinM_dA | dpfinM_dcalib], folded (UpdaterLidar.cpp:320-329; ML_G in common.cuh) ----
+  {
     // -n^T RGtoM RItoG skew(w) = (w x nI)^T, w = RLtoI (pfinL - pIinL)
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-      v[a] = pfinL[a] - c.pIinL_fej[a];
-    d_mat3_vec(c.RLtoI_fej, v, w);
-    d_cross(w, nI, cr);
-    g[0] = cr[0], g[1] = cr[1], g[2] = cr[2];
-    g[3] = nG[0], g[4] = nG[1], g[5] = nG[2];
-    // n^T RItoL skew(u) = (a2 x u)^T, a2 = RItoL^T n, u = RGtoA (pIinG + RItoG pLinI - pAinG + RLtoG pfinL)
-    double a2[3], u[3], t1[3], t2[3];
-    d_mat3T_vec(c.RItoL_fej, n, a2);
-    d_mat3_vec(c.RItoG_fej, c.pLinI_fej, t1);
-    d_mat3_vec(c.RLtoG_fej, pfinL, t2);
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-      v[a] = c.pIinG_fej[a] + t1[a] - c.pAinG_fej[a] + t2[a];
-    d_mat3_vec(c.RGtoA_fej, v, u);
-    d_cross(a2, u, cr);
-    g[6] = cr[0], g[7] = cr[1], g[8] = cr[2];
-    // (the A position block is -nG: folded into rows 3-5 of T, see ML_G)
-    // n^T (skew(c1) - skew(c2) + RLtoM skew(c3)) = (n x c1) - (n x c2) + (a3 x c3)
-    double c1[3], c2[3], c3[3], a3[3], x1[3], x2[3], x3[3];
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-      v[a] = c.pIinG_fej[a] - c.pAinG_fej[a];
-    d_mat3_vec(c.RGtoM_fej, v, c1);
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-      c3[a] = c.pIinL_fej[a] - pfinL[a];
-    d_mat3_vec(c.RLtoM_fej, c3, c2);
-    d_mat3T_vec(c.RLtoM_fej, n, a3);
-    d_cross(n, c1, x1);
-    d_cross(n, c2, x2);
-    d_cross(a3, c3, x3);
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-      g[9 + a] = x1[a] - x2[a] + x3[a];
-      g[12 + a] = n[a] - a3[a];
-    }
-    if (c.calib_col < 0) {
-#pragma unroll
-      for (int a = 9; a < ML_G; a++)
-        g[a] = 0.0;
+    const double wx = fma(rc.RLtoI[0], qx, fma(rc.RLtoI[1], qy, fma(rc.RLtoI[2], qz, rc.pLinI[0])));
+    const double wy = fma(rc.RLtoI[3], qx, fma(rc.RLtoI[4], qy, fma(rc.RLtoI[5], qz, rc.pLinI[1])));
+    const double wz = fma(rc.RLtoI[6], qx, fma(rc.RLtoI[7], qy, fma(rc.RLtoI[8], qz, rc.pLinI[2])));
+    const double ix = fma(rc.RItoM[0], n0, fma(rc.RItoM[3], n1, rc.RItoM[6] * n2));
+    const double iy = fma(rc.RItoM[1], n0, fma(rc.RItoM[4], n1, rc.RItoM[7] * n2));
+    const double iz = fma(rc.RItoM[2], n0, fma(rc.RItoM[5], n1, rc.RItoM[8] * n2));
+    g[0] = fma(wy, iz, -wz * iy), g[1] = fma(wz, ix, -wx * iz), g[2] = fma(wx, iy, -wy * ix);
+    g[3] = fma(rc.RGtoM[0], n0, fma(rc.RGtoM[3], n1, rc.RGtoM[6] * n2));
+    g[4] = fma(rc.RGtoM[1], n0, fma(rc.RGtoM[4], n1, rc.RGtoM[7] * n2));
+    g[5] = fma(rc.RGtoM[2], n0, fma(rc.RGtoM[5], n1, rc.RGtoM[8] * n2));
+    // n^T RItoL skew(u) = (a2 x u)^T, a2 = RItoL^T n
+    const double ax = fma(rc.RItoL[0], n0, fma(rc.RItoL[3], n1, rc.RItoL[6] * n2));
+    const double ay = fma(rc.RItoL[1], n0, fma(rc.RItoL[4], n1, rc.RItoL[7] * n2));
+    const double az = fma(rc.RItoL[2], n0, fma(rc.RItoL[5], n1, rc.RItoL[8] * n2));
+    const double ux = fma(rc.U1[0], qx, fma(rc.U1[1], qy, fma(rc.U1[2], qz, rc.U0[0])));
+    const double uy = fma(rc.U1[3], qx, fma(rc.U1[4], qy, fma(rc.U1[5], qz, rc.U0[1])));
+    const double uz = fma(rc.U1[6], qx, fma(rc.U1[7], qy, fma(rc.U1[8], qz, rc.U0[2])));
+    g[6] = fma(ay, uz, -az * uy), g[7] = fma(az, ux, -ax * uz), g[8] = fma(ax, uy, -ay * ux);
+    if (NB == 5) {
+      // n^T (skew(c1) - skew(c2) + RLtoM skew(c3)) = n x (c1 - c2) + a3 x c3, c3 = pIinL - pfinL, c2 = RLtoM c3, a3 = RLtoM^T n
+      const double c3x = rc.pIinL[0] - qx, c3y = rc.pIinL[1] - qy, c3z = rc.pIinL[2] - qz;
+      const double ex = rc.c1[0] - fma(rc.RLtoM_fej[0], c3x, fma(rc.RLtoM_fej[1], c3y, rc.RLtoM_fej[2] * c3z));
+      const double ey = rc.c1[1] - fma(rc.RLtoM_fej[3], c3x, fma(rc.RLtoM_fej[4], c3y, rc.RLtoM_fej[5] * c3z));
+      const double ez = rc.c1[2] - fma(rc.RLtoM_fej[6], c3x, fma(rc.RLtoM_fej[7], c3y, rc.RLtoM_fej[8] * c3z));
+      const double tx = fma(rc.RLtoM_fej[0], n0, fma(rc.RLtoM_fej[3], n1, rc.RLtoM_fej[6] * n2));
+      const double ty = fma(rc.RLtoM_fej[1], n0, fma(rc.RLtoM_fej[4], n1, rc.RLtoM_fej[7] * n2));
+      const double tz = fma(rc.RLtoM_fej[2], n0, fma(rc.RLtoM_fej[5], n1, rc.RLtoM_fej[8] * n2));
+      g[9] = fma(n1, ez, -n2 * ey) + fma(ty, c3z, -tz * c3y);
+      g[10] = fma(n2, ex, -n0 * ez) + fma(tz, c3x, -tx * c3z);
+      g[11] = fma(n0, ey, -n1 * ex) + fma(tx, c3y, -ty * c3x);
+      g[12] = n0 - tx, g[13] = n1 - ty, g[14] = n2 - tz;
     }
   }
   // ---- interpolation-error inflation (UpdaterLidar.cpp:332-337) and whitening scales (:353-354) ----
   double intr_std = 0.0;
-  if (!c.at_clone_m || !c.at_clone_a)
-    intr_std = sqrt(c.ie_o * (g[0] * g[0] + g[1] * g[1] + g[2] * g[2]) + c.ie_p * (g[3] * g[3] + g[4] * g[4] + g[5] * g[5]));
-  const double raw_n = nn * c.raw_noise + intr_std;
-  const double map_n = nn * c.map_noise + intr_std;
-  // ---- neighbour residuals (UpdaterLidar.cpp:305-310), pushed through the same reflectors: Q^T res_nb ----
-  double rn[K];
-#pragma unroll
-  for (int j = 0; j < K; j++)
-    rn[j] = -(n[0] * PN[j][0] + n[1] * PN[j][1] + n[2] * PN[j][2]) - dmean;
-#pragma unroll
-  for (int cc = 0; cc < 3; cc++) {
-    const double inv2 = vn2[cc] > 0.0 ? 2.0 / vn2[cc] : 0.0;
-    double dot = vdiag[cc] * rn[cc];
-#pragma unroll
-    for (int r = cc + 1; r < K; r++)
-      dot += A[r][cc] * rn[r];
-    const double f = dot * inv2;
-    rn[cc] -= f * vdiag[cc];
-#pragma unroll
-    for (int r = cc + 1; r < K; r++)
-      rn[r] -= f * A[r][cc];
-  }
-  // beta_nb = R^-1 (Q^T res_nb)[0:3] (zero up to rounding: res_nb is the least-squares residual of the plane fit)
-  double beta[3];
-  beta[2] = rn[2] / Rd[2];
-  beta[1] = (rn[1] - A[1][2] * beta[2]) / Rd[1];
-  beta[0] = (rn[0] - A[0][1] * beta[1] - A[0][2] * beta[2]) / Rd[0];
-  double rss_nb = 0.0;
-#pragma unroll
-  for (int r = 3; r < K; r++)
-    rss_nb += rn[r] * rn[r];
-  rss_nb /= (map_n * map_n);
-  // leverage of the scan-point row: t = (map_n/raw_n)^2 || R^-T pfinM_fej ||^2
-  double z[3];
-  z[0] = pfinM_fej[0] / Rd[0];
-  z[1] = (pfinM_fej[1] - A[0][1] * z[0]) / Rd[1];
-  z[2] = (pfinM_fej[2] - A[0][2] * z[0] - A[1][2] * z[1]) / Rd[2];
-  const double ratio = map_n / raw_n;
-  const double tlev = ratio * ratio * (z[0] * z[0] + z[1] * z[1] + z[2] * z[2]);
-  // deleted residual of the scan-point row (whitened)
-  const double e5 = (res5 - (pfinM_fej[0] * beta[0] + pfinM_fej[1] * beta[1] + pfinM_fej[2] * beta[2])) / raw_n;
-  const double wv = 1.0 / (1.0 + tlev);
+  if (rc.intr)
+    intr_std = fast_sqrt(fma(rc.ie_o, fma(g[0], g[0], fma(g[1], g[1], g[2] * g[2])), rc.ie_p * fma(g[3], g[3], fma(g[4], g[4], g[5] * g[5]))));
+  const double raw_n = fma(nn, rc.raw_noise, intr_std);
+  const double map_n = fma(nn, rc.map_noise, intr_std);
+  const double inv = 1.0 / (raw_n * map_n); // one division for both reciprocals
+  const double ir = inv * map_n, im = inv * raw_n;
+  const double ratio = map_n * ir;
+  const double wv = 1.0 / fma(ratio * ratio, zz, 1.0); // ||v||^2 = 1 / (1 + t)
+  const double e5 = res5 * ir;
   const double vr = e5 * wv;
-  const double rss = rss_nb + e5 * e5 * wv;
-  // ---- s = h^T P h = g_w^T Q g_w ----
-  const double ir = 1.0 / raw_n;
-#pragma unroll
-  for (int a = 0; a < ML_G; a++)
-    g[a] *= ir;
-  // sQ = packed upper triangle of Q (ML_G x ML_G) by rows, off-diagonal entries doubled (Q is symmetric). Only the leading
-  // 3*NB entries of g are non-zero (NB = 3 without extrinsic calibration: 45 terms; NB = 5: 120 terms).
+  const double rss = fma(rss_nb * im, im, e5 * e5 * wv);
+  // ---- s = h^T P h = g^T Q g / raw_n^2: sQ = upper triangle of Q by rows with the off-diagonal entries doubled, row a at
+  //      sQ[a * 3 NB ...] (full row stride: no index arithmetic) ----
   double s = 0.0;
-  {
 #pragma unroll
-    for (int a = 0; a < 3 * NB; a++) {
-      double acc = 0.0;
+  for (int a = 0; a < 3 * NB; a++) {
+    double acc = 0.0;
 #pragma unroll
-      for (int bq = a; bq < 3 * NB; bq++)
-        acc += sQ[a * ML_G - (a * (a - 1)) / 2 + (bq - a)] * g[bq];
-      s += g[a] * acc;
-    }
+    for (int b = a; b < 3 * NB; b++)
+      acc = fma(sQ[a * (3 * NB) + b], g[b], acc);
+    s = fma(g[a], acc, s);
   }
-  const double chi2 = rss - s * vr * vr / (1.0 + s * wv);
-#pragma unroll
-  for (int a = 0; a < ML_G; a++)
-    out.g[a] = g[a];
-  out.w = wv;
-  out.vr = vr;
-  out.chi2 = chi2;
-  out.res = res5 / raw_n;
-  out.raw_n = raw_n;
-  out.rss = rss;
-  out.status = (chi2 < c.chi2_mult * chi2_q95(K - 2)) ? 0 : 4; // NaN -> reject (UpdaterStatistics.cpp:117)
+  s *= ir * ir;
+  const double chi2 = rss - s * vr * vr / fma(s, wv, 1.0);
+  o.W = wv * ir * ir;
+  o.V = vr * ir;
+  o.chi2 = chi2;
+  o.rss = rss;
+  o.raw_n = raw_n;
+  o.res5 = res5;
+  return (chi2 < rc.chi2_thr) ? 0 : 4; // NaN -> reject (UpdaterStatistics.cpp:117)
 }
 
 // ------------------------------------------------------------------------------------------------
 // Fused rows + reduction + finalize (one launch per scan). Warp-autonomous: no CTA-wide barrier in the main loop.
 //  * the scan is cut into tiles of 32 points; tile j belongs to global warp j mod NW, with global warp id
 //    gw = warp_in_cta * gridDim + cta (so a partial last round spreads over all SMs). A warp walks its tiles in order.
-//  * phase 1 (32 lanes): lane computes point_row of its point and leaves g (ML_G = 15 folded numbers, 9 non-zero without
-//    extrinsic calibration), w, v^T r in the warp's shared-memory slab (never in HBM unless the parity export `rows_out` is
-//    requested); chi2 statistics by a fixed shuffle tree.
-//  * phase 2: G = sum w g g^T is cut into 3x3 blocks; with NB = 3 (no calibration) or 5 block rows there are
+//    The host picks the block size so that the number of tile rounds per warp is whole or nearly so (launch_rows_nb).
+//  * phase 1 (32 lanes): lane computes point_row of its point from the k neighbour coordinates the kNN kernel left in `nbr`
+//    (coalesced: 16 k bytes per point, scan order) and leaves g (3 NB numbers, un-whitened), W, V in the warp's shared-memory
+//    slab (never in HBM unless the parity export `rows_out` is requested); chi2 statistics by a fixed shuffle tree.
+//  * phase 2: G = sum W g g^T is cut into 3x3 blocks; with NB = 3 (no calibration) or 5 block rows there are
 //    NB(NB+1)/2 = 6 or 15 upper-triangle blocks ("roles"). The 32 lanes are split into 5 (or 2) groups of roles; group j
 //    adds the points p = j, j + groups, ... of the tile, so one tile costs 7 (or 16) iterations of 7 shared loads and 9 to 12
-//    FMAs instead of 32; diagonal blocks also carry b = sum g (v^T r). Running sums live in the warp's slab, one slot per lane.
+//    FMAs instead of 32; diagonal blocks also carry b = sum g V. Running sums live in the warp's slab, one slot per lane.
 //  * end: one barrier, CTA partial = sum over its warps and groups in fixed order -> parts[e][cta] (entry-major so the final
 //    pass reads coalesced); the last CTA to finish (ticket) adds the partials in CTA order, expands HtH = T^T G T,
-//    Htr = T^T b and writes the result block. Every sum has a fixed order for a given scan size and SM count: bit-reproducible.
+//    Htr = T^T b and writes the result block. Every sum has a fixed order for a given scan size and launch shape: bit-reproducible.
 // ------------------------------------------------------------------------------------------------
-#ifndef ML_RR_BLOCK
-#define ML_RR_BLOCK 512
-#endif
-constexpr int RR_BLOCK = ML_RR_BLOCK;
-constexpr int RR_WARPS = RR_BLOCK / 32;
-constexpr int RR_NE = ML_GSYM + ML_G; // 135
-constexpr int RR_ROW = ML_G + 2;      // odd row stride of g in shared memory (bank-conflict-free stores)
+constexpr int RR_BLOCK = 512, RR_BLOCK_MID = 896, RR_BLOCK_BIG = 1024; // 16, 28 or 32 warps per SM (one CTA per SM either way)
 constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diagonal blocks)
-#define ML_NRED (RR_NE + 3)           // + sum_chi, sum_chi2, sum_res2
+// reduced entries for NB block rows: upper triangle of G (NG (NG + 1) / 2), b (NG), sum_chi, sum_chi2, sum_res2
+#define ML_NRED (ML_GSYM + ML_G + 3)
 struct RRParts {
-  double v[ML_NRED][ML_NPART_MAX];
+  double v[ML_NRED][ML_NPART_MAX]; // entry-major: the final pass reads an entry's CTA partials as one contiguous run
   int c[5][ML_NPART_MAX];
 };
-// per-warp slab: g rows | w | vr | running sums (one slot per lane) | 4 statistics
-constexpr int RR_SLAB = 32 * RR_ROW + 32 + 32 + 32 * RR_RACC + 4;
-constexpr size_t RR_SMEM = sizeof(double) * ((size_t)RR_WARPS * RR_SLAB + ML_GSYM + 1) + sizeof(ml_scan_consts) + 64;
+// per-warp slab: g rows (odd stride: conflict-free stores) | W | V | running sums (one slot per lane) | statistics
+template <int NB> struct RRLayout {
+  static constexpr int NG = 3 * NB;
+  static constexpr int NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 3;
+  static constexpr int ROW = NG + 2;
+  static constexpr int SLAB = 32 * ROW + 32 + 32 + 32 * RR_RACC + 8; // + chi, chi^2, rss | 5 status counters (as int)
+  static constexpr int TAIL = 256 + NG * NG + 32 + NG * ML_MAX_HX + ML_MAX_HX * ML_MAX_HX + ML_MAX_HX; // last CTA's scratch
+  static constexpr int FIXED = NG * NG + NG * ML_MAX_HX + 16;                                          // Q | T | scan state
+  static constexpr size_t smem(int warps) {
+    return sizeof(double) * (size_t)((warps * SLAB > TAIL ? warps * SLAB : TAIL) + FIXED);
+  }
+};
 
 template <int NB> __device__ __forceinline__ int rr_role_of(int bi, int bj) { return bi * NB - (bi * (bi - 1)) / 2 + (bj - bi); }
 
-template <int K, int NB>
-__global__ void __launch_bounds__(RR_BLOCK, 1)
-    k_rows_reduce(const ScanState *__restrict__ st, const float4 *__restrict__ scan_L, const float4 *__restrict__ map_pts,
-                  const int32_t *__restrict__ knn_idx, const uint8_t *__restrict__ knn_ok, const DevConsts *__restrict__ dc,
-                  PointRow *__restrict__ rows_out, RRParts *__restrict__ parts, unsigned int *__restrict__ ticket,
-                  LinsysOut *__restrict__ out) {
+// EXPORT: also write the per-point rows (parity export, ml_point_rows); the timed instantiation carries none of that state.
+template <int K, int NB, int BLOCK, bool EXPORT>
+__global__ void __launch_bounds__(BLOCK, 1)
+    k_rows_reduce(const __grid_constant__ RowConsts rc, const ScanState *__restrict__ st, int n_ub, const float4 *__restrict__ scan_L,
+                  const float4 *__restrict__ nbr, const DevConsts *__restrict__ dc, PointRow *__restrict__ rows_out,
+                  RRParts *__restrict__ parts, unsigned int *__restrict__ ticket, LinsysOut *__restrict__ out,
+                  unsigned long long *__restrict__ tl /* debug timeline (ml_debug_timeline) or NULL */) {
+  using LY = RRLayout<NB>;
+  tl_mark(tl, 0);
+  constexpr int NG = LY::NG, ROW = LY::ROW, SLAB = LY::SLAB, WARPS = BLOCK / 32, NSYM = LY::NSYM, NE = LY::NE, NRED = LY::NRED;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *slabs = reinterpret_cast<double *>(smem_raw);
-  double *sQ = slabs + (size_t)RR_WARPS * RR_SLAB; // packed Qu (171)
-  ml_scan_consts *scp = reinterpret_cast<ml_scan_consts *>(sQ + ML_GSYM + 1);
+  double *sQ = slabs + (WARPS * SLAB > LY::TAIL ? WARPS * SLAB : LY::TAIL); // [NG][NG], upper triangle used
+  double *sT = sQ + NG * NG;                                                 // [NG][ML_MAX_HX]: rows of T (for the last CTA)
+  int *sst = reinterpret_cast<int *>(sT + NG * ML_MAX_HX);                   // ScanState
   __shared__ int scnt[5];
   __shared__ unsigned int s_last;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
-  pdl_enter();
+  const int nb = gridDim.x;
+  // Tile -> warp: round r = wid, wid + WARPS, ... covers the nb tiles [r nb, (r + 1) nb); inside a round the CTAs are rotated
+  // by r, so a CTA's tiles do not share a residue mod nb. A spinning LiDAR's scan is periodic in the point index (rings x
+  // azimuths: 32 consecutive points are the lower or the upper half of a 64-beam column) and a plain stride nb gave the even
+  // CTAs all the ground returns and the odd ones the sky: 11 us against 4.6 us of tile loop on neighbouring SMs.
+  const auto tile_of = [&](int r) { return r * nb + (((int)blockIdx.x + nb - r % nb) % nb); };
+  // Per-scan constants first: Q, T (k_prep_consts on the side stream, joined by an event BEFORE this launch) and the scan state
+  // (front end, two kernels back) are complete whenever this kernel runs at all, so they are staged before the programmatic
+  // dependency on the kNN kernel is waited for - behind its tail instead of on the critical path.
+  pdl_launch();
   {
-    const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
-    const int *src = reinterpret_cast<const int *>(&dc->c);
-    int *dst = reinterpret_cast<int *>(scp);
-    for (int e = t; e < nw; e += RR_BLOCK)
-      dst[e] = src[e];
-    for (int e = t; e < ML_GSYM; e += RR_BLOCK)
-      sQ[e] = dc->Qu[e];
+    // upper triangle of Q (leading NG x NG block) with the off-diagonal entries doubled
+    for (int e = t; e < NG * NG; e += BLOCK) {
+      const int a = e / NG, b = e - a * NG;
+      sQ[e] = b < a ? 0.0 : (b == a ? dc->Q[a * ML_G + a] : dc->Q[a * ML_G + b] + dc->Q[b * ML_G + a]);
+    }
+    for (int e = t; e < NG * ML_MAX_HX; e += BLOCK)
+      sT[e] = dc->T[e];
+    if (t < (int)(sizeof(ScanState) / sizeof(int)))
+      sst[t] = reinterpret_cast<const int *>(st)[t];
     if (t < 5)
       scnt[t] = 0;
   }
-  double *sg = slabs + (size_t)wid * RR_SLAB; // [32][RR_ROW]
-  double *sw = sg + 32 * RR_ROW;               // [32]
-  double *svr = sw + 32;                       // [32]
-  double *sacc = svr + 32;                     // [32 lanes][RR_RACC]
-  double *sstat = sacc + 32 * RR_RACC;         // chi, chi^2, rss
-  for (int e = lane; e < 32 * RR_RACC + 4; e += 32)
+  double *sg = slabs + (size_t)wid * SLAB; // [32][ROW]
+  double *sw = sg + 32 * ROW;              // [32]
+  double *sv = sw + 32;                    // [32]
+  double *sacc = sv + 32;                  // [32 lanes][RR_RACC]
+  double *sstat = sacc + 32 * RR_RACC;     // chi, chi^2, rss
+  int *scst = reinterpret_cast<int *>(sstat + 3); // 5 status counters of this warp
+  for (int e = lane; e < 32 * RR_RACC + 8; e += 32)
     sacc[e] = 0.0;
+  pdl_wait();
+  tl_mark(tl, 1);
+  // the inputs of this warp's first tile are requested before the CTA barrier (n_ub = host-side bound of the scan size; what
+  // lies past the device-side count is stale but readable, and discarded below)
+  float4 nb0[K], pl0;
+  {
+    const int i0 = (tile_of(wid) << 5) + lane;
+    const bool pre = i0 < n_ub;
+#pragma unroll
+    for (int j = 0; j < K; j++)
+      nb0[j] = pre ? __ldg(&nbr[(size_t)i0 * K + j]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    pl0 = pre ? __ldg(&scan_L[i0]) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   __syncthreads();
-  const ml_scan_consts &c = *scp;
-  const int n = st->n_scan;
-  const int nb = gridDim.x;
-  const int NW = nb * RR_WARPS;
-  const int gw = wid * nb + (int)blockIdx.x;
+  tl_mark(tl, 2);
+  const int n = reinterpret_cast<const ScanState *>(sst)->n_scan;
   const int ntiles = (n + 31) >> 5;
-  // phase-2 role of this lane: group `grp` of points, block (bi, bj), bi <= bj
+  // phase-2 role of this lane: group of points, block (bi, bj), bi <= bj
   constexpr int ROLES = NB * (NB + 1) / 2;
   constexpr int GROUPS = 32 / ROLES;
-  const int grp = lane / ROLES, role = lane - grp * ROLES;
   const bool p2_lane = lane < ROLES * GROUPS;
-  int bi = 0, bj = 0;
-  {
-    int r = 0, rem = role;
-    while (rem >= NB - r) {
-      rem -= NB - r;
-      r++;
-    }
-    bi = r;
-    bj = r + rem;
-  }
-  int c_st[5] = {0, 0, 0, 0, 0};
 
-  for (int tile = gw; tile < ntiles; tile += NW) {
-    const int i = (tile << 5) + lane;
+  const int nrounds = (ntiles + nb - 1) / nb;
+  for (int r = wid; r < nrounds; r += WARPS) {
+    const int tile = tile_of(r);
+    const int i = (tile << 5) + lane; // >= n for the tiles of the last round that do not exist: the warp idles through
     // ---- phase 1 ----
-    PointRow pr;
+    if (r != wid && i < n) {
 #pragma unroll
-    for (int a = 0; a < ML_G; a++)
-      pr.g[a] = 0.0;
-    pr.w = pr.vr = pr.chi2 = pr.res = pr.raw_n = pr.rss = 0.0;
-    pr.plane[0] = pr.plane[1] = pr.plane[2] = pr.plane[3] = 0.0;
-    pr.pad = 0;
-    pr.status = 1;
-    if (i < n) {
-      point_row<K, NB>(i, c, sQ, scan_L, map_pts, knn_idx, knn_ok, pr);
-      if (rows_out)
-        rows_out[i] = pr;
+      for (int j = 0; j < K; j++)
+        nb0[j] = __ldg(&nbr[(size_t)i * K + j]);
+      pl0 = __ldg(&scan_L[i]);
     }
-    const bool okp = i < n && pr.status == 0;
+    int status = 1;
+    double g[NG];
+    RowOut ro;
+    ro.W = ro.V = ro.chi2 = ro.rss = ro.raw_n = ro.res5 = ro.d = 0.0;
+    ro.n[0] = ro.n[1] = ro.n[2] = 0.0;
 #pragma unroll
-    for (int a = 0; a < ML_G; a++)
-      sg[lane * RR_ROW + a] = okp ? pr.g[a] : 0.0;
-    sw[lane] = okp ? pr.w : 0.0;
-    svr[lane] = okp ? pr.vr : 0.0;
+    for (int a = 0; a < NG; a++)
+      g[a] = 0.0;
+    // the kNN kernel marks a query get_neighbors rejects (LidarHelper.cpp:280-285) with a NaN first coordinate
+    if (i < n && nb0[0].x == nb0[0].x)
+      status = point_row<K, NB>(rc, sQ, pl0, nb0, g, ro);
+    const bool okp = status == 0;
+    if (EXPORT && i < n) { // parity export only: whitened g like the reference's H row
+      PointRow pr;
+      const bool reached = status == 0 || status == 4;
+      const double ir = reached ? 1.0 / ro.raw_n : 0.0;
+#pragma unroll
+      for (int a = 0; a < ML_G; a++)
+        pr.g[a] = (a < NG && reached) ? g[a < NG ? a : 0] * ir : 0.0;
+      pr.w = reached ? ro.W * ro.raw_n * ro.raw_n : 0.0;
+      pr.vr = reached ? ro.V * ro.raw_n : 0.0;
+      pr.chi2 = reached ? ro.chi2 : 0.0;
+      pr.res = reached ? ro.res5 * ir : 0.0;
+      pr.raw_n = reached ? ro.raw_n : 0.0;
+      pr.rss = reached ? ro.rss : 0.0;
+      const bool has_plane = status == 0 || status == 3 || status == 4;
+      pr.plane[0] = has_plane ? ro.n[0] : 0.0, pr.plane[1] = has_plane ? ro.n[1] : 0.0, pr.plane[2] = has_plane ? ro.n[2] : 0.0;
+      pr.plane[3] = has_plane ? ro.d : 0.0;
+      pr.status = status;
+      pr.pad = 0;
+      rows_out[i] = pr;
+    }
+#pragma unroll
+    for (int a = 0; a < NG; a++)
+      sg[lane * ROW + a] = okp ? g[a] : 0.0;
+    sw[lane] = okp ? ro.W : 0.0;
+    sv[lane] = okp ? ro.V : 0.0;
     {
-      const bool tested = i < n && (pr.status == 0 || pr.status == 4) && (pr.chi2 == pr.chi2);
-      double vchi = tested ? pr.chi2 : 0.0, vrss = tested ? pr.rss : 0.0;
+      const bool tested = (status == 0 || status == 4) && (ro.chi2 == ro.chi2);
+      double vchi = tested ? ro.chi2 : 0.0, vrss = tested ? ro.rss : 0.0;
       double vchi2 = vchi * vchi;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
@@ -530,28 +540,48 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
         sstat[1] += vchi2;
         sstat[2] += vrss;
       }
+      // status counters: lane q < 5 counts status q
+      int mine = 0;
 #pragma unroll
-      for (int q = 0; q < 5; q++)
-        c_st[q] += __popc(__ballot_sync(0xffffffffu, i < n && pr.status == q));
+      for (int q = 0; q < 5; q++) {
+        const int cq = __popc(__ballot_sync(0xffffffffu, i < n && status == q));
+        mine = lane == q ? cq : mine;
+      }
+      if (lane < 5)
+        scst[lane] += mine;
     }
     const unsigned any_ok = __ballot_sync(0xffffffffu, okp);
     __syncwarp();
     // ---- phase 2 ----
     if (any_ok && p2_lane) {
+      const int grp = lane / ROLES, role = lane - grp * ROLES;
+      int bi = 0, bj = 0;
+      {
+        int r = 0, rem = role;
+#pragma unroll
+        for (int q = 0; q < NB; q++) {
+          if (rem >= NB - r) {
+            rem -= NB - r;
+            r++;
+          }
+        }
+        bi = r;
+        bj = r + rem;
+      }
       double a9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       double b3[3] = {0, 0, 0};
       const double *gI = sg + 3 * bi, *gJ = sg + 3 * bj;
 #pragma unroll 4
       for (int p = grp; p < 32; p += GROUPS) {
         const double w = sw[p];
-        const double x0 = gI[p * RR_ROW] * w, x1 = gI[p * RR_ROW + 1] * w, x2 = gI[p * RR_ROW + 2] * w;
-        const double y0 = gJ[p * RR_ROW], y1 = gJ[p * RR_ROW + 1], y2 = gJ[p * RR_ROW + 2];
+        const double x0 = gI[p * ROW] * w, x1 = gI[p * ROW + 1] * w, x2 = gI[p * ROW + 2] * w;
+        const double y0 = gJ[p * ROW], y1 = gJ[p * ROW + 1], y2 = gJ[p * ROW + 2];
         a9[0] += x0 * y0, a9[1] += x0 * y1, a9[2] += x0 * y2;
         a9[3] += x1 * y0, a9[4] += x1 * y1, a9[5] += x1 * y2;
         a9[6] += x2 * y0, a9[7] += x2 * y1, a9[8] += x2 * y2;
         if (bi == bj) {
-          const double vr = svr[p];
-          b3[0] += y0 * vr, b3[1] += y1 * vr, b3[2] += y2 * vr;
+          const double v = sv[p];
+          b3[0] += y0 * v, b3[1] += y1 * v, b3[2] += y2 * v;
         }
       }
       double *my = sacc + lane * RR_RACC;
@@ -564,50 +594,44 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     }
     __syncwarp();
   }
-  if (lane == 0) {
-#pragma unroll
-    for (int q = 0; q < 5; q++)
-      if (c_st[q])
-        atomicAdd(&scnt[q], c_st[q]);
-  }
+  __syncwarp();
+  tl_mark(tl, 3);
+  if (lane < 5 && scst[lane])
+    atomicAdd(&scnt[lane], scst[lane]);
   __syncthreads();
-  // ---- CTA partial: sum over the warps in warp order ----
-  if (t < RR_NE) {
-    int erole = -1, q = 0;
-    if (t < ML_GSYM) {
+  tl_mark(tl, 4);
+  // ---- CTA partial: sum over the warps in warp order. Entry e < NSYM: G(gi, gj), gi <= gj, by rows of the NG x NG upper
+  //      triangle; NSYM <= e < NE: b; then the three statistics ----
+  if (t < NE) {
+    int erole, q;
+    if (t < NSYM) {
       int r = 0, rem = t;
-      while (rem >= ML_G - r) {
-        rem -= ML_G - r;
+      while (rem >= NG - r) {
+        rem -= NG - r;
         r++;
       }
       const int gi = r, gj = r + rem;
-      if (gj < 3 * NB) {
-        erole = rr_role_of<NB>(gi / 3, gj / 3);
-        q = (gi % 3) * 3 + (gj % 3);
-      }
+      erole = rr_role_of<NB>(gi / 3, gj / 3);
+      q = (gi % 3) * 3 + (gj % 3);
     } else {
-      const int a = t - ML_GSYM;
-      if (a < 3 * NB) {
-        erole = rr_role_of<NB>(a / 3, a / 3);
-        q = 9 + a % 3;
-      }
+      const int a = t - NSYM;
+      erole = rr_role_of<NB>(a / 3, a / 3);
+      q = 9 + a % 3;
     }
     double v = 0.0;
-    if (erole >= 0) {
-      for (int w = 0; w < RR_WARPS; w++)
+    for (int w = 0; w < WARPS; w++)
 #pragma unroll
-        for (int gq = 0; gq < GROUPS; gq++)
-          v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + (gq * ROLES + erole) * RR_RACC + q];
-    }
-    parts->v[t][blockIdx.x] = v;
-  } else if (t < RR_NE + 3) {
-    const int q = t - RR_NE;
+      for (int gq = 0; gq < GROUPS; gq++)
+        v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + (gq * ROLES + erole) * RR_RACC + q];
+    __stcg(&parts->v[t][blockIdx.x], v);
+  } else if (t < NRED) {
+    const int q = t - NE;
     double v = 0.0;
-    for (int w = 0; w < RR_WARPS; w++)
-      v += slabs[(size_t)w * RR_SLAB + 32 * RR_ROW + 64 + 32 * RR_RACC + q];
-    parts->v[t][blockIdx.x] = v;
+    for (int w = 0; w < WARPS; w++)
+      v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + 32 * RR_RACC + q];
+    __stcg(&parts->v[t][blockIdx.x], v);
   } else if (t >= 192 && t < 197) {
-    parts->c[t - 192][blockIdx.x] = scnt[t - 192];
+    __stcg(&parts->c[t - 192][blockIdx.x], scnt[t - 192]);
   }
   // ---- last CTA finalizes ----
   __threadfence();
@@ -617,96 +641,119 @@ __global__ void __launch_bounds__(RR_BLOCK, 1)
     s_last = (prev == (unsigned int)nb - 1u) ? 1u : 0u;
   }
   __syncthreads();
-  if (!s_last)
+  tl_mark(tl, 5);
+  if (!s_last) {
+    if (tl && t == 0) { // slot 7 of a CTA that is not the last one: the SM it ran on
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      tl[(size_t)blockIdx.x * ML_TL_SLOTS + 7] = smid;
+    }
     return;
+  }
   __threadfence();
   // shared-memory carve-up for the tail (the slabs are dead now)
-  double *fsum = slabs;               // [ML_NRED]
-  double *G = fsum + 256;             // [18][18]
-  double *bv = G + ML_G * ML_G;       // [18]
-  double *sT = bv + 32;               // [18][ML_MAX_HX]
-  double *GT = sT + ML_G * ML_MAX_HX; // [18][ML_MAX_HX]
-  const int hx = c.total_hx;
-  const volatile RRParts *vp = parts; // written by other CTAs: do not serve from L1
-  for (int q = wid; q < ML_NRED; q += RR_WARPS) {
-    double v = 0.0;
-    for (int bq = lane; bq < nb; bq += 32)
-      v += vp->v[q][bq];
+  double *fsum = slabs;              // [NRED]
+  double *G = fsum + 256;            // [NG][NG]
+  double *bv = G + NG * NG;          // [NG]
+  double *GT = bv + 32;              // [NG][ML_MAX_HX]
+  double *Hs = GT + NG * ML_MAX_HX;  // [hx][hx] + [hx]
+  const int hx = rc.total_hx;
+  // the partials of every entry: all loads of a warp's entries are issued before the first shuffle (one L2 round trip; they were
+  // written by other CTAs: __ldcg reads L2, never a stale L1 line)
+  {
+    constexpr int EPW = (NRED + WARPS - 1) / WARPS; // entries per warp
+    double acc[EPW];
+    int cacc = 0; // integer counters: the last 5 warps take one each, in the same batch of loads
+    const int cq = wid - (WARPS - 5);
+    if (cq >= 0)
+      for (int bq = lane; bq < nb; bq += 32)
+        cacc += __ldcg(&parts->c[cq][bq]);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-      v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0)
-      fsum[q] = v;
-  }
-  if (wid < 5) { // integer counters
-    int v = 0;
-    for (int bq = lane; bq < nb; bq += 32)
-      v += vp->c[wid][bq];
+    for (int u = 0; u < EPW; u++) {
+      const int q = wid + u * WARPS;
+      double v = 0.0;
+      if (q < NRED)
+        for (int bq = lane; bq < nb; bq += 32)
+          v += __ldcg(&parts->v[q][bq]);
+      acc[u] = v;
+    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-      v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0)
-      scnt[wid] = v;
+    for (int u = 0; u < EPW; u++) {
+      double v = acc[u];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+      const int q = wid + u * WARPS;
+      if (lane == 0 && q < NRED)
+        fsum[q] = v;
+    }
+    if (cq >= 0) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        cacc += __shfl_xor_sync(0xffffffffu, cacc, o);
+      if (lane == 0)
+        scnt[cq] = cacc;
+    }
   }
-  for (int q = t; q < ML_G * ML_MAX_HX; q += RR_BLOCK)
-    sT[q] = dc->T[q];
   __syncthreads();
-  if (t < ML_GSYM) {
+  tl_mark(tl, 6);
+  if (t < NSYM) {
     int r = 0, rem = t;
-    while (rem >= ML_G - r) {
-      rem -= ML_G - r;
+    while (rem >= NG - r) {
+      rem -= NG - r;
       r++;
     }
-    G[r * ML_G + r + rem] = fsum[t];
-    G[(r + rem) * ML_G + r] = fsum[t];
-  } else if (t < RR_NE) {
-    bv[t - ML_GSYM] = fsum[t];
-  } else if (t == RR_NE) {
+    G[r * NG + r + rem] = fsum[t];
+    G[(r + rem) * NG + r] = fsum[t];
+  } else if (t < NE) {
+    bv[t - NSYM] = fsum[t];
+  } else if (t == NE) {
     ml_counters cn;
     cn.n_points = n;
     cn.n_acc = scnt[0], cn.n_knn_fail = scnt[1], cn.n_plane_fail = scnt[2], cn.n_badmatch = scnt[3], cn.n_chi_rej = scnt[4];
-    cn.sum_chi = fsum[RR_NE + 0], cn.sum_chi2 = fsum[RR_NE + 1], cn.sum_res = 0.0, cn.sum_res2 = fsum[RR_NE + 2];
+    cn.sum_chi = fsum[NE + 0], cn.sum_chi2 = fsum[NE + 1], cn.sum_res = 0.0, cn.sum_res2 = fsum[NE + 2];
     out->cnt = cn;
-    out->st = *st;
     *ticket = 0u; // ready for the next scan
+  } else if (t >= NE + 1 && t < NE + 1 + (int)(sizeof(ScanState) / sizeof(int))) {
+    reinterpret_cast<int *>(&out->st)[t - NE - 1] = sst[t - NE - 1];
   }
   __syncthreads();
-  for (int idx = t; idx < ML_G * hx; idx += RR_BLOCK) {
+  for (int idx = t; idx < NG * hx; idx += BLOCK) {
     const int r = idx / hx, j = idx - r * hx;
     double s = 0.0;
 #pragma unroll
-    for (int l = 0; l < ML_G; l++)
-      s += G[r * ML_G + l] * sT[l * ML_MAX_HX + j];
+    for (int l = 0; l < NG; l++)
+      s += G[r * NG + l] * sT[l * ML_MAX_HX + j];
     GT[r * ML_MAX_HX + j] = s;
   }
   __syncthreads();
   // upper triangle computed once and mirrored: HtH is exactly symmetric. Staged in shared memory and written out in
-  // full 128-byte lines: `out` is pinned HOST memory (the result crosses PCIe as ~150 posted writes, no D2H copy node).
-  double *Hs = GT + ML_G * ML_MAX_HX; // [hx][hx] + [hx]
-  for (int idx = t; idx < hx * hx; idx += RR_BLOCK) {
+  // full 128-byte lines: `out` is pinned HOST memory (the result crosses PCIe as ~150 posted writes, no D2H copy node; the
+  // end of the kernel makes them visible to the host)
+  for (int idx = t; idx < hx * hx; idx += BLOCK) {
     const int a = idx / hx, b2 = idx - a * hx;
     if (a > b2)
       continue;
     double s = 0.0;
 #pragma unroll
-    for (int l = 0; l < ML_G; l++)
+    for (int l = 0; l < NG; l++)
       s += sT[l * ML_MAX_HX + a] * GT[l * ML_MAX_HX + b2];
     Hs[idx] = s;
     Hs[b2 * hx + a] = s;
   }
-  for (int a = t; a < hx; a += RR_BLOCK) {
+  for (int a = t; a < hx; a += BLOCK) {
     double s = 0.0;
 #pragma unroll
-    for (int l = 0; l < ML_G; l++)
+    for (int l = 0; l < NG; l++)
       s += sT[l * ML_MAX_HX + a] * bv[l];
     Hs[hx * hx + a] = s;
   }
   __syncthreads();
-  for (int idx = t; idx < hx * hx; idx += RR_BLOCK)
+  for (int idx = t; idx < hx * hx; idx += BLOCK)
     out->HtH[idx] = Hs[idx];
-  for (int a = t; a < hx; a += RR_BLOCK)
+  for (int a = t; a < hx; a += BLOCK)
     out->Htr[a] = Hs[hx * hx + a];
-  __threadfence_system();
+  tl_mark(tl, 7);
 }
 
 // parity export: h = T^T g for every point (n x hx)

@@ -610,8 +610,11 @@ template <int K>
 __global__ void __launch_bounds__(KNN_WARPS * 32)
     k_knn(const KnnUnit *__restrict__ units, ScanState *__restrict__ st, int ph, const float4 *__restrict__ q_sorted,
           const GridDesc *__restrict__ gd, const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
-          int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok, QSlot *__restrict__ qtab, int q_slots) {
+          int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok, QSlot *__restrict__ qtab, int q_slots,
+          const float4 *__restrict__ map_pts, float4 *__restrict__ nbr, unsigned long long *__restrict__ tl) {
+  tl_mark(tl, 0);
   pdl_enter();
+  tl_mark(tl, 1);
   const int lane = threadIdx.x & 31;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
@@ -626,11 +629,15 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     st->n_units[ph ^ 1] = 0;
     st->n_qsorted[ph ^ 1] = 0;
+    st->knn_next[ph ^ 1] = 0;
   }
   const GridDesc g = *gd;
   const int R = max(1, (int)ceil(sqrt((double)max_d2) * (1.0 + 1e-5) * g.inv_cell));
 
-  for (int u = warp; u < n_units; u += nwarps) {
+  // Units differ widely in cost (candidates in reach, depth of the walk): a warp's first unit is static (no atomic on the way
+  // in), every further one is taken from a ticket, so the kernel ends when the work does and not with the unluckiest stride.
+  // Results are per query and do not depend on who computes them.
+  for (int u = warp; u < n_units;) {
     const KnnUnit un = units[u];
     const bool active = lane < un.cnt;
     const float4 q = q_sorted[un.qbase + (active ? lane : 0)];
@@ -648,9 +655,31 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
           knn_d2[(size_t)qi * K + j] = in ? best.d[j] : INFINITY;
         }
       }
-      knn_ok[qi] = (found && !((double)best.d[K - 1] > (double)max_d2)) ? 1 : 0;
+      const bool ok = found && !((double)best.d[K - 1] > (double)max_d2);
+      knn_ok[qi] = ok ? 1 : 0;
+      // what KD_TREE::Nearest_Search hands to compute_plane: the neighbours' COORDINATES (ikd_Tree.cpp:383-387), in scan order
+      // (16 K contiguous bytes per query), so that the rows kernel reads them coalesced instead of gathering by index
+      // A query get_neighbors rejects is marked with a NaN first coordinate (the rows kernel needs no other flag).
+      if (nbr) {
+        if (ok) {
+          float4 p[K];
+#pragma unroll
+          for (int j = 0; j < K; j++)
+            p[j] = __ldg(&map_pts[best.i[j]]);
+#pragma unroll
+          for (int j = 0; j < K; j++)
+            nbr[(size_t)qi * K + j] = p[j];
+        } else {
+          nbr[(size_t)qi * K] = make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);
+        }
+      }
     }
+    int nxt = 0;
+    if (lane == 0)
+      nxt = nwarps + atomicAdd(&st->knn_next[ph], 1);
+    u = __shfl_sync(0xffffffffu, nxt, 0);
   }
+  tl_mark(tl, 2);
 }
 
 } // namespace ml

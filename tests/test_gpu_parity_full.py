@@ -102,10 +102,10 @@ def test_g64_mode_b_downsampled_scan(make_map, po, workload):
     assert np.array_equal(m.scan(2), in_range)                    # pointcloud_original keeps every in-range point
     out = m.scan(0)
     counts = check_voxel_contract(in_range, out, op.raw_downsample_size, po)
-    assert 0.2 * len(in_range) < len(out) < 0.9 * len(in_range) and counts.max() > 20
+    assert 0.05 * len(in_range) < len(out) < 0.5 * len(in_range) and counts.max() > 20
     assert np.array_equal(m.scan(1), po.transform_f32(out, w["T_LtoM"]))
     n, odd = against_reference_tree(po, m, w, op, HtH, Htr, cnt)
-    assert n == len(out) and cnt.n_acc > 0.4 * n
+    assert n == len(out) and cnt.n_acc > 0.2 * n  # the far half of the scan fails the condition gate (LidarHelper.cpp:310)
 
 
 @pytest.mark.parametrize("downsample", [True, False])
@@ -115,8 +115,12 @@ def test_kaist_option_set(make_map, po, workload, downsample):
     w = workload("G-vlp", downsample=downsample, options="kaist")
     op = w["op"]
     assert op.map_ngbr_max_d == 10.0 and op.raw_downsample_size == 2.0 and op.map_downsample_size == 0.5
+    # thin the map out ahead of the sensor (1 point in 40 beyond x = 3 m) so that part of the scan finds its 5th neighbour
+    # metres away: cube walks to the last level, and queries beyond the gate (k-th squared distance > 10, LidarHelper.cpp:284)
+    mp = w["map"]
+    mp = np.ascontiguousarray(mp[(mp[:, 0] < 3.0) | (np.arange(len(mp)) % 40 == 0)])
     m = make_map(max_scan_points=1 << 16, max_map_points=1 << 18)
-    m.Build(w["map"])
+    m.Build(mp)
     rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
     assert rc == 0
     in_range = po.range_filter(w["raw"], w["t_rel"], op.max_range, op.min_range)
@@ -127,21 +131,20 @@ def test_kaist_option_set(make_map, po, workload, downsample):
     else:
         assert np.array_equal(sc, in_range)
     assert np.array_equal(sm, po.transform_f32(sc, w["T_LtoM"]))
+    rows, h = m.point_rows()                                       # the export must follow the update directly
     idx, d2, ok = m.get_neighbors(op.map_ngbr_num, op.map_ngbr_max_d)
-    oidx, od2, ook = po.knn_brute(w["map"], sm, op.map_ngbr_num, np.float32(op.map_ngbr_max_d))
+    oidx, od2, ook = po.knn_brute(mp, sm, op.map_ngbr_num, np.float32(op.map_ngbr_max_d))
     assert np.array_equal(ok, ook) and np.array_equal(idx, oidx) and np.array_equal(d2, od2)
-    far = od2[:, -1] > 4.0                                        # queries whose 5th neighbour lies beyond 2 m: deep walks
-    assert far.sum() > 0
-    ref = po.scan_linsys(w["consts"], w["P"], w["map"], sc, sm)
-    rows, h = m.point_rows()
+    assert (od2[ook][:, -1] > 4.0).sum() > 20 and (~ook).sum() > 20   # 5th neighbour beyond 2 m; beyond the gate
+    ref = po.scan_linsys(w["consts"], w["P"], mp, sc, sm)
     assert np.array_equal(rows["status"], ref["rows"]["status"])
-    assert cnt.n_acc == ref["cnt"].n_acc > 0.2 * cnt.n_points
+    assert cnt.n_acc == ref["cnt"].n_acc > 0.1 * cnt.n_points
     both = rows["status"] == 0
     assert rel(h[both], ref["h"][both]) <= TOL
     assert rel(HtH, ref["HtH"]) <= TOL and rel(Htr, ref["Htr"]) <= TOL
     # the map side of the option set: register the scan at 0.5 m voxels, re-anchor with decay 30 s / 30 m
     n_live = m.register_scan(op)
-    ref_map = po.map_insert(w["map"], po.transform_f32(in_range, w["T_LtoM"]), True, op.map_downsample_size)
+    ref_map = po.map_insert(mp, po.transform_f32(in_range, w["T_LtoM"]), True, op.map_downsample_size)
     assert n_live == len(ref_map) and np.array_equal(m.flatten(), ref_map)
 
 
