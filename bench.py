@@ -440,7 +440,9 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        kern = {"knn": "k_knn<5>", "rows_reduce": "k_rows_reduce<5,3> (plane fit + residual/Jacobian + chi2 + reduction + finalize)",
+        fused = stage.get("upload_filter", 0.0) == 0.0 and stage.get("bin", 0.0) == 0.0
+        kern = {"knn": "k_front_knn<5> (range filter + transform + cell grouping + exact kNN, one persistent kernel)" if fused else "k_knn<5>",
+                "rows_reduce": "k_rows_reduce<5,3> (plane fit + residual/Jacobian + chi2 + reduction)",
                 "bin": "k_unit_alloc + k_query_scatter", "upload_filter": "k_range_filter_bin (range filter + transform + query binning)"}
         cand = {k_: stage.get(k_, 0.0) / args.steps for k_ in kern}
         dom = max(cand, key=cand.get)

@@ -8,6 +8,7 @@
 #include "scan.cuh"
 #include "sim.cuh"
 #include "update.cuh"
+#include "fused.cuh"
 #include "icp.cuh"
 
 #include <algorithm>
@@ -28,8 +29,6 @@ static std::string g_global_error;
 struct ml_handle {
   ml_config cfg;
   cudaStream_t stream = nullptr;
-  cudaStream_t stream2 = nullptr; // per-scan constants (H2D + k_prep_consts) run beside the scan pipeline
-  cudaEvent_t ev_prep = nullptr, ev_fork = nullptr;
   int n_sm = 148;
   int knn_calls = 0; // parity of the kNN work-list counters (ScanState::n_units)
   std::string err;
@@ -56,7 +55,8 @@ struct ml_handle {
   float4 *add_pts = nullptr;
   // scan
   float *d_raw = nullptr;
-  float *h_raw = nullptr; // pinned staging
+  float *h_raw = nullptr; // pinned staging (device-mapped: h_raw_dev)
+  const float *h_raw_dev = nullptr;
   float4 *scan_pts = nullptr, *scan_orig = nullptr, *scan_map = nullptr, *scan_tmp = nullptr;
   ScanState *d_st = nullptr;
   // decoupled look-back (prims.cuh), shared by every single-pass scan/compaction on the handle's stream: tile states
@@ -106,10 +106,24 @@ struct ml_handle {
   uint8_t *knn_ok = nullptr;
   float4 *nbr = nullptr; // k neighbour coordinates per query, scan order (written by k_knn, read by k_rows_reduce)
   RowConsts rowc;        // per-scan constants of the rows kernel (kernel parameter), filled by consts_async
-  DevConsts *d_consts = nullptr;
+  double *d_T = nullptr; // T on the device: parity export only (k_expand_h)
   PointRow *rows = nullptr;
-  RRParts *parts = nullptr;
-  unsigned int *ticket = nullptr;
+  RRPart *h_parts = nullptr; // pinned, device-mapped: one reduced system per CTA of the rows kernel (rows.cuh)
+  int rows_nb = 0;           // CTAs of the last rows launch
+  // fused front end + kNN (fused.cuh)
+  FusedCtl *d_fctl = nullptr;
+  uint32_t *units_tag = nullptr;
+  bool use_fused_knn = true; // MINS_FUSED_KNN=0: the separate kernels (A/B)
+  int fused_producers = 0;   // MINS_FUSED_PRODUCERS: 0 = by input kind
+  bool fused_attr[ML_MAX_K + 1][2] = {};
+  // host -> device pipeline of the fused path: the scan crosses PCIe in chunks on the copy engine (stream_copy), each followed
+  // by a stream memory operation that stamps chunk_flag[c]; the producers of the fused kernel wait per chunk
+  cudaStream_t stream_copy = nullptr;
+  uint32_t *chunk_flag = nullptr;
+  int dma_chunks = 0; // MINS_DMA_CHUNKS > 0: chunked copy-engine transfer instead of zero-copy reads by the kernel. Measured
+                      // (G-64, 2.1 MB): zero-copy 132 us e2e, 2 chunks 136, 4 chunks 152, 8 chunks 191 - every (copy, flag) pair
+                      // costs the copy engine ~5 us, more than the overlap wins; kept as an A/B switch
+  int (*write_value32)(cudaStream_t, unsigned long long, unsigned int, unsigned int) = nullptr; // cuStreamWriteValue32
   bool rows_exported = false;
   bool rows_attr[ML_MAX_K + 1][8] = {};
   // debug timeline (ml_debug_timeline): per-CTA %globaltimer stamps of the kNN and rows kernels
@@ -118,12 +132,10 @@ struct ml_handle {
   int rows_block = 0; // 0 = chosen per scan size; MINS_ROWS_BLOCK=512|1024 pins it (profiling) // cudaFuncAttributeMaxDynamicSharedMemorySize set for k_rows_reduce<K, NB> on THIS handle's device
   double *d_hrows = nullptr;            // parity export (ml_point_rows): n x total_hx, grown on demand, never on the per-scan path
   size_t hrows_cap = 0;
-  // pinned host mirrors
-  struct HostIn {
-    ml_scan_consts c;
-    double P[ML_MAX_HX * ML_MAX_HX];
-  } *h_in = nullptr;
-  LinsysOut *h_out = nullptr;
+  // per-scan constants, host side: the caller's struct, T (h = T^T g) and the result of the last rows launch
+  ml_scan_consts consts;
+  double hT[ML_G * ML_MAX_HX];
+  int last_n_scan = 0;
   bool rows_valid = false;
   int rows_k = 0;
   // timing
@@ -339,12 +351,15 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     h->zero_copy = !(e[0] == '0');
   if (const char *e = getenv("MINS_ROWS_BLOCK"))
     h->rows_block = atoi(e);
+  if (const char *e = getenv("MINS_FUSED_KNN"))
+    h->use_fused_knn = !(e[0] == '0');
+  if (const char *e = getenv("MINS_DMA_CHUNKS"))
+    h->dma_chunks = std::max(0, std::min(8, atoi(e)));
+  if (const char *e = getenv("MINS_FUSED_PRODUCERS"))
+    h->fused_producers = atoi(e);
   if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
     h->use_fused_front = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
-  CK(cudaEventCreateWithFlags(&h->ev_prep, cudaEventDisableTiming));
-  CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CK(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, cfg->device));
   if (h->n_sm > ML_NPART_MAX)
     h->n_sm = ML_NPART_MAX;
@@ -379,7 +394,14 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMemset(h->d_ints, 0, sizeof(int) * 16));
   CK(cudaMalloc(&h->add_pts, sizeof(float4) * cs));
   CK(cudaMalloc(&h->d_raw, sizeof(float) * 4 * cs));
-  CK(cudaMallocHost(&h->h_raw, sizeof(float) * 4 * cs));
+  CK(cudaHostAlloc(&h->h_raw, sizeof(float) * 4 * cs, cudaHostAllocMapped));
+  {
+    void *dp = nullptr;
+    if (cudaHostGetDevicePointer(&dp, h->h_raw, 0) == cudaSuccess)
+      h->h_raw_dev = (const float *)dp;
+    else
+      cudaGetLastError();
+  }
   CK(cudaMalloc(&h->scan_pts, sizeof(float4) * cs));
   CK(cudaMalloc(&h->scan_orig, sizeof(float4) * cs));
   CK(cudaMalloc(&h->scan_map, sizeof(float4) * cs));
@@ -420,13 +442,25 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->knn_d2, sizeof(float) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->knn_ok, cs));
   CK(cudaMalloc(&h->nbr, sizeof(float4) * cs * ML_MAX_K));
-  CK(cudaMalloc(&h->d_consts, sizeof(DevConsts)));
+  CK(cudaMalloc(&h->d_T, sizeof(double) * ML_G * ML_MAX_HX));
+  CK(cudaStreamCreateWithFlags(&h->stream_copy, cudaStreamNonBlocking));
+  CK(cudaMalloc(&h->chunk_flag, sizeof(uint32_t) * 16));
+  CK(cudaMemset(h->chunk_flag, 0, sizeof(uint32_t) * 16));
+  {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
+      h->write_value32 = reinterpret_cast<int (*)(cudaStream_t, unsigned long long, unsigned int, unsigned int)>(fn);
+    else
+      cudaGetLastError();
+  }
+  CK(cudaMalloc(&h->d_fctl, sizeof(FusedCtl)));
+  CK(cudaMemset(h->d_fctl, 0, sizeof(FusedCtl)));
+  CK(cudaMalloc(&h->units_tag, sizeof(uint32_t) * ((size_t)h->units_cap + 16384)));
+  CK(cudaMemset(h->units_tag, 0, sizeof(uint32_t) * ((size_t)h->units_cap + 16384)));
   CK(cudaMalloc(&h->rows, sizeof(PointRow) * cs));
-  CK(cudaMalloc(&h->parts, sizeof(RRParts)));
-  CK(cudaMalloc(&h->ticket, sizeof(unsigned int)));
-  CK(cudaMemset(h->ticket, 0, sizeof(unsigned int)));
-  CK(cudaMallocHost(&h->h_in, sizeof(*h->h_in)));
-  CK(cudaMallocHost(&h->h_out, sizeof(LinsysOut)));
+  CK(cudaHostAlloc(&h->h_parts, sizeof(RRPart) * ML_NPART_MAX, cudaHostAllocMapped));
+  memset(h->h_parts, 0, sizeof(RRPart) * ML_NPART_MAX);
   *out = h;
   return ML_OK;
 }
@@ -436,14 +470,17 @@ void ml_destroy(ml_handle *h) {
     return;
   use_device(h);
   cudaStreamSynchronize(h->stream);
-  cudaStreamSynchronize(h->stream2);
+  if (h->stream_copy) {
+    cudaStreamSynchronize(h->stream_copy);
+    cudaStreamDestroy(h->stream_copy);
+  }
   if (h->h_merge)
     cudaFreeHost(h->h_merge);
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_state, h->radix_ghist, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
-                 h->knn_idx, h->knn_d2, h->knn_ok, h->nbr, h->d_consts, h->rows, h->parts, h->ticket,
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->nbr, h->d_T, h->d_fctl, h->units_tag, h->chunk_flag, h->rows,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
                  h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->d_hrows, h->tl_rows, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
   for (void *p : dev)
@@ -451,17 +488,12 @@ void ml_destroy(ml_handle *h) {
       cudaFree(p);
   if (h->h_raw)
     cudaFreeHost(h->h_raw);
-  if (h->h_in)
-    cudaFreeHost(h->h_in);
-  if (h->h_out)
-    cudaFreeHost(h->h_out);
+  if (h->h_parts)
+    cudaFreeHost(h->h_parts);
   if (h->h_icp)
     cudaFreeHost(h->h_icp);
   for (auto &e : h->ev)
     cudaEventDestroy(e);
-  cudaEventDestroy(h->ev_prep);
-  cudaEventDestroy(h->ev_fork);
-  cudaStreamDestroy(h->stream2);
   cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -648,6 +680,41 @@ int ml_map_size(ml_handle *h, int *n) {
 }
 
 // ---------------------------------------------------------------------------------------------- scan
+// Where the kernels read the raw scan from. *over_pcie: the kernel itself pulls the bytes across the bus.
+//  * device (or managed) memory: used in place, no copy (e.g. the simulator's ray-caster, a device-side driver)
+//  * pinned, device-mapped host memory and the one-pass front end: the kernel reads the scan straight over PCIe (each point
+//    is read exactly once), so there is no separate DMA copy to wait for
+//  * pinned without a device mapping: DMA copy; pageable: the kernel reads the handle's own pinned staging buffer, which the
+//    host fills with one memcpy (no DMA node either: the copy engine's launch latency is longer than the memcpy)
+static int resolve_input(ml_handle *h, const float *xyz, int stride, int n, const float **raw_src, bool *over_pcie) {
+  const size_t bytes = sizeof(float) * (size_t)stride * (size_t)n;
+  cudaPointerAttributes at;
+  const bool known = cudaPointerGetAttributes(&at, xyz) == cudaSuccess;
+  cudaGetLastError();
+  const bool pinned = known && at.type == cudaMemoryTypeHost;
+  const bool on_device = known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+  *over_pcie = false;
+  if (on_device) {
+    *raw_src = xyz;
+  } else if (pinned && h->zero_copy && at.devicePointer && h->use_fused_front) {
+    *raw_src = (const float *)at.devicePointer;
+    *over_pcie = true;
+  } else if (!pinned && h->zero_copy && h->use_fused_front && h->h_raw_dev) {
+    memcpy(h->h_raw, xyz, bytes);
+    *raw_src = h->h_raw_dev;
+    *over_pcie = true;
+  } else {
+    const float *src = xyz;
+    if (!pinned) { // pageable host memory: stage through the handle's pinned buffer
+      memcpy(h->h_raw, xyz, bytes);
+      src = h->h_raw;
+    }
+    CK(cudaMemcpyAsync(h->d_raw, src, bytes, cudaMemcpyHostToDevice, h->stream));
+    *raw_src = h->d_raw;
+  }
+  return ML_OK;
+}
+
 // LiDARData ctor on the device. T_LtoM (may be NULL): when the map transform is already known the compaction pass writes
 // pointcloud_in_map as well (LidarHelper.cpp:192), saving one pass over the scan.
 // vg_leaf > 0: a voxel filter with this leaf follows at once (one-call path): the front end also prepares its grid (h->vg_ready)
@@ -672,30 +739,10 @@ static int scan_upload_async(ml_handle *h, const float *xyz, int stride, int n, 
     LAUNCH(k_scanstate_zero, 1, 1, h->d_st);
     return check_launch(h);
   }
-  const float *raw_src = h->d_raw;
-  {
-    const size_t bytes = sizeof(float) * (size_t)stride * (size_t)n;
-    cudaPointerAttributes at;
-    const bool known = cudaPointerGetAttributes(&at, xyz) == cudaSuccess;
-    cudaGetLastError();
-    const bool pinned = known && at.type == cudaMemoryTypeHost;
-    const bool on_device = known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
-    if (on_device) {
-      // scan already resident in HBM (e.g. produced by a device-side driver): used in place, no copy
-      raw_src = xyz;
-    } else if (pinned && h->zero_copy && at.devicePointer && h->use_fused_front) {
-      // pinned, device-mapped host memory and the one-pass front end: the kernel reads the scan straight over PCIe (each
-      // point is read exactly once), so there is no separate DMA copy to wait for
-      raw_src = (const float *)at.devicePointer;
-    } else {
-      const float *src = xyz;
-      if (!pinned) { // pageable host memory: stage through the handle's pinned buffer
-        memcpy(h->h_raw, xyz, bytes);
-        src = h->h_raw;
-      }
-      CK(cudaMemcpyAsync(h->d_raw, src, bytes, cudaMemcpyHostToDevice, h->stream));
-    }
-  }
+  const float *raw_src = nullptr;
+  bool over_pcie = false;
+  if (int rc_in = resolve_input(h, xyz, stride, n, &raw_src, &over_pcie))
+    return rc_in;
   const int tiles = cdiv(n, RF_TILE);
   float4 *in_map = T_LtoM ? h->scan_map : nullptr;
   if (h->use_fused_front) {
@@ -997,9 +1044,10 @@ template <int K, int NB, int BLOCK, bool EXPORT> static int launch_rows_cfg(ml_h
     CK(cudaFuncSetAttribute(k_rows_reduce<K, NB, BLOCK, EXPORT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
+  h->rows_nb = nb;
   launch_pdl(h, k_rows_reduce<K, NB, BLOCK, EXPORT>, nb, BLOCK, smem, h->rowc, (const ScanState *)h->d_st, h->n_raw,
-             (const float4 *)h->scan_pts, (const float4 *)h->nbr, (const DevConsts *)h->d_consts, rows_out, h->parts, h->ticket,
-             h->h_out /* pinned host memory, written by the last CTA */, h->tl_on ? h->tl_rows : (unsigned long long *)nullptr);
+             (const float4 *)h->scan_pts, (const float4 *)h->nbr, rows_out, h->h_parts /* pinned host memory */,
+             h->tl_on ? h->tl_rows : (unsigned long long *)nullptr);
   return ML_OK;
 }
 // Launch shape: one CTA per SM (fewer for small scans), and the block size whose warps walk the 32-point tiles in the most even
@@ -1031,7 +1079,7 @@ template <int K, int NB> static int launch_rows_nb(ml_handle *h, PointRow *rows_
 }
 // NB = 3-wide blocks of the folded Jacobian direction that can be non-zero: 3 without extrinsic calibration, 5 with
 template <int K> static int launch_rows(ml_handle *h, PointRow *rows_out) {
-  return h->h_in->c.calib_col >= 0 ? launch_rows_nb<K, 5>(h, rows_out) : launch_rows_nb<K, 3>(h, rows_out);
+  return h->consts.calib_col >= 0 ? launch_rows_nb<K, 5>(h, rows_out) : launch_rows_nb<K, 3>(h, rows_out);
 }
 static int launch_rows_k(ml_handle *h, int k, PointRow *rows_out) {
   switch (k) {
@@ -1046,12 +1094,7 @@ static int launch_rows_k(ml_handle *h, int k, PointRow *rows_out) {
   }
 }
 
-// join_consts: the rows kernel follows (ml_linsys / ml_scan_update). The constants' stream (k_prep_consts) is joined HERE, in
-// front of the kNN kernel, not in front of the rows kernel: an event wait between two kernels makes the second one wait for
-// the full completion of the first and pay a launch gap (3.5 us measured between the last kNN CTA and the first rows CTA);
-// with kNN -> rows adjacent in the stream the rows CTAs are launched programmatically behind the kNN's and stage their
-// constants while it drains. k_prep_consts (~20 us, one CTA) has run beside the front end and the binning by then.
-static int knn_async(ml_handle *h, int k, float max_d2, bool join_consts = false) {
+static int knn_async(ml_handle *h, int k, float max_d2) {
   if (k < 1 || k > ML_MAX_K)
     return fail(h, ML_ERR_ARG, "knn: k out of range [1, ML_MAX_K]");
   if (!h->map_init)
@@ -1059,11 +1102,8 @@ static int knn_async(ml_handle *h, int k, float max_d2, bool join_consts = false
   if (!h->have_T)
     return fail(h, ML_ERR_ARG, "knn: ml_scan_transform has not been called for this scan");
   const int n = h->n_raw;
-  if (n <= 0) {
-    if (join_consts)
-      CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
+  if (n <= 0)
     return ML_OK;
-  }
   const uint32_t mask = (uint32_t)h->q_slots - 1u;
   const int ph = h->knn_calls & 1;
   h->knn_calls++;
@@ -1074,8 +1114,6 @@ static int knn_async(ml_handle *h, int k, float max_d2, bool join_consts = false
   h->bin_done = false;
   LAUNCHP(k_unit_alloc, cdiv(h->q_slots, 256), 256, h->qtab, h->q_slots, h->d_st, ph, h->units, h->units_cap);
   LAUNCHP(k_query_scatter, cdiv(n, 256), 256, h->scan_map, h->d_st, h->qtab, h->q_slot, h->q_rank, h->q_sorted);
-  if (join_consts)
-    CK(cudaStreamWaitEvent(h->stream, h->ev_prep, 0));
   if (h->timing == 1)
     cudaEventRecord(h->ev[4], h->stream);
   switch (k) {
@@ -1182,49 +1220,165 @@ static void make_row_consts(const ml_scan_consts &c, RowConsts *r) {
   r->total_hx = c.total_hx;
 }
 
-// per-scan constants: H2D + k_prep_consts on the side stream, so they overlap the scan pipeline (filter, binning, kNN)
-static int consts_async(ml_handle *h, const ml_scan_consts *c, const double *P) {
+// T (ML_G x ML_MAX_HX, row-major): h = T^T g. Rows = the 15 folded pose-space directions (ML_G, common.cuh), columns = state
+// columns: the reference's dTdxI / dTdxA blocks at their map_hx columns (State.cpp:745-816, UpdaterLidar.cpp:343-347) and the
+// identity on the calibration columns (:349). Columns of different blocks may coincide (I and A clones overlap): added in order.
+static void build_T(const ml_scan_consts &c, double *T) {
+  memset(T, 0, sizeof(double) * ML_G * ML_MAX_HX);
+  for (int r = 0; r < 6; r++) // I rotation rows 0-2, I position rows 3-5
+    for (int b = 0; b < c.nI; b++)
+      for (int cc = 0; cc < c.dTdxI[b].width; cc++)
+        T[r * ML_MAX_HX + c.dTdxI[b].col + cc] += c.dTdxI[b].D[6 * r + cc];
+  for (int r = 3; r < 6; r++) // ... minus A position rows (g_A,pos = -g_I,pos)
+    for (int b = 0; b < c.nA; b++)
+      for (int cc = 0; cc < c.dTdxA[b].width; cc++)
+        T[r * ML_MAX_HX + c.dTdxA[b].col + cc] -= c.dTdxA[b].D[6 * r + cc];
+  for (int r = 6; r < 9; r++) // A rotation rows
+    for (int b = 0; b < c.nA; b++)
+      for (int cc = 0; cc < c.dTdxA[b].width; cc++)
+        T[r * ML_MAX_HX + c.dTdxA[b].col + cc] += c.dTdxA[b].D[6 * (r - 6) + cc];
+  if (c.calib_col >= 0)
+    for (int r = 9; r < ML_G; r++)
+      T[r * ML_MAX_HX + c.calib_col + (r - 9)] += 1.0;
+}
+
+// Per-scan constants, all on the host (~20 k multiply-adds; they are computed while the device runs the front end and the
+// kNN, so they cost the scan nothing): the folded rows-kernel parameter incl. Q = T P T^T (h^T P h = g^T Q g), and T for the
+// host tail. There is no constants kernel, no side stream and no event between the kNN and the rows kernel.
+static int consts_host(ml_handle *h, const ml_scan_consts *c, const double *P) {
   const int hx = c->total_hx;
-  h->h_in->c = *c;
-  memcpy(h->h_in->P, P, sizeof(double) * (size_t)hx * hx);
+  h->consts = *c;
+  build_T(*c, h->hT);
   make_row_consts(*c, &h->rowc);
-  // no fork event: every entry point that launches the rows kernel (the only reader of d_consts) synchronises the main
-  // stream before it returns, so d_consts is idle here; an event record here would also split the kernel chain
-  // no copy nodes: k_prep_consts reads the pinned staging block over PCIe (24 KB) and leaves c, T, Q in device memory
-  k_prep_consts<<<1, 1024, 0, h->stream2>>>(h->d_consts, &h->h_in->c, h->h_in->P);
-  h->launches++;
-  CK(cudaEventRecord(h->ev_prep, h->stream2));
+  const int NG = c->calib_col >= 0 ? ML_G : 9;
+  double TP[ML_G][ML_MAX_HX], Q[ML_G][ML_G];
+  int nz[ML_G][ML_MAX_HX], nnz[ML_G];
+  for (int r = 0; r < NG; r++) {
+    nnz[r] = 0;
+    for (int l = 0; l < hx; l++)
+      if (h->hT[r * ML_MAX_HX + l] != 0.0)
+        nz[r][nnz[r]++] = l;
+    for (int j = 0; j < hx; j++)
+      TP[r][j] = 0.0;
+    for (int q = 0; q < nnz[r]; q++) {
+      const int l = nz[r][q];
+      const double t = h->hT[r * ML_MAX_HX + l];
+      const double *Pl = P + (size_t)l * hx;
+      for (int j = 0; j < hx; j++)
+        TP[r][j] += t * Pl[j];
+    }
+  }
+  for (int r = 0; r < NG; r++)
+    for (int q = 0; q < NG; q++) {
+      double acc = 0.0;
+      for (int e = 0; e < nnz[q]; e++)
+        acc += TP[r][nz[q][e]] * h->hT[q * ML_MAX_HX + nz[q][e]];
+      Q[r][q] = acc;
+    }
+  for (int a = 0; a < NG; a++)
+    for (int b = 0; b < NG; b++)
+      h->rowc.Qu[a * NG + b] = b < a ? 0.0 : (b == a ? Q[a][a] : Q[a][b] + Q[b][a]);
   return ML_OK;
 }
 
-// everything after the transform; one synchronisation at the end. consts_async must have been issued.
-static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *HtH, double *Htr, ml_counters *cnt) {
-  const int hx = c->total_hx, k = c->map_ngbr_num;
-  int rc = knn_async(h, k, (float)c->map_ngbr_max_d, true);
-  if (rc) {
-    cudaStreamSynchronize(h->stream2);
-    return rc;
+// Host tail of the rows kernel: add the CTAs' reduced systems in CTA order (fixed: bit-reproducible), then the chain rule
+// HtH = T^T G T, Htr = T^T b (T is block sparse: zero entries are skipped), and the counters.
+static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
+  const ml_scan_consts &c = h->consts;
+  const int hx = c.total_hx, nb = h->rows_nb;
+  const int NG = c.calib_col >= 0 ? ML_G : 9, NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 3;
+  double sum[ML_NRED];
+  int cs[5] = {0, 0, 0, 0, 0};
+  for (int e = 0; e < NRED; e++)
+    sum[e] = 0.0;
+  for (int b = 0; b < nb; b++) {
+    const RRPart &p = h->h_parts[b];
+    for (int e = 0; e < NRED; e++)
+      sum[e] += p.v[e];
+    for (int q = 0; q < 5; q++)
+      cs[q] += p.c[q];
   }
-  rc = launch_rows_k(h, k, nullptr);
+  h->last_n_scan = h->h_parts[0].n_scan;
+  if (cnt) {
+    cnt->n_points = h->last_n_scan;
+    cnt->n_acc = cs[0], cnt->n_knn_fail = cs[1], cnt->n_plane_fail = cs[2], cnt->n_badmatch = cs[3], cnt->n_chi_rej = cs[4];
+    cnt->sum_chi = sum[NE + 0], cnt->sum_chi2 = sum[NE + 1], cnt->sum_res = 0.0, cnt->sum_res2 = sum[NE + 2];
+  }
+  if (HtH || Htr) {
+    double G[ML_G][ML_G], GT[ML_G][ML_MAX_HX];
+    {
+      int e = 0;
+      for (int a = 0; a < NG; a++)
+        for (int b = a; b < NG; b++, e++)
+          G[a][b] = G[b][a] = sum[e];
+    }
+    const double *T = h->hT;
+    for (int r = 0; r < NG; r++) {
+      for (int j = 0; j < hx; j++)
+        GT[r][j] = 0.0;
+      for (int l = 0; l < NG; l++) {
+        const double gv = G[r][l];
+        const double *Tl = T + l * ML_MAX_HX;
+        for (int j = 0; j < hx; j++)
+          GT[r][j] += gv * Tl[j];
+      }
+    }
+    if (HtH) {
+      for (int a = 0; a < hx; a++) {
+        double *Ha = HtH + (size_t)a * hx;
+        for (int b = a; b < hx; b++)
+          Ha[b] = 0.0;
+        for (int l = 0; l < NG; l++) {
+          const double t = T[l * ML_MAX_HX + a];
+          if (t == 0.0)
+            continue;
+          const double *Gl = GT[l];
+          for (int b = a; b < hx; b++)
+            Ha[b] += t * Gl[b];
+        }
+      }
+      for (int a = 0; a < hx; a++) // upper triangle computed once and mirrored: exactly symmetric
+        for (int b = 0; b < a; b++)
+          HtH[(size_t)a * hx + b] = HtH[(size_t)b * hx + a];
+    }
+    if (Htr)
+      for (int a = 0; a < hx; a++) {
+        double acc = 0.0;
+        for (int l = 0; l < NG; l++)
+          acc += T[l * ML_MAX_HX + a] * sum[NSYM + l];
+        Htr[a] = acc;
+      }
+  }
+  return cs[0] > 0 ? ML_OK : ML_SOFT_NO_ROWS;
+}
+
+// rows kernel + the wait + the host tail; the kNN results of the resident scan must be in flight on the stream
+static int rows_and_wait(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
+  const int k = h->consts.map_ngbr_num;
+  int rc = launch_rows_k(h, k, nullptr);
   if (rc)
     return rc;
   h->rows_exported = false;
   if (h->timing == 1)
     cudaEventRecord(h->ev[6], h->stream);
-  // no D2H copy: the kernel's last CTA wrote the result block straight into the pinned host mirror
+  // no D2H copy: every CTA wrote its reduced system straight into the pinned result area
   if (h->timing)
     cudaEventRecord(h->ev[8], h->stream);
   CK(cudaStreamSynchronize(h->stream));
   CK(cudaGetLastError());
   h->rows_valid = true;
   h->rows_k = k;
-  if (HtH)
-    memcpy(HtH, h->h_out->HtH, sizeof(double) * (size_t)hx * hx);
-  if (Htr)
-    memcpy(Htr, h->h_out->Htr, sizeof(double) * (size_t)hx);
-  if (cnt)
-    *cnt = h->h_out->cnt;
-  if (h->timing == 1) {
+  return rows_host_tail(h, HtH, Htr, cnt);
+}
+
+// everything after the transform; one synchronisation at the end. consts_host must have been called.
+static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *HtH, double *Htr, ml_counters *cnt) {
+  const int k = c->map_ngbr_num;
+  int rc = knn_async(h, k, (float)c->map_ngbr_max_d);
+  if (rc)
+    return rc;
+  rc = rows_and_wait(h, HtH, Htr, cnt);
+  if (h->timing == 1 && rc >= 0) {
     auto el = [&](int a, int b) {
       float ms = 0.f;
       if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
@@ -1239,7 +1393,7 @@ static int linsys_async_and_wait(ml_handle *h, const ml_scan_consts *c, double *
     h->last_ms[5] = ran ? el(5, 6) : 0.f;
     h->last_ms[6] = el(6, 8);
   }
-  return h->h_out->cnt.n_acc > 0 ? ML_OK : ML_SOFT_NO_ROWS;
+  return rc;
 }
 
 int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
@@ -1251,7 +1405,7 @@ int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *Ht
     return rc;
   if (h->timing)
     cudaEventRecord(h->ev[0], h->stream);
-  rc = consts_async(h, c, P);
+  rc = consts_host(h, c, P);
   if (rc)
     return rc;
   rc = linsys_async_and_wait(h, c, HtH, Htr, cnt);
@@ -1266,6 +1420,133 @@ int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *Ht
   return rc;
 }
 
+} // extern "C"
+
+// The fused front end + kNN of the un-down-sampled one-call path (fused.cuh): one launch.
+template <int K, bool VEC4>
+static int launch_front_knn(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2,
+                            int producers, uint32_t epoch, int tiles_per_chunk) {
+  bool &attr_set = h->fused_attr[K][VEC4 ? 1 : 0];
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(k_front_knn<K, VEC4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FK_SMEM));
+    attr_set = true;
+  }
+  const int grid = h->n_sm * 3;
+  launch_pdl(h, k_front_knn<K, VEC4>, grid, FK_BLOCK, FK_SMEM, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
+             h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, epoch, h->d_fctl, std::min(producers, grid),
+             (const GridDesc *)h->d_grid, h->q_sorted, h->units, h->units_tag, (const uint32_t *)h->cell_start,
+             (const float4 *)h->cell_pts, max_d2, (int32_t *)nullptr, (float *)nullptr, (uint8_t *)nullptr,
+             (const float4 *)h->map_pts[h->cur], h->nbr, (const uint32_t *)(tiles_per_chunk > 0 ? h->chunk_flag : nullptr), tiles_per_chunk,
+             h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
+  return check_launch(h);
+}
+template <int K>
+static int launch_front_knn_k(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2,
+                              int producers, uint32_t epoch, int tiles_per_chunk) {
+  const bool vec4 = stride == 4 && (((uintptr_t)raw_src) & 15u) == 0;
+  return vec4 ? launch_front_knn<K, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk)
+              : launch_front_knn<K, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+}
+__global__ void k_set_u32(uint32_t *p, uint32_t v) { *p = v; }
+static int scan_front_knn_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM,
+                                int k, float max_d2) {
+  if (n < 0 || (n > 0 && !xyz) || (stride != 3 && stride != 4))
+    return fail(h, ML_ERR_ARG, "ml_scan_update: bad argument (stride must be 3 or 4)");
+  if (n > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_scan_update: more points than max_scan_points");
+  drop_stale_bins(h);
+  h->n_raw = n;
+  h->rows_valid = false;
+  h->vg_ready = false;
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 4; c++)
+      h->T_LtoM.m[4 * r + c] = T_LtoM[4 * r + c];
+  h->have_T = true;
+  // Where the scan comes from decides how it reaches the kernel:
+  //  * device memory: read in place;
+  //  * host memory (pinned or pageable), dma_chunks > 0: the copy engine brings it across PCIe in chunks on its own stream
+  //    (pageable chunks pass through the handle's pinned staging buffer), a stream memory operation behind each chunk stamps its
+  //    flag, and the kernel - already running - hands each tile to its producer as soon as its chunk has landed: the transfer of
+  //    chunk c + 1 overlaps the grouping and the search of chunk c;
+  //  * MINS_DMA_CHUNKS=0: the kernel reads pinned, device-mapped memory itself (zero-copy), every tile at once.
+  const int ntiles = cdiv(n, RF_TILE);
+  const uint32_t epoch = lb_next_epoch(h);
+  const float *raw_src = nullptr;
+  int tiles_per_chunk = 0;
+  cudaPointerAttributes at;
+  const bool known = cudaPointerGetAttributes(&at, xyz) == cudaSuccess;
+  cudaGetLastError();
+  const bool on_device = known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+  const bool pinned = known && at.type == cudaMemoryTypeHost;
+  int rc_launch = ML_OK;
+  auto launch = [&](int producers) {
+    producers = std::max(1, std::min(h->fused_producers > 0 ? h->fused_producers : producers, ntiles));
+    switch (k) {
+    case 3: return launch_front_knn_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 4: return launch_front_knn_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 5: return launch_front_knn_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 6: return launch_front_knn_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 7: return launch_front_knn_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 8: return launch_front_knn_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    case 9: return launch_front_knn_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    default: return launch_front_knn_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+    }
+  };
+  if (on_device) {
+    raw_src = xyz;
+    return launch(ntiles);
+  }
+  if (h->dma_chunks == 0 && pinned && h->zero_copy && at.devicePointer) {
+    raw_src = (const float *)at.devicePointer;
+    return launch(ntiles);
+  }
+  if (h->dma_chunks == 0) { // whole-scan copy on the main stream, then the kernel
+    bool dummy;
+    if (int rc = resolve_input(h, xyz, stride, n, &raw_src, &dummy))
+      return rc;
+    return launch(ntiles);
+  }
+  // chunked DMA. Chunk = a whole number of tiles; the first chunk is on its way before the kernel is launched.
+  const int chunks = std::max(1, std::min(h->dma_chunks, ntiles));
+  tiles_per_chunk = cdiv(ntiles, chunks);
+  raw_src = h->d_raw;
+  const size_t pt_bytes = sizeof(float) * (size_t)stride;
+  auto copy_chunk = [&](int c) -> int {
+    const size_t i0 = (size_t)c * tiles_per_chunk * RF_TILE, i1 = std::min((size_t)n, i0 + (size_t)tiles_per_chunk * RF_TILE);
+    if (i0 >= i1)
+      return ML_OK;
+    const char *src = (const char *)xyz + i0 * pt_bytes;
+    if (!pinned) { // pageable: through the pinned staging buffer, chunk by chunk (the DMA of chunk c runs beside the memcpy of c + 1)
+      memcpy((char *)h->h_raw + i0 * pt_bytes, src, (i1 - i0) * pt_bytes);
+      src = (const char *)h->h_raw + i0 * pt_bytes;
+    }
+    CK(cudaMemcpyAsync((char *)h->d_raw + i0 * pt_bytes, src, (i1 - i0) * pt_bytes, cudaMemcpyHostToDevice, h->stream_copy));
+    if (h->write_value32) {
+      if (h->write_value32(h->stream_copy, (unsigned long long)(uintptr_t)(h->chunk_flag + c), epoch, 0) != 0)
+        return fail(h, ML_ERR_CUDA, "cuStreamWriteValue32 failed");
+    } else {
+      k_set_u32<<<1, 1, 0, h->stream_copy>>>(h->chunk_flag + c, epoch);
+    }
+    return ML_OK;
+  };
+  if (int rc = copy_chunk(0))
+    return rc;
+  rc_launch = launch(ntiles);
+  if (rc_launch)
+    return rc_launch;
+  for (int c = 1; c * tiles_per_chunk < ntiles; c++)
+    if (int rc = copy_chunk(c)) {
+      // the kernel is waiting for this chunk: let it run out (on whatever the buffer holds) before reporting the failure
+      for (int q = c; q * tiles_per_chunk < ntiles; q++)
+        k_set_u32<<<1, 1, 0, h->stream_copy>>>(h->chunk_flag + q, epoch);
+      cudaStreamSynchronize(h->stream);
+      return rc;
+    }
+  return ML_OK;
+}
+
+extern "C" {
+
 int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, float leaf,
                    const float T_LtoM[16], const ml_scan_consts *c, const double *P, double *HtH, double *Htr, ml_counters *cnt) {
   if (!h || !P || !T_LtoM)
@@ -1279,44 +1560,63 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
   if (h->timing)
     cudaEventRecord(h->ev[0], h->stream);
   const bool ds = leaf > 0.f;
+  auto el = [&](int a, int b) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
+      cudaGetLastError();
+      return 0.f;
+    }
+    return ms;
+  };
+  if (!ds && h->use_fused_knn && h->use_fused_front && n > 0) {
+    // two launches: front end + kNN (fused.cuh), rows + reduction (rows.cuh). The host folds the scan constants while the first
+    // one runs; nothing sits between the two kernels in the stream (programmatic dependent launch).
+    rc = scan_front_knn_async(h, xyz, stride, n, t_rel, rmin, rmax, T_LtoM, c->map_ngbr_num, (float)c->map_ngbr_max_d);
+    if (rc)
+      return rc;
+    rc = consts_host(h, c, P);
+    if (rc)
+      return rc;
+    if (h->timing == 1)
+      cudaEventRecord(h->ev[5], h->stream);
+    rc = rows_and_wait(h, HtH, Htr, cnt);
+    if (h->timing && rc >= 0) {
+      for (int q = 0; q < 7; q++)
+        h->last_ms[q] = 0.f;
+      if (h->timing == 1) {
+        h->last_ms[4] = el(0, 5); // front end + cell grouping + kNN: one kernel
+        h->last_ms[5] = el(5, 6);
+      }
+      h->last_ms[7] = el(0, 8);
+    }
+    return rc;
+  }
   // without down-sampling the compaction pass also writes pointcloud_in_map
   rc = scan_upload_async(h, xyz, stride, n, t_rel, rmin, rmax, ds ? nullptr : T_LtoM, ds ? leaf : 0.f);
   if (rc)
     return rc;
-  // the constants are enqueued after the scan so that the GPU already works while the host stages them
-  rc = consts_async(h, c, P);
+  // the constants are folded after the scan is enqueued, so that the GPU already works meanwhile
+  rc = consts_host(h, c, P);
   if (rc)
     return rc;
   if (h->timing == 1)
     cudaEventRecord(h->ev[1], h->stream);
   if (ds) {
     rc = scan_downsample_async(h, leaf, T_LtoM);
-    if (rc) {
-      cudaStreamSynchronize(h->stream2);
+    if (rc)
       return rc;
-    }
   }
   if (h->timing == 1)
     cudaEventRecord(h->ev[2], h->stream);
   if (ds && !h->bin_done) { // not fused (MINS_NO_FUSED_FRONT=1): separate transform, binning inside the kNN stage
     rc = scan_transform_async(h, T_LtoM);
-    if (rc) {
-      cudaStreamSynchronize(h->stream2);
+    if (rc)
       return rc;
-    }
   }
   if (h->timing == 1)
     cudaEventRecord(h->ev[9], h->stream);
   rc = linsys_async_and_wait(h, c, HtH, Htr, cnt);
   if (h->timing && rc >= 0) {
-    auto el = [&](int a, int b) {
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) {
-        cudaGetLastError();
-        return 0.f;
-      }
-      return ms;
-    };
     if (h->timing == 1) {
       h->last_ms[0] = el(0, 1);
       h->last_ms[1] = el(1, 2);
@@ -1337,8 +1637,8 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
   if (!h->rows_valid)
     return fail(h, ML_ERR_ARG, "ml_point_rows: no ml_linsys result for the current scan and map (the export must follow "
                                "ml_linsys / ml_scan_update directly)");
-  const int cnt = h->h_out->st.n_scan;
-  const int hx = h->h_in->c.total_hx;
+  const int cnt = h->last_n_scan;
+  const int hx = h->consts.total_hx;
   const int m = std::min(cap, cnt);
   if (n)
     *n = cnt;
@@ -1376,7 +1676,8 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
       CK(cudaMalloc(&h->d_hrows, sizeof(double) * need));
       h->hrows_cap = need;
     }
-    LAUNCH(k_expand_h, std::min(148 * 8, cdiv((long long)cnt * hx, 256)), 256, h->d_st, h->rows, h->d_consts, h->d_hrows);
+    CK(cudaMemcpyAsync(h->d_T, h->hT, sizeof(double) * ML_G * ML_MAX_HX, cudaMemcpyHostToDevice, h->stream));
+    LAUNCH(k_expand_h, std::min(148 * 8, cdiv((long long)cnt * hx, 256)), 256, h->d_st, h->rows, (const double *)h->d_T, hx, h->d_hrows);
     CK(cudaMemcpyAsync(h_rows, h->d_hrows, sizeof(double) * (size_t)m * hx, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
   }

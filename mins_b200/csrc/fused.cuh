@@ -1,0 +1,368 @@
+// One persistent kernel for the front of the un-down-sampled scan update: LiDARData's range filter (LidarTypes.cpp:36-55) as a
+// stable single-pass compaction, the fp32 transform into the map frame (LidarHelper.cpp:192), the grouping of the queries by grid
+// cell into warp units, and the exact k-NN (LidarHelper::get_neighbors / KD_TREE::Nearest_Search) of every unit.
+// Replaces k_range_filter_bin + k_unit_alloc + k_query_scatter + k_knn (4 launches, a 4 MB global hash table and two extra
+// passes over the scan) on the one-call path.
+//
+// Why one kernel: with the scan in pinned HOST memory the front end is a PCIe read (2.1 MB at ~47 GB/s = 45 us for a
+// 131 072-ray scan) and nothing downstream could start before its last byte had arrived. Here the first `producers` CTAs walk
+// the 2048-ray tiles IN ORDER (an atomic ticket), so the bytes of tile t arrive before those of tile t + producers; a finished
+// tile publishes its units at once and every other warp of the grid is a consumer that takes published units from a second
+// ticket and searches them while later tiles are still crossing the bus. A producer CTA turns consumer when the tiles run out.
+//
+// Producer, per tile (256 threads x 8 rays):
+//   load -> range test -> ballots -> decoupled look-back (prims.cuh) for the tile's offset in the compacted clouds -> write
+//   pointcloud / pointcloud_original / pointcloud_in_map in scan order -> group the tile's queries by grid cell in a
+//   SHARED-MEMORY hash table (warp-aggregated: one probe per distinct cell per warp) -> exclusive scan over the table slots ->
+//   reserve a range of the unit list (one global atomic per tile; the tile's range of the cell-ordered query array is its range
+//   of the compacted clouds) -> scatter queries, write unit records -> fence -> stamp the units' tags with the scan's epoch ->
+//   only then the three clouds (nobody waits for them) -> tiles_done++.
+//   A cell that spans two tiles becomes two units (+14 % units on the 64-beam scan at 2048-ray tiles): the result of a query does
+//   not depend on its unit.
+// Consumer, per warp: u = unit ticket; wait until tag[u] == epoch (or until all tiles are done and u is past the final count);
+//   cube walk of update.cuh (bit-identical arithmetic and order), outputs by original scan index.
+// Tags carry the epoch of the scan, so nothing is cleared between scans; the control block is reset by the last CTA to leave.
+#pragma once
+#include "update.cuh"
+
+namespace ml {
+
+struct FusedCtl {
+  // written by the producers (a few atomics per tile), read by waiting consumers
+  unsigned int tile_next;    // front tiles handed out
+  unsigned int tiles_done;   // front tiles whose units are published
+  unsigned int unit_reserve; // units reserved so far; final once tiles_done == ntiles
+  unsigned int pad0[29];
+  // written by the consumers (one atomic per unit): its own 128-byte line
+  unsigned int unit_next;    // unit tickets handed out
+  unsigned int ctas_out;     // CTAs that have left
+  unsigned int pad1[30];
+};
+
+constexpr int FK_BLOCK = RF_BLOCK;        // 256
+constexpr int FK_SLOTS = 2 * RF_TILE;     // 4096: shared-memory hash table, load factor <= 1/2
+constexpr size_t FK_SMEM = (size_t)FK_SLOTS * (sizeof(unsigned long long) + 2 * sizeof(uint32_t)); // 64 KB
+
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// the raw scan is read once and may have been written by the copy engine while this kernel was already running: L2 loads
+template <bool VEC4> __device__ __forceinline__ float4 load_raw_cg(const float *raw, int stride, int i) {
+  if (VEC4)
+    return __ldcg(reinterpret_cast<const float4 *>(raw) + i);
+  const float *p = raw + (size_t)i * stride;
+  return make_float4(__ldcg(p), __ldcg(p + 1), __ldcg(p + 2), 0.f);
+}
+
+template <int K, bool VEC4>
+__global__ void __launch_bounds__(FK_BLOCK, 3)
+    k_front_knn(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax, ScanState *__restrict__ st,
+                float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
+                unsigned long long *tile_state, uint32_t epoch, FusedCtl *ctl, int producers, const GridDesc *__restrict__ gd,
+                float4 *__restrict__ q_sorted, KnnUnit *__restrict__ units, uint32_t *__restrict__ units_tag,
+                const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
+                int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok,
+                const float4 *__restrict__ map_pts, float4 *__restrict__ nbr, const uint32_t *chunk_flag, int tiles_per_chunk,
+                unsigned long long *__restrict__ tl) {
+  extern __shared__ __align__(16) unsigned char fk_smem[];
+  unsigned long long *hkey = reinterpret_cast<unsigned long long *>(fk_smem); // [FK_SLOTS] 0 = empty
+  uint32_t *hcnt = reinterpret_cast<uint32_t *>(hkey + FK_SLOTS);             // [FK_SLOTS] queries of the cell in this tile
+  uint32_t *hpre = hcnt + FK_SLOTS;                                           // [FK_SLOTS] (query base) | (unit base) << 16
+  __shared__ uint32_t wsum[FK_BLOCK / 32];
+  __shared__ uint32_t s_tile, s_prefix, s_tq, s_gu, s_tu;
+  tl_mark(tl, 0);
+  pdl_enter();
+  tl_mark(tl, 1);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const uint32_t ntiles = (uint32_t)((n + RF_TILE - 1) / RF_TILE);
+  const GridDesc g = *gd;
+
+  // ------------------------------------------------------------------------------------------ producer
+  if ((int)blockIdx.x < producers) {
+    // a producer's first tile is its block index (no ticket round trip on the way in); the ticket hands out the rest
+    for (uint32_t tile = blockIdx.x;;) {
+      if (tile >= ntiles)
+        break;
+      // the scan may still be on its way: the copy engine brings it in chunks and stamps chunk_flag[c] with the scan's epoch
+      // behind each (stream order); a tile waits for its chunk only
+      if (chunk_flag) {
+        if (threadIdx.x == 0) {
+          const uint32_t *f = chunk_flag + tile / (uint32_t)tiles_per_chunk;
+          while (ld_acquire_u32(f) != epoch)
+            __nanosleep(200);
+        }
+        __syncthreads();
+      }
+      const int wbase = (int)tile * RF_TILE + wid * (RF_TILE / (FK_BLOCK / 32));
+      float4 pt[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const int i = wbase + r * 32 + lane;
+        pt[r] = i < n ? load_raw_cg<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      // clear the table while the loads are in flight
+      for (int s = threadIdx.x; s < FK_SLOTS; s += FK_BLOCK) {
+        hkey[s] = 0ull;
+        hcnt[s] = 0u;
+      }
+      uint32_t bal[8];
+      uint32_t cnt = 0;
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const int i = wbase + r * 32 + lane;
+        const bool k = i < n && range_keep(pt[r], rmin, rmax);
+        bal[r] = __ballot_sync(0xffffffffu, k);
+        cnt += __popc(bal[r]);
+      }
+      if (lane == 0)
+        wsum[wid] = cnt;
+      __syncthreads();
+      tl_mark(tl, 4); // loads landed, range test done
+      // warp 0: the tile's offset in the compacted clouds (decoupled look-back). The other warps go on to the hash fill, which
+      // needs no offset: the look-back's L2 round trips hide behind it.
+      if (wid == 0) {
+        uint32_t tot = lane < FK_BLOCK / 32 ? wsum[lane] : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+          tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
+        if (lane == 0) {
+          s_prefix = excl;
+          s_tq = tot;
+          if (tile == 0) {
+            st->n_raw = n;
+            st->vox_n = 0;
+            st->vox_passthrough = 0;
+          }
+          if (tile == ntiles - 1) {
+            st->n_orig = (int)(excl + tot);
+            st->n_scan = (int)(excl + tot);
+          }
+        }
+      }
+      // hash fill: cell of every kept query (its map-frame position is recomputed for the cloud stores below: cheaper than
+      // 24 more live registers), warp-aggregated insert; sr = slot | rank << 16
+      // In phases over the 8 rows, so that the long-latency steps of different rows overlap (a row at a time costs 8 dependent
+      // chains of match -> CAS -> atomicAdd -> shuffle: 6 us per tile measured): keys, peer sets, slot claims, counts, broadcast.
+      const uint32_t lt = (1u << lane) - 1u;
+      unsigned long long key[8];
+      uint32_t peers[8], sr[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const float4 qm = tf_apply(T, pt[r]);
+        const int lim = 1 << 19;
+        const int cx = max(-lim, min(lim, cell_coord((double)qm.x, g.ox, g.inv_cell)));
+        const int cy = max(-lim, min(lim, cell_coord((double)qm.y, g.oy, g.inv_cell)));
+        const int cz = max(-lim, min(lim, cell_coord((double)qm.z, g.oz, g.inv_cell)));
+        key[r] = cell_key(cx, cy, cz);
+      }
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const bool kept = (bal[r] >> lane) & 1u;
+        // rays the range gate dropped get a key of their own (0 is no cell key): they match nobody
+        peers[r] = __match_any_sync(0xffffffffu, kept ? key[r] : (unsigned long long)lane) & bal[r];
+      }
+#pragma unroll
+      for (int r = 0; r < 8; r++) { // leaders claim the slot of their cell
+        sr[r] = 0u;
+        const bool kept = (bal[r] >> lane) & 1u;
+        if (kept && lane == __ffs(peers[r]) - 1) {
+          uint32_t s = hash64(key[r]) & (FK_SLOTS - 1);
+          for (;;) {
+            const unsigned long long prev = atomicCAS(&hkey[s], 0ull, key[r]);
+            if (prev == 0ull || prev == key[r])
+              break;
+            s = (s + 1) & (FK_SLOTS - 1);
+          }
+          sr[r] = s;
+        }
+      }
+      uint32_t base[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) { // ... and reserve the ranks of all their peers with one atomicAdd
+        const bool kept = (bal[r] >> lane) & 1u;
+        base[r] = (kept && lane == __ffs(peers[r]) - 1) ? atomicAdd(&hcnt[sr[r]], (uint32_t)__popc(peers[r])) : 0u;
+      }
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const bool kept = (bal[r] >> lane) & 1u;
+        const int leader = kept ? __ffs(peers[r]) - 1 : lane;
+        const uint32_t s = __shfl_sync(0xffffffffu, sr[r], leader);
+        const uint32_t b = __shfl_sync(0xffffffffu, base[r], leader);
+        sr[r] = kept ? (s | ((b + (uint32_t)__popc(peers[r] & lt)) << 16)) : 0u;
+      }
+      __syncthreads();
+      tl_mark(tl, 5); // look-back done, hash filled
+      // exclusive scan over the slots: queries and units (ceil(cnt / 32)) of every occupied slot, 16 consecutive slots per thread
+      uint32_t my_gu = 0, my_tu = 0;
+      {
+        constexpr int SPT = FK_SLOTS / FK_BLOCK; // 16
+        uint32_t lq = 0, lu = 0;
+#pragma unroll
+        for (int j = 0; j < SPT; j++) {
+          const uint32_t c = hcnt[threadIdx.x * SPT + j];
+          lq += c;
+          lu += (c + 31u) >> 5;
+        }
+        // one block scan for both: the sums fit 16 bits each (<= 2048)
+        uint32_t tot2;
+        const uint32_t e2 = block_excl_scan<FK_BLOCK>(lq | (lu << 16), &tot2);
+        uint32_t rq = e2 & 0xffffu, ru = e2 >> 16;
+#pragma unroll
+        for (int j = 0; j < SPT; j++) {
+          const uint32_t c = hcnt[threadIdx.x * SPT + j];
+          hpre[threadIdx.x * SPT + j] = rq | (ru << 16);
+          rq += c;
+          ru += (c + 31u) >> 5;
+        }
+        if (threadIdx.x == 0) { // the round trip of the reservation hides behind the query scatter below (result used after it)
+          my_tu = tot2 >> 16;
+          my_gu = my_tu ? atomicAdd(&ctl->unit_reserve, my_tu) : 0u;
+        }
+      }
+      __syncthreads();
+      tl_mark(tl, 6); // slots scanned
+      // The tile's queries in cell order: its range of the cell-ordered array IS its range of the compacted clouds (same
+      // count, unique by the look-back), so only the unit list needs a reservation. One unit record per 32 queries of a slot.
+      const uint32_t gq = s_prefix;
+      uint32_t pos = gq;
+      for (int w = 0; w < wid; w++)
+        pos += wsum[w];
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        if ((bal[r] >> lane) & 1u) {
+          const uint32_t o = pos + __popc(bal[r] & lt);
+          const uint32_t s = sr[r] & 0xffffu, rank = sr[r] >> 16;
+          const float4 qm = tf_apply(T, pt[r]);
+          q_sorted[gq + (hpre[s] & 0xffffu) + rank] = make_float4(qm.x, qm.y, qm.z, __int_as_float((int)o)); // tagged with its scan index
+        }
+        pos += __popc(bal[r]);
+      }
+      if (threadIdx.x == 0)
+        s_gu = my_gu, s_tu = my_tu;
+      __syncthreads();
+      const uint32_t gu = s_gu, tu = s_tu;
+      for (int s = threadIdx.x; s < FK_SLOTS; s += FK_BLOCK) {
+        const uint32_t c = hcnt[s];
+        if (c) {
+          const uint32_t qb = gq + (hpre[s] & 0xffffu), ub = gu + (hpre[s] >> 16);
+          int cx, cy, cz;
+          cell_unkey(hkey[s], &cx, &cy, &cz);
+          for (uint32_t j = 0; j * 32u < c; j++) {
+            KnnUnit u;
+            u.qbase = (int)(qb + 32u * j);
+            u.cnt = (int)min(32u, c - 32u * j);
+            u.cx = cx, u.cy = cy, u.cz = cz;
+            units[ub + j] = u;
+          }
+        }
+      }
+      // publish: only the query and unit stores are outstanding at this fence (the clouds are written after it)
+      __threadfence();
+      __syncthreads();
+      tl_mark(tl, 7); // queries and unit records visible
+      for (uint32_t j = threadIdx.x; j < tu; j += FK_BLOCK)
+        units_tag[gu + j] = epoch;
+      // next tile's ticket; the thread that reserved the units (thread 0) also counts the tile as done: its fence orders the
+      // reservation before the count, which is all a leaving consumer relies on (unit_reserve final once tiles_done == ntiles)
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(&ctl->tiles_done, 1u);
+        s_tile = (uint32_t)producers + atomicAdd(&ctl->tile_next, 1u);
+      }
+      // the clouds in scan order: pointcloud, pointcloud_original, pointcloud_in_map (nobody in this kernel reads them)
+      pos = gq;
+      for (int w = 0; w < wid; w++)
+        pos += wsum[w];
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        if ((bal[r] >> lane) & 1u) {
+          const uint32_t o = pos + __popc(bal[r] & lt);
+          const float4 q = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
+          cloud[o] = q;
+          orig[o] = q;
+          in_map[o] = tf_apply(T, q);
+        }
+        pos += __popc(bal[r]);
+      }
+      __syncthreads(); // the ticket is in; this tile's shared state is dead
+      tile = s_tile;
+    }
+  }
+  tl_mark(tl, 2);
+
+  // ------------------------------------------------------------------------------------------ consumer
+  const int R = max(1, (int)ceil(sqrt((double)max_d2) * (1.0 + 1e-5) * g.inv_cell));
+  for (;;) {
+    // A ticket is taken only when an unclaimed unit has been reserved (two relaxed loads, backing off up to 2 us while the
+    // producers are still at work): thousands of warps spinning on tags and tickets cost the producers their L2 round trips
+    // and their issue slots (a tile took 27 us instead of 8 us with every idle warp polling at 64 ns).
+    uint32_t u = 0;
+    bool have = false;
+    if (lane == 0) {
+      unsigned ns = 128;
+      for (;;) {
+        const uint32_t res = ld_relaxed_u32(&ctl->unit_reserve), nxt = ld_relaxed_u32(&ctl->unit_next);
+        if (nxt < res) {
+          u = atomicAdd(&ctl->unit_next, 1u);
+          // wait for this unit to be published (it has been reserved, or will be within a tile's time); leave when every tile
+          // is done and the ticket lies past the final count
+          for (;;) {
+            if (ld_acquire_u32(&units_tag[u]) == epoch) {
+              have = true;
+              break;
+            }
+            // every tile done: the reservation count is final; a ticket below it WILL be published, one past it never
+            if (ld_acquire_u32(&ctl->tiles_done) == ntiles && u >= ld_acquire_u32(&ctl->unit_reserve))
+              break;
+            __nanosleep(256);
+          }
+          break;
+        }
+        if (ld_acquire_u32(&ctl->tiles_done) == ntiles && ld_relaxed_u32(&ctl->unit_next) >= ld_acquire_u32(&ctl->unit_reserve))
+          break; // everything has been published and claimed
+        __nanosleep(ns);
+        ns = min(ns * 2u, 2048u);
+      }
+    }
+    u = __shfl_sync(0xffffffffu, u, 0);
+    have = __shfl_sync(0xffffffffu, (int)have, 0) != 0;
+    __syncwarp();
+    if (!have)
+      break;
+    // the unit record and its queries were written by another SM during this kernel: read them from L2 (an L1 line fetched for
+    // an earlier unit may hold the bytes of this one from before they were written)
+    KnnUnit un;
+    {
+      const int *up = reinterpret_cast<const int *>(units + u);
+      un.qbase = __ldcg(up), un.cnt = __ldcg(up + 1), un.cx = __ldcg(up + 2), un.cy = __ldcg(up + 3), un.cz = __ldcg(up + 4);
+    }
+    const bool active = lane < un.cnt;
+    const float4 q = __ldcg(&q_sorted[un.qbase + (active ? lane : 0)]);
+    TopK<K> best;
+    knn_walk<K>(un, q, active, g, R, cell_start, cell_pts, best);
+    if (active)
+      knn_emit<K>(best, __float_as_int(q.w), max_d2, knn_idx, knn_d2, knn_ok, map_pts, nbr);
+  }
+  tl_mark(tl, 3);
+  // the last CTA to leave resets the control block for the next scan (every ticket has been taken by then)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl->ctas_out, 1u) == gridDim.x - 1u) {
+      ctl->tile_next = 0u, ctl->tiles_done = 0u, ctl->unit_reserve = 0u, ctl->unit_next = 0u;
+      __threadfence();
+      ctl->ctas_out = 0u;
+    }
+  }
+}
+
+} // namespace ml

@@ -88,94 +88,6 @@ __device__ __forceinline__ void sym3_eig_minmax(double a00, double a01, double a
   *lmin = q - p * fma(1.7320508075688772, sn, c);
 }
 
-// T (18 x hx) and Q = T P T^T from the scan constants. One block of 1024; T and T P staged in shared memory, P read
-// coalesced (thread index runs along P's rows).
-// `c_in` and `P` may live in pinned HOST memory (the library's staging block): the kernel pulls the ~24 KB over PCIe itself, so
-// the side stream carries no copy nodes at all.
-__global__ void __launch_bounds__(1024) k_prep_consts(DevConsts *dc, const ml_scan_consts *__restrict__ c_in, const double *__restrict__ P) {
-  __shared__ double sT[ML_G * ML_MAX_HX];
-  __shared__ double sTP[ML_G * ML_MAX_HX];
-  __shared__ double sP[ML_MAX_HX * ML_MAX_HX]; // 32 KB: P staged with every load in flight at once (one DRAM round trip)
-  const int hx = c_in->total_hx;
-  for (int e = threadIdx.x; e < hx * hx; e += blockDim.x)
-    sP[e] = __ldg(&P[e]);
-  {
-    const int nw = (int)(sizeof(ml_scan_consts) / sizeof(int));
-    const int *src = reinterpret_cast<const int *>(c_in);
-    int *dst = reinterpret_cast<int *>(&dc->c);
-    for (int e = threadIdx.x; e < nw; e += blockDim.x)
-      dst[e] = __ldg(&src[e]);
-  }
-  __syncthreads(); // dc->c is complete and visible to the whole CTA from here on
-  const ml_scan_consts &c = dc->c;
-  for (int e = threadIdx.x; e < ML_G * ML_MAX_HX; e += blockDim.x)
-    sT[e] = 0.0;
-  __syncthreads();
-  // columns of different blocks may coincide (I and A clones overlap): one thread per row adds its blocks in order
-  if (threadIdx.x < ML_G) {
-    const int r = threadIdx.x;
-    double *Tr = sT + r * ML_MAX_HX;
-    if (r < 6) { // I rotation rows 0-2, I position rows 3-5
-      for (int b = 0; b < c.nI; b++)
-        for (int cc = 0; cc < c.dTdxI[b].width; cc++)
-          Tr[c.dTdxI[b].col + cc] += c.dTdxI[b].D[6 * r + cc];
-    }
-    if (r >= 3 && r < 6) { // ... minus A position rows (g_A,pos = -g_I,pos)
-      for (int b = 0; b < c.nA; b++)
-        for (int cc = 0; cc < c.dTdxA[b].width; cc++)
-          Tr[c.dTdxA[b].col + cc] -= c.dTdxA[b].D[6 * r + cc];
-    } else if (r >= 6 && r < 9) { // A rotation rows
-      for (int b = 0; b < c.nA; b++)
-        for (int cc = 0; cc < c.dTdxA[b].width; cc++)
-          Tr[c.dTdxA[b].col + cc] += c.dTdxA[b].D[6 * (r - 6) + cc];
-    } else if (r >= 9 && c.calib_col >= 0) {
-      Tr[c.calib_col + (r - 9)] += 1.0;
-    }
-  }
-  __syncthreads();
-  for (int e = threadIdx.x; e < ML_G * ML_MAX_HX; e += blockDim.x)
-    dc->T[e] = sT[e];
-  for (int e = threadIdx.x; e < ML_G * hx; e += blockDim.x) {
-    const int r = e / hx, j = e - r * hx;
-    double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    int l = 0;
-    for (; l + 4 <= hx; l += 4) {
-      s0 += sT[r * ML_MAX_HX + l] * sP[l * hx + j];
-      s1 += sT[r * ML_MAX_HX + l + 1] * sP[(l + 1) * hx + j];
-      s2 += sT[r * ML_MAX_HX + l + 2] * sP[(l + 2) * hx + j];
-      s3 += sT[r * ML_MAX_HX + l + 3] * sP[(l + 3) * hx + j];
-    }
-    for (; l < hx; l++)
-      s0 += sT[r * ML_MAX_HX + l] * sP[l * hx + j];
-    sTP[r * ML_MAX_HX + j] = (s0 + s1) + (s2 + s3);
-  }
-  __syncthreads();
-  for (int e = threadIdx.x; e < ML_G * ML_G; e += blockDim.x) {
-    const int r = e / ML_G, q = e - r * ML_G;
-    double s0 = 0, s1 = 0;
-    int l = 0;
-    for (; l + 2 <= hx; l += 2) {
-      s0 += sTP[r * ML_MAX_HX + l] * sT[q * ML_MAX_HX + l];
-      s1 += sTP[r * ML_MAX_HX + l + 1] * sT[q * ML_MAX_HX + l + 1];
-    }
-    for (; l < hx; l++)
-      s0 += sTP[r * ML_MAX_HX + l] * sT[q * ML_MAX_HX + l];
-    dc->Q[e] = s0 + s1;
-  }
-  __syncthreads();
-  __threadfence_block();
-  // packed upper triangle, off-diagonals doubled, for the per-point quadratic form g^T Q g
-  for (int e = threadIdx.x; e < ML_GSYM; e += blockDim.x) {
-    int r = 0, rem = e;
-    while (rem >= ML_G - r) {
-      rem -= ML_G - r;
-      r++;
-    }
-    const int q = r + rem;
-    dc->Qu[e] = (q == r) ? dc->Q[r * ML_G + r] : dc->Q[r * ML_G + q] + dc->Q[q * ML_G + r];
-  }
-}
-
 // ------------------------------------------------------------------------------------------------
 // Per-scan constants of the point loop in the form the kernel consumes them, derived on the host from ml_scan_consts
 // (make_row_consts, api.cu) and passed BY VALUE as a __grid_constant__ kernel parameter: parameters live in the constant
@@ -199,6 +111,9 @@ struct RowConsts {
   double chi2_thr;     // chi2_mult * quantile(chi_squared(K - 2), 0.95)
   int intr;            // !at_clone_m || !at_clone_a (UpdaterLidar.cpp:332)
   int total_hx;
+  // Q = T P T^T restricted to the 3 NB directions that can be non-zero, upper triangle by rows with row stride 3 NB and the
+  // off-diagonal entries doubled: h^T P h = g^T Q g = sum_a g_a sum_{b >= a} Qu[a][b] g_b (host: make_row_consts)
+  double Qu[ML_G * ML_G];
 };
 
 // One scan point: k neighbour coordinates -> plane -> gates -> g (UN-whitened, 3 NB numbers), weights, chi2.
@@ -218,8 +133,8 @@ struct RowOut {
   double n[3], d;
 };
 template <int K, int NB>
-__device__ __forceinline__ int point_row(const RowConsts &rc, const double *__restrict__ sQ, const float4 pl4,
-                                         const float4 (&nb)[K], double *__restrict__ g, RowOut &o) {
+__device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, const float4 (&nb)[K], double *__restrict__ g,
+                                         RowOut &o) {
   // ---- neighbours: Gram matrix, column sums, mean range (LidarHelper.cpp:293-302) ----
   float px[K], py[K], pz[K];
   double g00 = 0, g01 = 0, g02 = 0, g11 = 0, g12 = 0, g22 = 0, sx = 0, sy = 0, sz = 0, dsum = 0;
@@ -345,15 +260,14 @@ __device__ __forceinline__ int point_row(const RowConsts &rc, const double *__re
   const double e5 = res5 * ir;
   const double vr = e5 * wv;
   const double rss = fma(rss_nb * im, im, e5 * e5 * wv);
-  // ---- s = h^T P h = g^T Q g / raw_n^2: sQ = upper triangle of Q by rows with the off-diagonal entries doubled, row a at
-  //      sQ[a * 3 NB ...] (full row stride: no index arithmetic) ----
+  // ---- s = h^T P h = g^T Q g / raw_n^2 (rc.Qu: kernel parameter = constant-bank operands of the FMAs) ----
   double s = 0.0;
 #pragma unroll
   for (int a = 0; a < 3 * NB; a++) {
     double acc = 0.0;
 #pragma unroll
     for (int b = a; b < 3 * NB; b++)
-      acc = fma(sQ[a * (3 * NB) + b], g[b], acc);
+      acc = fma(rc.Qu[a * (3 * NB) + b], g[b], acc);
     s = fma(g[a], acc, s);
   }
   s *= ir * ir;
@@ -387,9 +301,14 @@ constexpr int RR_BLOCK = 512, RR_BLOCK_MID = 896, RR_BLOCK_BIG = 1024; // 16, 28
 constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diagonal blocks)
 // reduced entries for NB block rows: upper triangle of G (NG (NG + 1) / 2), b (NG), sum_chi, sum_chi2, sum_res2
 #define ML_NRED (ML_GSYM + ML_G + 3)
-struct RRParts {
-  double v[ML_NRED][ML_NPART_MAX]; // entry-major: the final pass reads an entry's CTA partials as one contiguous run
-  int c[5][ML_NPART_MAX];
+// What one CTA returns: its reduced system in the folded pose space (G = sum W g g^T upper triangle by rows, b = sum g V),
+// the chi2 statistics and the status counters. Lives in PINNED HOST memory: the CTA's last act is ~0.5 KB of posted PCIe
+// writes; no ticket, no fence, no serial tail on the device. The library's host tail (rows_host_tail, api.cu) adds the
+// blocks in CTA order - a fixed order, so the result is bit-reproducible - and applies the chain rule HtH = T^T G T.
+struct RRPart {
+  double v[ML_NRED];
+  int c[5];
+  int n_scan; // written by CTA 0: the device-side size of the scan
 };
 // per-warp slab: g rows (odd stride: conflict-free stores) | W | V | running sums (one slot per lane) | statistics
 template <int NB> struct RRLayout {
@@ -397,32 +316,38 @@ template <int NB> struct RRLayout {
   static constexpr int NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 3;
   static constexpr int ROW = NG + 2;
   static constexpr int SLAB = 32 * ROW + 32 + 32 + 32 * RR_RACC + 8; // + chi, chi^2, rss | 5 status counters (as int)
-  static constexpr int TAIL = 256 + NG * NG + 32 + NG * ML_MAX_HX + ML_MAX_HX * ML_MAX_HX + ML_MAX_HX; // last CTA's scratch
-  static constexpr int FIXED = NG * NG + NG * ML_MAX_HX + 16;                                          // Q | T | scan state
-  static constexpr size_t smem(int warps) {
-    return sizeof(double) * (size_t)((warps * SLAB > TAIL ? warps * SLAB : TAIL) + FIXED);
-  }
+  static constexpr size_t smem(int warps) { return sizeof(double) * (size_t)(warps * SLAB); }
 };
 
 template <int NB> __device__ __forceinline__ int rr_role_of(int bi, int bj) { return bi * NB - (bi * (bi - 1)) / 2 + (bj - bi); }
 
+// ------------------------------------------------------------------------------------------------
+// Fused rows + reduction (one launch per scan). Warp-autonomous: no CTA-wide barrier in the main loop.
+//  * the scan is cut into tiles of 32 points; round r covers the tiles [r nb, (r + 1) nb) (nb = CTAs), one tile per CTA, rotated
+//    by r; warp w of a CTA walks the rounds w, w + WARPS, ... The host picks the block size so that the rounds per warp are
+//    whole or nearly so (launch_rows_nb).
+//  * phase 1 (32 lanes): lane computes point_row of its point from the k neighbour coordinates the kNN kernel left in `nbr`
+//    (coalesced: 16 k bytes per point, scan order) and leaves g (3 NB numbers, un-whitened), W, V in the warp's shared-memory
+//    slab (never in HBM unless the parity export is requested); chi2 statistics by a fixed shuffle tree.
+//  * phase 2: G = sum W g g^T is cut into 3x3 blocks; with NB = 3 (no calibration) or 5 block rows there are
+//    NB(NB+1)/2 = 6 or 15 upper-triangle blocks ("roles"). The 32 lanes are split into 5 (or 2) groups of roles; group j
+//    adds the points p = j, j + groups, ... of the tile, so one tile costs 7 (or 16) iterations of 7 shared loads and 9 to 12
+//    FMAs instead of 32; diagonal blocks also carry b = sum g V. Running sums live in the warp's slab, one slot per lane.
+//  * end: one barrier, CTA partial = sum over its warps and groups in fixed order -> this CTA's RRPart in pinned host memory.
+//    Every sum has a fixed order for a given scan size and launch shape: bit-reproducible.
 // EXPORT: also write the per-point rows (parity export, ml_point_rows); the timed instantiation carries none of that state.
+// ------------------------------------------------------------------------------------------------
 template <int K, int NB, int BLOCK, bool EXPORT>
 __global__ void __launch_bounds__(BLOCK, 1)
     k_rows_reduce(const __grid_constant__ RowConsts rc, const ScanState *__restrict__ st, int n_ub, const float4 *__restrict__ scan_L,
-                  const float4 *__restrict__ nbr, const DevConsts *__restrict__ dc, PointRow *__restrict__ rows_out,
-                  RRParts *__restrict__ parts, unsigned int *__restrict__ ticket, LinsysOut *__restrict__ out,
+                  const float4 *__restrict__ nbr, PointRow *__restrict__ rows_out, RRPart *__restrict__ parts /* pinned host */,
                   unsigned long long *__restrict__ tl /* debug timeline (ml_debug_timeline) or NULL */) {
   using LY = RRLayout<NB>;
   tl_mark(tl, 0);
   constexpr int NG = LY::NG, ROW = LY::ROW, SLAB = LY::SLAB, WARPS = BLOCK / 32, NSYM = LY::NSYM, NE = LY::NE, NRED = LY::NRED;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double *slabs = reinterpret_cast<double *>(smem_raw);
-  double *sQ = slabs + (WARPS * SLAB > LY::TAIL ? WARPS * SLAB : LY::TAIL); // [NG][NG], upper triangle used
-  double *sT = sQ + NG * NG;                                                 // [NG][ML_MAX_HX]: rows of T (for the last CTA)
-  int *sst = reinterpret_cast<int *>(sT + NG * ML_MAX_HX);                   // ScanState
   __shared__ int scnt[5];
-  __shared__ unsigned int s_last;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
   const int nb = gridDim.x;
   // Tile -> warp: round r = wid, wid + WARPS, ... covers the nb tiles [r nb, (r + 1) nb); inside a round the CTAs are rotated
@@ -430,23 +355,9 @@ __global__ void __launch_bounds__(BLOCK, 1)
   // azimuths: 32 consecutive points are the lower or the upper half of a 64-beam column) and a plain stride nb gave the even
   // CTAs all the ground returns and the odd ones the sky: 11 us against 4.6 us of tile loop on neighbouring SMs.
   const auto tile_of = [&](int r) { return r * nb + (((int)blockIdx.x + nb - r % nb) % nb); };
-  // Per-scan constants first: Q, T (k_prep_consts on the side stream, joined by an event BEFORE this launch) and the scan state
-  // (front end, two kernels back) are complete whenever this kernel runs at all, so they are staged before the programmatic
-  // dependency on the kNN kernel is waited for - behind its tail instead of on the critical path.
   pdl_launch();
-  {
-    // upper triangle of Q (leading NG x NG block) with the off-diagonal entries doubled
-    for (int e = t; e < NG * NG; e += BLOCK) {
-      const int a = e / NG, b = e - a * NG;
-      sQ[e] = b < a ? 0.0 : (b == a ? dc->Q[a * ML_G + a] : dc->Q[a * ML_G + b] + dc->Q[b * ML_G + a]);
-    }
-    for (int e = t; e < NG * ML_MAX_HX; e += BLOCK)
-      sT[e] = dc->T[e];
-    if (t < (int)(sizeof(ScanState) / sizeof(int)))
-      sst[t] = reinterpret_cast<const int *>(st)[t];
-    if (t < 5)
-      scnt[t] = 0;
-  }
+  if (t < 5)
+    scnt[t] = 0;
   double *sg = slabs + (size_t)wid * SLAB; // [32][ROW]
   double *sw = sg + 32 * ROW;              // [32]
   double *sv = sw + 32;                    // [32]
@@ -457,8 +368,8 @@ __global__ void __launch_bounds__(BLOCK, 1)
     sacc[e] = 0.0;
   pdl_wait();
   tl_mark(tl, 1);
-  // the inputs of this warp's first tile are requested before the CTA barrier (n_ub = host-side bound of the scan size; what
-  // lies past the device-side count is stale but readable, and discarded below)
+  // the inputs of this warp's first tile and the scan size are requested together (n_ub = host-side bound of the scan size;
+  // what lies past the device-side count is stale but readable, and discarded below)
   float4 nb0[K], pl0;
   {
     const int i0 = (tile_of(wid) << 5) + lane;
@@ -468,10 +379,10 @@ __global__ void __launch_bounds__(BLOCK, 1)
       nb0[j] = pre ? __ldg(&nbr[(size_t)i0 * K + j]) : make_float4(0.f, 0.f, 0.f, 0.f);
     pl0 = pre ? __ldg(&scan_L[i0]) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  const int n = st->n_scan;
+  const int ntiles = (n + 31) >> 5;
   __syncthreads();
   tl_mark(tl, 2);
-  const int n = reinterpret_cast<const ScanState *>(sst)->n_scan;
-  const int ntiles = (n + 31) >> 5;
   // phase-2 role of this lane: group of points, block (bi, bj), bi <= bj
   constexpr int ROLES = NB * (NB + 1) / 2;
   constexpr int GROUPS = 32 / ROLES;
@@ -498,7 +409,7 @@ __global__ void __launch_bounds__(BLOCK, 1)
       g[a] = 0.0;
     // the kNN kernel marks a query get_neighbors rejects (LidarHelper.cpp:280-285) with a NaN first coordinate
     if (i < n && nb0[0].x == nb0[0].x)
-      status = point_row<K, NB>(rc, sQ, pl0, nb0, g, ro);
+      status = point_row<K, NB>(rc, pl0, nb0, g, ro);
     const bool okp = status == 0;
     if (EXPORT && i < n) { // parity export only: whitened g like the reference's H row
       PointRow pr;
@@ -557,16 +468,16 @@ __global__ void __launch_bounds__(BLOCK, 1)
       const int grp = lane / ROLES, role = lane - grp * ROLES;
       int bi = 0, bj = 0;
       {
-        int r = 0, rem = role;
+        int rr = 0, rem = role;
 #pragma unroll
         for (int q = 0; q < NB; q++) {
-          if (rem >= NB - r) {
-            rem -= NB - r;
-            r++;
+          if (rem >= NB - rr) {
+            rem -= NB - rr;
+            rr++;
           }
         }
-        bi = r;
-        bj = r + rem;
+        bi = rr;
+        bj = rr + rem;
       }
       double a9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       double b3[3] = {0, 0, 0};
@@ -601,7 +512,8 @@ __global__ void __launch_bounds__(BLOCK, 1)
   __syncthreads();
   tl_mark(tl, 4);
   // ---- CTA partial: sum over the warps in warp order. Entry e < NSYM: G(gi, gj), gi <= gj, by rows of the NG x NG upper
-  //      triangle; NSYM <= e < NE: b; then the three statistics ----
+  //      triangle; NSYM <= e < NE: b; then the three statistics. Straight into this CTA's block of the pinned result area ----
+  RRPart *mine = parts + blockIdx.x;
   if (t < NE) {
     int erole, q;
     if (t < NSYM) {
@@ -623,143 +535,25 @@ __global__ void __launch_bounds__(BLOCK, 1)
 #pragma unroll
       for (int gq = 0; gq < GROUPS; gq++)
         v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + (gq * ROLES + erole) * RR_RACC + q];
-    __stcg(&parts->v[t][blockIdx.x], v);
+    mine->v[t] = v;
   } else if (t < NRED) {
     const int q = t - NE;
     double v = 0.0;
     for (int w = 0; w < WARPS; w++)
       v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + 32 * RR_RACC + q];
-    __stcg(&parts->v[t][blockIdx.x], v);
+    mine->v[t] = v;
   } else if (t >= 192 && t < 197) {
-    __stcg(&parts->c[t - 192][blockIdx.x], scnt[t - 192]);
+    mine->c[t - 192] = scnt[t - 192];
+  } else if (t == 197) {
+    mine->n_scan = n;
   }
-  // ---- last CTA finalizes ----
-  __threadfence();
-  __syncthreads();
-  if (t == 0) {
-    const unsigned int prev = atomicAdd(ticket, 1u);
-    s_last = (prev == (unsigned int)nb - 1u) ? 1u : 0u;
-  }
-  __syncthreads();
   tl_mark(tl, 5);
-  if (!s_last) {
-    if (tl && t == 0) { // slot 7 of a CTA that is not the last one: the SM it ran on
-      unsigned int smid;
-      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-      tl[(size_t)blockIdx.x * ML_TL_SLOTS + 7] = smid;
-    }
-    return;
-  }
-  __threadfence();
-  // shared-memory carve-up for the tail (the slabs are dead now)
-  double *fsum = slabs;              // [NRED]
-  double *G = fsum + 256;            // [NG][NG]
-  double *bv = G + NG * NG;          // [NG]
-  double *GT = bv + 32;              // [NG][ML_MAX_HX]
-  double *Hs = GT + NG * ML_MAX_HX;  // [hx][hx] + [hx]
-  const int hx = rc.total_hx;
-  // the partials of every entry: all loads of a warp's entries are issued before the first shuffle (one L2 round trip; they were
-  // written by other CTAs: __ldcg reads L2, never a stale L1 line)
-  {
-    constexpr int EPW = (NRED + WARPS - 1) / WARPS; // entries per warp
-    double acc[EPW];
-    int cacc = 0; // integer counters: the last 5 warps take one each, in the same batch of loads
-    const int cq = wid - (WARPS - 5);
-    if (cq >= 0)
-      for (int bq = lane; bq < nb; bq += 32)
-        cacc += __ldcg(&parts->c[cq][bq]);
-#pragma unroll
-    for (int u = 0; u < EPW; u++) {
-      const int q = wid + u * WARPS;
-      double v = 0.0;
-      if (q < NRED)
-        for (int bq = lane; bq < nb; bq += 32)
-          v += __ldcg(&parts->v[q][bq]);
-      acc[u] = v;
-    }
-#pragma unroll
-    for (int u = 0; u < EPW; u++) {
-      double v = acc[u];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1)
-        v += __shfl_xor_sync(0xffffffffu, v, o);
-      const int q = wid + u * WARPS;
-      if (lane == 0 && q < NRED)
-        fsum[q] = v;
-    }
-    if (cq >= 0) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1)
-        cacc += __shfl_xor_sync(0xffffffffu, cacc, o);
-      if (lane == 0)
-        scnt[cq] = cacc;
-    }
-  }
-  __syncthreads();
-  tl_mark(tl, 6);
-  if (t < NSYM) {
-    int r = 0, rem = t;
-    while (rem >= NG - r) {
-      rem -= NG - r;
-      r++;
-    }
-    G[r * NG + r + rem] = fsum[t];
-    G[(r + rem) * NG + r] = fsum[t];
-  } else if (t < NE) {
-    bv[t - NSYM] = fsum[t];
-  } else if (t == NE) {
-    ml_counters cn;
-    cn.n_points = n;
-    cn.n_acc = scnt[0], cn.n_knn_fail = scnt[1], cn.n_plane_fail = scnt[2], cn.n_badmatch = scnt[3], cn.n_chi_rej = scnt[4];
-    cn.sum_chi = fsum[NE + 0], cn.sum_chi2 = fsum[NE + 1], cn.sum_res = 0.0, cn.sum_res2 = fsum[NE + 2];
-    out->cnt = cn;
-    *ticket = 0u; // ready for the next scan
-  } else if (t >= NE + 1 && t < NE + 1 + (int)(sizeof(ScanState) / sizeof(int))) {
-    reinterpret_cast<int *>(&out->st)[t - NE - 1] = sst[t - NE - 1];
-  }
-  __syncthreads();
-  for (int idx = t; idx < NG * hx; idx += BLOCK) {
-    const int r = idx / hx, j = idx - r * hx;
-    double s = 0.0;
-#pragma unroll
-    for (int l = 0; l < NG; l++)
-      s += G[r * NG + l] * sT[l * ML_MAX_HX + j];
-    GT[r * ML_MAX_HX + j] = s;
-  }
-  __syncthreads();
-  // upper triangle computed once and mirrored: HtH is exactly symmetric. Staged in shared memory and written out in
-  // full 128-byte lines: `out` is pinned HOST memory (the result crosses PCIe as ~150 posted writes, no D2H copy node; the
-  // end of the kernel makes them visible to the host)
-  for (int idx = t; idx < hx * hx; idx += BLOCK) {
-    const int a = idx / hx, b2 = idx - a * hx;
-    if (a > b2)
-      continue;
-    double s = 0.0;
-#pragma unroll
-    for (int l = 0; l < NG; l++)
-      s += sT[l * ML_MAX_HX + a] * GT[l * ML_MAX_HX + b2];
-    Hs[idx] = s;
-    Hs[b2 * hx + a] = s;
-  }
-  for (int a = t; a < hx; a += BLOCK) {
-    double s = 0.0;
-#pragma unroll
-    for (int l = 0; l < NG; l++)
-      s += sT[l * ML_MAX_HX + a] * bv[l];
-    Hs[hx * hx + a] = s;
-  }
-  __syncthreads();
-  for (int idx = t; idx < hx * hx; idx += BLOCK)
-    out->HtH[idx] = Hs[idx];
-  for (int a = t; a < hx; a += BLOCK)
-    out->Htr[a] = Hs[hx * hx + a];
-  tl_mark(tl, 7);
 }
 
 // parity export: h = T^T g for every point (n x hx)
 __global__ void __launch_bounds__(256) k_expand_h(const ScanState *__restrict__ st, const PointRow *__restrict__ rows,
-                                                 const DevConsts *__restrict__ dc, double *__restrict__ h_rows) {
-  const int hx = dc->c.total_hx;
+                                                 const double *__restrict__ T /* [ML_G][ML_MAX_HX] */, int hx,
+                                                 double *__restrict__ h_rows) {
   const long long tot = (long long)st->n_scan * hx;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < tot; idx += (long long)gridDim.x * blockDim.x) {
     const int p = (int)(idx / hx), j = (int)(idx - (long long)p * hx);
@@ -767,7 +561,7 @@ __global__ void __launch_bounds__(256) k_expand_h(const ScanState *__restrict__ 
     if (rows[p].status == 0 || rows[p].status == 4) {
 #pragma unroll
       for (int l = 0; l < ML_G; l++)
-        s += rows[p].g[l] * dc->T[l * ML_MAX_HX + j];
+        s += rows[p].g[l] * T[l * ML_MAX_HX + j];
     }
     h_rows[idx] = s;
   }

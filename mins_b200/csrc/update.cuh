@@ -606,6 +606,42 @@ __device__ __forceinline__ void knn_walk(const KnnUnit &un, const float4 q, cons
   }
 }
 
+// What one query hands on (all outputs optional): the parity export (indices, squared distances), get_neighbors' verdict
+// (LidarHelper.cpp:280-285) and - what KD_TREE::Nearest_Search hands to compute_plane - the neighbours' COORDINATES
+// (ikd_Tree.cpp:383-387) in scan order (16 K contiguous bytes per query), so that the rows kernel reads them coalesced instead of
+// gathering by index. A query get_neighbors rejects is marked with a NaN first coordinate (the rows kernel needs no other flag).
+template <int K>
+__device__ __forceinline__ void knn_emit(const TopK<K> &best, const int qi, const float max_d2, int32_t *__restrict__ knn_idx,
+                                         float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok, const float4 *__restrict__ map_pts,
+                                         float4 *__restrict__ nbr) {
+  const bool found = best.i[K - 1] != 0x7fffffff;
+  if (knn_idx) {
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+      // candidates beyond the search radius are not reported (same convention as the brute-force oracle)
+      const bool in = best.i[j] != 0x7fffffff && best.d[j] <= max_d2;
+      knn_idx[(size_t)qi * K + j] = in ? best.i[j] : -1;
+      knn_d2[(size_t)qi * K + j] = in ? best.d[j] : INFINITY;
+    }
+  }
+  const bool ok = found && !((double)best.d[K - 1] > (double)max_d2);
+  if (knn_ok)
+    knn_ok[qi] = ok ? 1 : 0;
+  if (nbr) {
+    if (ok) {
+      float4 p[K];
+#pragma unroll
+      for (int j = 0; j < K; j++)
+        p[j] = __ldg(&map_pts[best.i[j]]);
+#pragma unroll
+      for (int j = 0; j < K; j++)
+        nbr[(size_t)qi * K + j] = p[j];
+    } else {
+      nbr[(size_t)qi * K] = make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);
+    }
+  }
+}
+
 template <int K>
 __global__ void __launch_bounds__(KNN_WARPS * 32)
     k_knn(const KnnUnit *__restrict__ units, ScanState *__restrict__ st, int ph, const float4 *__restrict__ q_sorted,
@@ -643,37 +679,8 @@ __global__ void __launch_bounds__(KNN_WARPS * 32)
     const float4 q = q_sorted[un.qbase + (active ? lane : 0)];
     TopK<K> best;
     knn_walk<K>(un, q, active, g, R, cell_start, cell_pts, best);
-    if (active) {
-      const int qi = __float_as_int(q.w);
-      const bool found = best.i[K - 1] != 0x7fffffff;
-      if (knn_idx) {
-#pragma unroll
-        for (int j = 0; j < K; j++) {
-          // candidates beyond the search radius are not reported (same convention as the brute-force oracle)
-          const bool in = best.i[j] != 0x7fffffff && best.d[j] <= max_d2;
-          knn_idx[(size_t)qi * K + j] = in ? best.i[j] : -1;
-          knn_d2[(size_t)qi * K + j] = in ? best.d[j] : INFINITY;
-        }
-      }
-      const bool ok = found && !((double)best.d[K - 1] > (double)max_d2);
-      knn_ok[qi] = ok ? 1 : 0;
-      // what KD_TREE::Nearest_Search hands to compute_plane: the neighbours' COORDINATES (ikd_Tree.cpp:383-387), in scan order
-      // (16 K contiguous bytes per query), so that the rows kernel reads them coalesced instead of gathering by index
-      // A query get_neighbors rejects is marked with a NaN first coordinate (the rows kernel needs no other flag).
-      if (nbr) {
-        if (ok) {
-          float4 p[K];
-#pragma unroll
-          for (int j = 0; j < K; j++)
-            p[j] = __ldg(&map_pts[best.i[j]]);
-#pragma unroll
-          for (int j = 0; j < K; j++)
-            nbr[(size_t)qi * K + j] = p[j];
-        } else {
-          nbr[(size_t)qi * K] = make_float4(__int_as_float(0x7fc00000), 0.f, 0.f, 0.f);
-        }
-      }
-    }
+    if (active)
+      knn_emit<K>(best, __float_as_int(q.w), max_d2, knn_idx, knn_d2, knn_ok, map_pts, nbr);
     int nxt = 0;
     if (lane == 0)
       nxt = nwarps + atomicAdd(&st->knn_next[ph], 1);

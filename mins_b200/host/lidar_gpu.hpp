@@ -63,6 +63,9 @@ struct OptionsLidar {
   double max_range = 100.0, min_range = 0.05, chi2_mult = 1.0;
   bool raw_do_downsample = true, raw_remove_motion_blur = false;
   double raw_downsample_size = 0.1, raw_noise = 0.01, raw_point_dt = 1e-6;
+  int raw_total_points = 0; // v_angles.size() * h_angles.size() of the sensor (LidarHelper.cpp:57): rays of one sweep, for the
+                            // de-skew time stamps; 0 = the size of the scan
+  int deskew_knots = 16;    // poses sampled over the sweep for ml_scan_deskew (the device blends the two bracketing knots)
   bool map_do_downsample = true, map_use_icp = false;
   double map_downsample_size = 0.1, map_noise = 0.1, map_ngbr_max_d = 0.5, map_decay_time = 30, map_decay_dist = 100;
   double map_icp_dist = 20; // OptionsLidar.h:97

@@ -57,7 +57,11 @@ static int m_upload(ml_handle *h, const float *, int stride, int n, float t_rel,
   std::printf("h%d scan_upload n=%d stride=%d t_rel=%.3f range=[%.2f,%.1f]\n", h->id, n, stride, t_rel, rmin, rmax);
   return ML_OK;
 }
-static int m_deskew(ml_handle *, const float *, int, int) { return ML_OK; }
+static int m_deskew(ml_handle *h, const float *knots, int n_knots, int total) {
+  std::printf("h%d scan_deskew knots=%d total=%d tx_first=%.4f tx_last=%.4f\n", h->id, n_knots, total, knots[3], knots[(n_knots - 1) * 12 + 3]);
+  return ML_OK;
+}
+static int g_icp_fail = 0; // the next g_icp_fail ICP calls report failure (max iterations reached)
 static int m_down(ml_handle *h, float leaf, int *) {
   std::printf("h%d scan_downsample leaf=%.2f\n", h->id, leaf);
   return ML_OK;
@@ -106,6 +110,11 @@ static int m_icp(ml_handle *h, const float T[16], const ml_icp_options *o, ml_ic
   std::memset(r, 0, sizeof(*r));
   for (int i = 0; i < 16; i++)
     r->T_LtoM[i] = r->T_icp[i] = T[i];
+  if (g_icp_fail > 0) { // lidar->icp_success = false: T_LtoM stays the initial guess (LidarHelper.cpp:177-179)
+    g_icp_fail--;
+    r->success = 0, r->max_iter_reached = 1;
+    return ML_OK;
+  }
   r->T_LtoM[3] += 0.5f; // a visible correction
   r->success = 1;
   return ML_OK;
@@ -260,5 +269,23 @@ int main() {
   up.try_update();
   state_of();
   std::printf("icp_success=%d\n", (int)up.last_icp_success);
+  std::printf("# ICP fails in update(): register_scan retries transform_to_map (LidarHelper.cpp:198); the retry succeeds -> registered with the retry's transform\n");
+  st.clones = {11.50, 11.55, 11.60, 11.65, 11.70, 11.75, 11.80};
+  st.now = 11.80;
+  g_icp_fail = 1;
+  up.feed_measurement(0, 11.62, pts.data(), 10);
+  up.try_update();
+  std::printf("icp_success=%d last_up=%.2f\n", (int)up.last_icp_success, up.ikd_data[0]->last_up_time);
+  std::printf("# ICP fails twice: the scan is NOT added and last_up_time is NOT advanced (LidarHelper.cpp:201-206)\n");
+  g_icp_fail = 2;
+  up.feed_measurement(0, 11.66, pts.data(), 10);
+  up.try_update();
+  state_of();
+  std::printf("icp_success=%d last_up=%.2f\n", (int)up.last_icp_success, up.ikd_data[0]->last_up_time);
+  std::printf("# raw_remove_motion_blur: knots over the sweep from the state, ml_scan_deskew between upload and downsample\n");
+  up.op.map_use_icp = false, up.op.raw_remove_motion_blur = true, up.op.raw_total_points = 1000, up.op.raw_point_dt = 1e-5, up.op.deskew_knots = 5;
+  up.feed_measurement(0, 11.70, pts.data(), 10);
+  up.try_update();
+  state_of();
   return 0;
 }

@@ -58,7 +58,10 @@ public:
       auto &ikd = ikd_data.at((*it)->id);
       // map not initialised, or no successful registration for more than 1 s: (re)build it from this scan
       if (!api.map_initialized(ikd->tree) || ikd->last_up_time + 1 < (*it)->time) {
-        init_map_local(*it, ikd);
+        if (!init_map_local(*it, ikd)) { // de-skew poses not available yet: keep it (UpdaterLidar.cpp:82-85)
+          ++it;
+          continue;
+        }
         it = stack_lidar_raw.erase(it);
         continue;
       }
@@ -106,8 +109,9 @@ public:
   OptionsLidar op;              // the reference reads state->op->lidar; here the updater holds its copy
 
 private:
-  struct Pending { // what register_scan needs from update(): the transform used (LiDARData::T_LtoM)
+  struct Pending { // what register_scan needs from update(): LiDARData::T_LtoM and LiDARData::icp_success (LidarTypes.h)
     float T_LtoM[16];
+    bool icp_success = true;
   };
   std::map<const LiDARData *, Pending> pending;
   std::map<int, const LiDARData *> resident; // which scan currently sits in each handle's device buffers
@@ -123,20 +127,94 @@ private:
 
   // LidarHelper::init_map_local (LidarHelper.cpp:103-113) on a raw scan: constructor's range filter, optional
   // down-sampling (UpdaterLidar.cpp:88), then Build
-  void init_map_local(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd) {
-    upload(scan, ikd, /*downsample=*/op.raw_do_downsample);
+  bool init_map_local(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd) {
+    if (!upload(scan, ikd, /*downsample=*/op.raw_do_downsample))
+      return false;
     ck(api.map_build_from_scan(ikd->tree), "ml_map_build_from_scan", ikd->tree);
     ikd->time = scan->time;
     ikd->last_up_time = scan->time;
+    return true;
   }
 
-  void upload(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd, bool downsample) {
+  // LiDARData ctor + [remove_motion_blur] + [downsample] on the device (UpdaterLidar.cpp:61,82,88). Returns false when the
+  // de-skew poses are not available yet (the reference keeps the scan and retries, UpdaterLidar.cpp:82-85).
+  bool upload(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd, bool downsample) {
+    std::vector<float> knots;
+    if (op.raw_remove_motion_blur && !deskew_knots(scan, knots))
+      return false;
     ck(api.scan_upload(ikd->tree, scan->xyz.data(), 3, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
                        nullptr),
        "ml_scan_upload", ikd->tree);
+    if (!knots.empty())
+      ck(api.scan_deskew(ikd->tree, knots.data(), (int)(knots.size() / 12), sweep_points(scan)), "ml_scan_deskew", ikd->tree);
     if (downsample)
       ck(api.scan_downsample(ikd->tree, (float)op.raw_downsample_size, nullptr), "ml_scan_downsample", ikd->tree);
     resident[ikd->id] = scan.get();
+    return true;
+  }
+  int sweep_points(const std::shared_ptr<LiDARData> &scan) const { return op.raw_total_points > 0 ? op.raw_total_points : scan->size(); }
+
+  // LidarHelper::remove_motion_blur (LidarHelper.cpp:39-87) with the guard as intended (the reference's `if (get_interpolated_pose)
+  // return false` at :54-58 is inverted and makes the function unreachable): point i was taken at
+  // t_i = time + dt - (total - i) raw_point_dt and is moved into the frame of the scan time,
+  //   T_LitoL = [R_GtoL R_GtoIi^T R_LtoI | R_GtoL (p_Ii + R_GtoIi^T p_LinI - p_LinG)]   (:76-81, fp32),
+  // evaluated at `deskew_knots` times spread uniformly over the sweep; the device interpolates between the knots.
+  bool deskew_knots(const std::shared_ptr<LiDARData> &scan, std::vector<float> &knots) {
+    const int nk = std::max(2, op.deskew_knots), total = sweep_points(scan);
+    const double dt = state->lidar_dt(scan->id), t1 = scan->time + dt, t0 = t1 - total * op.raw_point_dt;
+    double RGtoL[9], pLinG[3];
+    if (!LidarHelper::get_pose_LinG(*state, scan->id, t1, RGtoL, pLinG) || !LidarHelper::get_pose_LinG(*state, scan->id, t0, RGtoL, pLinG))
+      return false;
+    LidarHelper::get_pose_LinG(*state, scan->id, t1, RGtoL, pLinG);
+    knots.resize((size_t)nk * 12);
+    for (int j = 0; j < nk; j++) {
+      double RGtoLi[9], pLiinG[3], RLitoG[9], R[9], d[3], p[3];
+      if (!LidarHelper::get_pose_LinG(*state, scan->id, t0 + (t1 - t0) * j / (nk - 1), RGtoLi, pLiinG))
+        return false;
+      tr33(RGtoLi, RLitoG);
+      mul33(RGtoL, RLitoG, R); // R_GtoL R_GtoLi^T = R_GtoL R_GtoIi^T R_LtoI
+      for (int a = 0; a < 3; a++)
+        d[a] = pLiinG[a] - pLinG[a];
+      mv3(RGtoL, d, p);
+      for (int a = 0; a < 3; a++) {
+        for (int b = 0; b < 3; b++)
+          knots[(size_t)j * 12 + 4 * a + b] = (float)R[3 * a + b];
+        knots[(size_t)j * 12 + 4 * a + 3] = (float)p[a];
+      }
+    }
+    return true;
+  }
+
+  // LidarHelper::transform_to_map (LidarHelper.cpp:115-194) from the CURRENT state: T_LtoM from the interpolated poses and,
+  // with map_use_icp, the ICP block on the (uploaded, down-sampled) scan cloud. Leaves the scan resident, not yet transformed.
+  bool transform_to_map(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd, float T[16], bool *icp_success) {
+    const double dt = state->lidar_dt(scan->id);
+    double RGtoL[9], pLinG[3], RGtoM[9], pMinG[3];
+    if (!LidarHelper::get_pose_LinG(*state, scan->id, scan->time + dt, RGtoL, pLinG))
+      return false; // "Cannot get pose for LiDAR" (:128-131)
+    if (!LidarHelper::get_pose_LinG(*state, scan->id, ikd->time + dt, RGtoM, pMinG))
+      return false;
+    LidarHelper::T_LtoM(RGtoL, pLinG, RGtoM, pMinG, T);
+    *icp_success = true;
+    if (op.map_use_icp) {
+      if (!upload(scan, ikd, op.raw_do_downsample))
+        return false;
+      *icp_success = run_icp(ikd, T);
+    }
+    return true;
+  }
+  // the PointMatcher<float>::ICP block (LidarHelper.cpp:156-187) on the resident scan cloud; T: initial guess in, lidar->T_LtoM out
+  bool run_icp(std::shared_ptr<iKDDATA> &ikd, float T[16]) {
+    ml_icp_options io;
+    api.icp_default_options(&io);
+    io.max_dist = op.map_icp_dist;
+    io.seed = op.icp_seed++;
+    ml_icp_result ir;
+    const int irc = api.scan_icp(ikd->tree, T, &io, &ir);
+    ck(irc, "ml_scan_icp", ikd->tree);
+    if (irc == ML_OK)
+      std::memcpy(T, ir.T_LtoM, sizeof(float) * 16);
+    return irc == ML_OK && ir.success;
   }
 
   void erase_old(std::vector<std::shared_ptr<LiDARData>> &v) {
@@ -155,17 +233,34 @@ private:
     erase_old(stack_lidar_used);
   }
 
-  // LidarHelper::register_scan (LidarHelper.cpp:196-207)
+  // LidarHelper::register_scan (LidarHelper.cpp:196-207): "If ICP failed, retry it here" with the state the update has just
+  // improved; the scan is added to the map - and the 1 s staleness clock (UpdaterLidar.cpp:91) reset - only if the alignment
+  // succeeded. A scan whose ICP fails twice is dropped, so a bad T_LtoM never reaches the map.
   void register_scan(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd) {
     auto p = pending.find(scan.get());
     if (p == pending.end())
       return;
-    if (resident[ikd->id] != scan.get()) { // another scan of this LiDAR was processed in between: bring this one back
-      upload(scan, ikd, false);
-      ck(api.scan_transform(ikd->tree, p->second.T_LtoM), "ml_scan_transform", ikd->tree);
+    Pending &pd = p->second;
+    if (!pd.icp_success) {
+      float T[16];
+      bool ok = false;
+      if (transform_to_map(scan, ikd, T, &ok)) {
+        std::memcpy(pd.T_LtoM, T, sizeof(T));
+        pd.icp_success = ok;
+        if (resident[ikd->id] == scan.get()) // uploaded for the ICP: pointcloud_in_map with the new transform
+          ck(api.scan_transform(ikd->tree, pd.T_LtoM), "ml_scan_transform", ikd->tree);
+      }
     }
-    ck(api.map_add_scan(ikd->tree, op.map_do_downsample ? 1 : 0, (float)op.map_downsample_size, nullptr), "ml_map_add_scan", ikd->tree);
-    ikd->last_up_time = scan->time;
+    if (pd.icp_success) {
+      if (resident[ikd->id] != scan.get()) { // another scan of this LiDAR was processed in between: bring this one back
+        if (upload(scan, ikd, false))
+          ck(api.scan_transform(ikd->tree, pd.T_LtoM), "ml_scan_transform", ikd->tree);
+      }
+      if (resident[ikd->id] == scan.get()) {
+        ck(api.map_add_scan(ikd->tree, op.map_do_downsample ? 1 : 0, (float)op.map_downsample_size, nullptr), "ml_map_add_scan", ikd->tree);
+        ikd->last_up_time = scan->time;
+      }
+    }
     pending.erase(p);
   }
 
@@ -301,29 +396,20 @@ private:
     ml_counters cnt;
     std::memset(&cnt, 0, sizeof(cnt));
     int rc;
-    if (!op.map_use_icp) {
+    if (!op.map_use_icp && !op.raw_remove_motion_blur) {
       rc = api.scan_update(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
                            (float)op.max_range, op.raw_do_downsample ? (float)op.raw_downsample_size : 0.f, pend.T_LtoM, &c,
                            P.data(), HtH.data(), Htr.data(), &cnt);
     } else {
+      // the separate calls: LiDARData ctor, [remove_motion_blur] (UpdaterLidar.cpp:82), [downsample] (:88), then
       // transform_to_map with the ICP block (LidarHelper.cpp:156-187): the scan cloud is matched against the map starting
       // from the state's T_LtoM; on success the ICP transform replaces it for the data association AND for register_scan
       // (lidar->T_LtoM), while the residual/Jacobian keep using the state estimate (UpdaterLidar.cpp:281-283).
-      ck(api.scan_upload(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
-                         (float)op.max_range, nullptr),
-         "ml_scan_upload", ikd->tree);
-      if (op.raw_do_downsample)
-        ck(api.scan_downsample(ikd->tree, (float)op.raw_downsample_size, nullptr), "ml_scan_downsample", ikd->tree);
-      ml_icp_options io;
-      api.icp_default_options(&io);
-      io.max_dist = op.map_icp_dist;
-      io.seed = op.icp_seed++;
-      ml_icp_result ir;
-      const int irc = api.scan_icp(ikd->tree, pend.T_LtoM, &io, &ir);
-      ck(irc, "ml_scan_icp", ikd->tree);
-      if (irc == ML_OK)
-        std::memcpy(pend.T_LtoM, ir.T_LtoM, sizeof(pend.T_LtoM));
-      last_icp_success = irc == ML_OK && ir.success; // lidar->icp_success
+      if (!upload(lidar, ikd, op.raw_do_downsample))
+        return false; // de-skew poses not available yet: keep the scan (UpdaterLidar.cpp:82-85)
+      if (op.map_use_icp)
+        pend.icp_success = run_icp(ikd, pend.T_LtoM); // lidar->icp_success
+      last_icp_success = pend.icp_success;
       ck(api.scan_transform(ikd->tree, pend.T_LtoM), "ml_scan_transform", ikd->tree);
       rc = api.linsys(ikd->tree, &c, P.data(), HtH.data(), Htr.data(), &cnt);
     }

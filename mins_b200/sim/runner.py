@@ -3,6 +3,7 @@ mins/src/run_simulation.cpp:71-130 restated — B-spline ground truth, IMU at 20
 plan, clone window at 20 Hz / 1 s, LiDAR updater behind a backend (GPU C ABI or CPU oracle) — and the evaluator's ATE
 (mins_eval/src/functions/ResultTrajectory.cpp:70-97: se3 alignment, per-pose position norm and so3-log angle, RMSE).
 """
+import os
 import time
 from dataclasses import dataclass, field
 
@@ -11,9 +12,14 @@ import numpy as np
 from ..lidar import OptionsLidar
 from .ekf import State
 from .se3 import exp_so3, log_so3, rot_to_quat_jpl
-from .traj import BsplineSE3, synthetic_control_poses
+from .traj import BsplineSE3, load_bspline_dataset, synthetic_control_poses
 from .updater import LidarUpdater
-from .world import PlaneWorld, lidar_ray_dirs, simulate_scan, synthetic_floorplan
+from .world import PlaneWorld, lidar_ray_dirs, load_floorplan, simulate_scan, synthetic_floorplan
+
+# the MINS simulation's own inputs (mins_data/BSplineDataset/UD_Warehouse.txt, mins_data/FloorPlans/UD_Warehouse.txt: the
+# dataset the reference's CI evaluates, .github/workflows/evaluation.yml), committed as fixtures
+_GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "tests", "golden")
+UD_WAREHOUSE = (os.path.join(_GOLDEN, "UD_Warehouse_bspline.txt"), os.path.join(_GOLDEN, "UD_Warehouse_floorplan.txt"))
 
 
 @dataclass
@@ -36,6 +42,10 @@ class SimConfig:
     init_pos_err: float = 0.02       # m
     use_lidar: bool = True
     scan_source: str = "numpy"       # "numpy": host ray-caster (world.py); "cuda": ml_sim_raycast (Philox noise keyed by seed, scan index)
+    bspline_path: str = ""           # BSplineDataset file ("" = the synthetic loop); UD_WAREHOUSE[0] for the reference's
+    floorplan_path: str = ""         # FloorPlans file ("" = the synthetic hall); UD_WAREHOUSE[1]
+    use_gt_lidar: bool = False       # config_init.yaml use_gt_lidar: seed the map from a dense scan at the true pose
+                                     # (Initializer::init_lidar_sim, mins/src/init/Initializer.cpp:308-340)
     op: OptionsLidar = field(default_factory=lambda: OptionsLidar(raw_do_downsample=True, map_use_icp=False))
 
 
@@ -71,8 +81,8 @@ def run(cfg, backend):
     rng_imu = np.random.default_rng([cfg.seed, 1])
     rng_ldr = np.random.default_rng([cfg.seed, 2])
     rng_init = np.random.default_rng([cfg.seed, 3])
-    spline = BsplineSE3(synthetic_control_poses(cfg.world_seed, cfg.duration + 6.0))
-    world = PlaneWorld(synthetic_floorplan(cfg.world_seed))
+    spline = BsplineSE3(load_bspline_dataset(cfg.bspline_path) if cfg.bspline_path else synthetic_control_poses(cfg.world_seed, cfg.duration + 6.0))
+    world = PlaneWorld(load_floorplan(cfg.floorplan_path) if cfg.floorplan_path else synthetic_floorplan(cfg.world_seed))
     op = cfg.op
     dirs_L = lidar_ray_dirs(cfg.v_angles, -180.0, 180.0, cfg.h_resolution)
     # lidar0 extrinsics of config_lidar.yaml:33-37: T_imu_lidar = [R_LtoI | p_LinI]
@@ -111,7 +121,16 @@ def run(cfg, backend):
         caster.sim_set_world(world.packed())
         caster.sim_set_rays(dirs_L)
     p_LinI = -R_ItoL.T @ p_IinL
-    n_steps = int(round(cfg.duration * cfg.freq_imu))
+    if cfg.use_lidar and cfg.use_gt_lidar:
+        # Initializer::init_lidar_sim: v_angles = -90..89; the 180 values -90..89 are APPENDED to the h_angles the options already
+        # hold (-180:h_res:180): 180 x 361 rays for the simulation YAML; the scan is taken at the true pose with the usual noise
+        # and becomes the map as it is (LiDARData ctor + init_map_local: range filter, no down-sampling)
+        h_ang = np.concatenate([np.arange(-180.0, 180.0 + 1e-9, cfg.h_resolution), np.arange(-90.0, 90.0)])
+        V, Hh = np.meshgrid(np.arange(-90.0, 90.0), h_ang, indexing="ij")
+        ph, th = np.deg2rad(90.0 - V).ravel(), np.deg2rad(Hh).ravel()
+        dense = np.stack([np.sin(ph) * np.cos(th), np.sin(ph) * np.sin(th), np.cos(ph)], 1)
+        upd.init_map_gt(t0, simulate_scan(world, k0[0], k0[1], R_ItoL, p_IinL, dense, op.min_range, op.max_range, op.raw_noise, rng_ldr))
+    n_steps = int(round(min(cfg.duration, spline.t_end - 0.05 - t0) * cfg.freq_imu))
     imu_per_clone = int(round(cfg.freq_imu / cfg.clone_freq))
     imu_per_scan = int(round(cfg.freq_imu / cfg.freq_lidar))
     est, gt, nees_p = [], [], []

@@ -79,6 +79,21 @@ class BsplineSE3:
         return R[2], p[2].copy(), w, v, a
 
 
+def load_bspline_dataset(path):
+    """mins_data/BSplineDataset/*.txt (ov_core DatasetReader::load_simulated_trajectory format): rows
+    [t, px, py, pz, qx, qy, qz, qw], '#' comments. Returns (N, 8)."""
+    rows = []
+    with open(path) as f:
+        for line in f:
+            line = line.strip()
+            if not line or line.startswith("#"):
+                continue
+            v = [float(x) for x in line.replace(",", " ").split()]
+            if len(v) == 8:
+                rows.append(v)
+    return np.asarray(rows, np.float64)
+
+
 def synthetic_control_poses(seed=0, duration=60.0, rate=2.0, half_x=14.0, half_y=8.0, z0=0.6):
     """A smooth loop inside a 2*half_x by 2*half_y hall (BSplineDataset row format), for boxes without mins_data.
     Lissajous-like path with gentle roll/pitch and heading following the velocity direction."""

@@ -24,17 +24,37 @@ class GpuBackend:
         self.resident = None
         self.device_ms = 0.0
         self.last_T = None
+        self.last_icp_success = True
         self.icp_runs = self.icp_ok = self.icp_iters = 0
 
     def close(self):
         self.m.close()
 
+    def _icp(self, scan, op, T_init):
+        """the ICP block of transform_to_map (LidarHelper.cpp:156-187) on the freshly uploaded scan cloud"""
+        self.m.feed_scan(scan["xyz"], scan["t_rel"], op)
+        if op.raw_do_downsample:
+            self.m.downsample(op.raw_downsample_size)
+        T, res = self.m.icp(T_init, op.map_icp_dist, seed=scan["key"] + 1000003 * scan.get("icp_tries", 0))
+        scan["icp_tries"] = scan.get("icp_tries", 0) + 1
+        self.icp_runs += 1
+        self.icp_ok += int(res.success)
+        self.icp_iters += res.iterations
+        self.resident = None  # uploaded, not transformed
+        return T, bool(res.success)
+
+    def align(self, scan, op, T_init):
+        """register_scan's retry of transform_to_map (LidarHelper.cpp:198): returns (T_LtoM, icp_success)"""
+        if not op.map_use_icp:
+            return np.array(T_init, np.float32).reshape(4, 4), True
+        return self._icp(scan, op, T_init)
+
     def initialized(self):
         return self.m.initialized()
 
-    def build_map_from_scan(self, scan, op):
+    def build_map_from_scan(self, scan, op, downsample=True):
         self.m.feed_scan(scan["xyz"], scan["t_rel"], op)
-        if op.raw_do_downsample:
+        if op.raw_do_downsample and downsample:
             self.m.downsample(op.raw_downsample_size)
         self.m.init_map_local()
         self.resident = scan["key"]
@@ -42,16 +62,11 @@ class GpuBackend:
     def scan_update(self, scan, op, T_LtoM, consts, P):
         if op.map_use_icp:
             # transform_to_map with the ICP block (LidarHelper.cpp:156-187), then the point loop on the resident scan
-            self.m.feed_scan(scan["xyz"], scan["t_rel"], op)
-            if op.raw_do_downsample:
-                self.m.downsample(op.raw_downsample_size)
-            T_LtoM, res = self.m.icp(T_LtoM, op.map_icp_dist, seed=scan["key"])
-            self.icp_runs += 1
-            self.icp_ok += int(res.success)
-            self.icp_iters += res.iterations
+            T_LtoM, self.last_icp_success = self._icp(scan, op, T_LtoM)
             self.m.transform_to_map(T_LtoM)
             rc, HtH, Htr, cnt = self.m.linsys(consts, P)
         else:
+            self.last_icp_success = True
             rc, HtH, Htr, cnt = self.m.scan_update(scan["xyz"], scan["t_rel"], op, T_LtoM, consts, P)
         self.last_T = np.array(T_LtoM, np.float32).reshape(4, 4)
         self.device_ms += self.m.timing()["total"]
@@ -85,8 +100,18 @@ class LidarUpdater:
         self.stack_raw, self.stack_new, self.stack_used = [], [], []
         self.t_hist = deque(maxlen=101)
         self.n_updates = 0
+        self.n_skipped_registrations = 0
         self.counters = []
         self._key = 0
+
+    # ---- Initializer::init_lidar_sim (mins/src/init/Initializer.cpp:308-340): the map is the dense ground-truth scan ---------
+    def init_map_gt(self, stamp, xyz):
+        if self.FT < 0:
+            self.FT = stamp
+        self._key += 1
+        scan = dict(time=stamp, xyz=np.ascontiguousarray(xyz, np.float32), t_rel=float(np.float32(stamp - self.FT)), key=self._key)
+        self.backend.build_map_from_scan(scan, self.op, downsample=False)  # LiDARData ctor + init_map_local, no down-sampling
+        self.ikd_time = self.last_up_time = stamp
 
     # ---- UpdaterLidar::feed_measurement (UpdaterLidar.cpp:50-104) ----------------------------------------------------
     def feed_measurement(self, stamp, xyz):
@@ -131,9 +156,32 @@ class LidarUpdater:
                 still.append(scan)
         self.stack_new = still
         for scan in self.stack_used:
-            self.backend.register_scan(scan, self.op, scan["T_LtoM"])  # LidarHelper::register_scan
-            self.last_up_time = scan["time"]
+            # LidarHelper::register_scan (LidarHelper.cpp:196-207): "If ICP failed, retry it here" with the state the update has
+            # just improved; the scan enters the map - and resets the 1 s staleness clock - only if the alignment succeeded
+            if not scan.get("icp_success", True):
+                T0 = self._T_LtoM_from_state(scan)
+                if T0 is not None:
+                    scan["T_LtoM"], scan["icp_success"] = self.backend.align(scan, self.op, T0)
+            if scan.get("icp_success", True):
+                self.backend.register_scan(scan, self.op, scan["T_LtoM"])
+                self.last_up_time = scan["time"]
+            else:
+                self.n_skipped_registrations += 1
         self.stack_used = []
+
+    def _T_LtoM_from_state(self, scan):
+        """the pose algebra of LidarHelper::transform_to_map (LidarHelper.cpp:115-151) from the current estimate"""
+        st = self.state
+        eI, eA = st.get_interpolated_pose(scan["time"] + self.dt), st.get_interpolated_pose(self.ikd_time + self.dt)
+        if eI is None or eA is None:
+            return None
+        RItoL, pLinI = st.R_ItoL, -st.R_ItoL.T @ st.p_IinL
+        RGtoL, pLinG = RItoL @ eI[0], eI[1] + eI[0].T @ pLinI
+        RGtoM, pMinG = RItoL @ eA[0], eA[1] + eA[0].T @ pLinI
+        T = np.eye(4, dtype=np.float32)
+        T[:3, :3] = (RGtoM @ RGtoL.T).astype(np.float32)
+        T[:3, 3] = (RGtoM @ (pLinG - pMinG)).astype(np.float32)
+        return T
 
     # ---- UpdaterLidar::propagate_map_frame (UpdaterLidar.cpp:147-160) + propagate_map_to_newest_clone ---------------
     def propagate_map_frame(self):
@@ -199,6 +247,7 @@ class LidarUpdater:
         if not st.ekf_update(H_order, Hc, rcv):
             return False
         scan["T_LtoM"] = getattr(self.backend, "last_T", None) if op.map_use_icp else T_LtoM  # lidar->T_LtoM
+        scan["icp_success"] = bool(getattr(self.backend, "last_icp_success", True))              # lidar->icp_success
         if scan["T_LtoM"] is None:
             scan["T_LtoM"] = T_LtoM
         self.n_updates += 1

@@ -56,6 +56,26 @@ class PlaneWorld:
         return best
 
 
+def load_floorplan(path):
+    """Simulator::load_plane_data (mins/src/sim/Simulator.cpp:990-1096): lines starting with '#' are comments; a line with ONE
+    number sets the units-to-metres factor; a line with FOUR comma-separated numbers is a wall segment
+    (start_x, start_y, end_x, end_y) in file units. Returns (S, 4) segments in metres (PlaneWorld extrudes them to z in [-1, 4]
+    and adds floor and ceiling over their bounding box, :1053-1090)."""
+    units, segs = 1.0, []
+    with open(path) as f:
+        for line in f:
+            if line.find("#") == 0:  # `!current_line.find("#")`: only lines that START with the comment sign
+                continue
+            data = [float(x) for x in line.strip().split(",") if x.strip() != ""]
+            if len(data) == 1:
+                units = data[0]
+            elif len(data) == 4:
+                segs.append(data)
+    if not segs:
+        raise ValueError(f"no plane in {path}")
+    return np.asarray(segs, np.float64) * units
+
+
 def synthetic_floorplan(seed=0, half_x=20.0, half_y=12.5):
     """An indoor hall with rooms along the walls and free-standing pillars (wall segments in metres), in the spirit of
     mins_data/FloorPlans/UD_Warehouse.txt (outer rectangle + rectangular obstacles)."""

@@ -16,6 +16,7 @@ class OracleBackend:
         self.init = False
         self.threads = threads
         self.last_T = None
+        self.last_icp_success = True
         self.icp_runs = self.icp_ok = self.icp_iters = 0
 
     def close(self):
@@ -30,8 +31,8 @@ class OracleBackend:
             sc, _ = po.voxel_downsample(sc, op.raw_downsample_size)                   # LidarHelper::downsample
         return sc
 
-    def build_map_from_scan(self, scan, op):
-        self.map = self._scan(scan, op, op.raw_do_downsample).copy()                  # init_map_local -> Build
+    def build_map_from_scan(self, scan, op, downsample=True):
+        self.map = self._scan(scan, op, op.raw_do_downsample and downsample).copy()   # init_map_local -> Build
         self.init = len(self.map) > 0
 
     def scan_update(self, scan, op, T_LtoM, consts, P):
@@ -39,19 +40,30 @@ class OracleBackend:
         sc = self._scan(scan, op, op.raw_do_downsample)
         if len(sc) == 0:
             return capi.ML_SOFT_NO_ROWS, None, None, capi.ml_counters()
+        self.last_icp_success = True
         if op.map_use_icp:                                                            # LidarHelper.cpp:156-187
-            from . import icp_oracle
-            r = icp_oracle.icp(sc[:, :3], self.map, T_LtoM, op.map_icp_dist, seed=scan["key"])
-            T_LtoM = r["T_LtoM"]
-            self.icp_runs += 1
-            self.icp_ok += int(r["success"])
-            self.icp_iters += r["iterations"]
+            T_LtoM, self.last_icp_success = self._icp(scan, sc, op, T_LtoM)
         self.last_T = np.array(T_LtoM, np.float32).reshape(4, 4)
         sm = po.transform_f32(sc, T_LtoM)                                             # transform_to_map
         ref = po.scan_linsys(consts, P, self.map, sc, sm, threads=self.threads, want_compress=True)
         if ref["cnt"].n_acc == 0:
             return capi.ML_SOFT_NO_ROWS, None, None, ref["cnt"]
         return 0, ref["Hc"], ref["rc"], ref["cnt"]
+
+    def _icp(self, scan, sc, op, T_init):
+        from . import icp_oracle
+        r = icp_oracle.icp(sc[:, :3], self.map, T_init, op.map_icp_dist, seed=scan["key"] + 1000003 * scan.get("icp_tries", 0))
+        scan["icp_tries"] = scan.get("icp_tries", 0) + 1
+        self.icp_runs += 1
+        self.icp_ok += int(r["success"])
+        self.icp_iters += r["iterations"]
+        return r["T_LtoM"], bool(r["success"])
+
+    def align(self, scan, op, T_init):
+        """register_scan's retry of transform_to_map (LidarHelper.cpp:198)"""
+        if not op.map_use_icp:
+            return np.array(T_init, np.float32).reshape(4, 4), True
+        return self._icp(scan, self._scan(scan, op, op.raw_do_downsample), op, T_init)
 
     def register_scan(self, scan, op, T_LtoM):
         sc = po.range_filter(scan["xyz"], scan["t_rel"], op.max_range, op.min_range)  # pointcloud_original

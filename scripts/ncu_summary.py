@@ -60,7 +60,7 @@ def main():
                 d[k] /= n
         d["dram_bytes_per_launch"] = d.get("dram_read", 0.0) + d.get("dram_write", 0.0)
     out = {"all": acc, "source": os.path.basename(rep)}
-    for alias, pat in (("knn", "k_knn<5>"), ("rows_reduce", "k_rows_reduce<5"), ("front", "k_range_filter_bin")):
+    for alias, pat in (("knn", "k_knn<5>"), ("knn", "k_front_knn<5"), ("rows_reduce", "k_rows_reduce<5"), ("front", "k_range_filter_bin")):
         for name, d in acc.items():
             if name.startswith(pat):
                 out[alias] = d

@@ -2,7 +2,8 @@
 """Per-CTA timeline of the kNN and rows kernels of one G-64 scan (ml_debug_timeline: %globaltimer stamps by thread 0 of every
 CTA). Prints, per mark, min / median / max over the CTAs in microseconds after the first CTA of the kNN kernel started.
 
-  kNN  marks: 0 entry, 1 after griddepcontrol.wait, 2 exit
+  kNN  marks (fused kernel): 0 entry, 1 after griddepcontrol.wait, 2 producer phase over, 3 exit; producers, last tile:
+              4 loads landed + range test, 5 look-back done, 6 clouds written + hash filled, 7 scan + scatter + unit records
   rows marks: 0 entry, 1 after griddepcontrol.wait, 2 constants staged, 3 warp 0 left the tile loop, 4 CTA barrier passed,
               5 ticket taken, 6 (last CTA) partials summed + T staged, 7 (last CTA) result block written
 """
@@ -25,6 +26,8 @@ n = int(w["n_rays"])
 m = LidarMap(max_scan_points=n, max_map_points=len(w["map"]) + 2 * n)
 m.Build(w["map"])
 dev = torch.from_numpy(w["raw"]).cuda()
+pin = torch.from_numpy(w["raw"]).pin_memory()
+src = pin if os.environ.get("TL_HOST") else dev
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 hx = w["total_hx"]
 out = (np.zeros((hx, hx)), np.zeros(hx), capi.ml_counters())
@@ -33,7 +36,7 @@ P = np.ascontiguousarray(w["P"], np.float64)
 
 
 def step():
-    rc = m.lib.ml_scan_update(m.h, dev.data_ptr(), 4, n, w["t_rel"], op.min_range, op.max_range, 0.0, T.ctypes.data, C.byref(w["consts"]),
+    rc = m.lib.ml_scan_update(m.h, src.data_ptr(), 4, n, w["t_rel"], op.min_range, op.max_range, 0.0, T.ctypes.data, C.byref(w["consts"]),
                               P.ctypes.data, out[0].ctypes.data, out[1].ctypes.data, C.byref(out[2]))
     assert rc == 0
 

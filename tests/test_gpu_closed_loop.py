@@ -51,7 +51,7 @@ def test_closed_loop_with_gpu_icp_and_gpu_raycaster(cuda_ok):
         gpu.close()
     r_cpu = run(SimConfig(seed=3, duration=4.0, op=op), OracleBackend())
     for x in (r, r_cpu):
-        assert x["icp_runs"] >= 35 and x["icp_ok"] >= 0.9 * x["icp_runs"]
+        assert x["icp_runs"] >= 35 and x["icp_ok"] >= 0.8 * x["icp_runs"]  # retries of failed alignments count as runs
         assert 4 < x["icp_iters"] / x["icp_runs"] < 25
         assert x["rmse_pos_m"] < 0.3 and x["n_updates"] >= 35
     assert 0.4 < r["rmse_pos_m"] / r_cpu["rmse_pos_m"] < 2.5

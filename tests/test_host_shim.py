@@ -71,3 +71,25 @@ def test_queueing_policy_trace():
     expect("EKFUpdate")
     expect("h0 map_add_scan")
     expect("icp_success=1")
+    # ICP failed in update(): the point loop ran with the state's T_LtoM (tx = 0.120); register_scan retries transform_to_map
+    # (upload -> downsample -> ICP again) and registers with the retry's result (LidarHelper.cpp:196-207)
+    assert "tx=0.120" in expect("h0 scan_icp")
+    assert "tx=0.120" in expect("h0 scan_transform")
+    expect("EKFUpdate")
+    expect("h0 scan_upload")
+    assert "tx=0.120" in expect("h0 scan_icp")
+    assert "tx=0.620" in expect("h0 scan_transform")
+    expect("h0 map_add_scan")
+    assert "icp_success=0 last_up=11.62" in expect("icp_success")
+    # ICP fails twice: no map_add_scan, last_up_time stays (so the 1 s staleness re-initialisation can trigger, UpdaterLidar.cpp:91)
+    tail = out[out.index("# ICP fails twice"):out.index("# raw_remove_motion_blur")]
+    assert tail.count("scan_icp") == 2 and "map_add_scan" not in tail and "last_up=11.62" in tail and "raw=0 new=0 used=0" in tail
+    # raw_remove_motion_blur (UpdaterLidar.cpp:82, LidarHelper.cpp:39-87): 5 knots over a 10 ms sweep at 1 m/s: the first knot
+    # sits 1 cm behind the scan-time frame, the last one is the identity
+    expect("h0 scan_upload")
+    d = expect("h0 scan_deskew")
+    assert "knots=5 total=1000 tx_first=-0.0100 tx_last=0.0000" in d
+    expect("h0 scan_downsample")
+    expect("h0 scan_transform")
+    expect("h0 linsys")
+    expect("h0 map_add_scan")
