@@ -116,14 +116,6 @@ struct ml_handle {
   bool use_fused_knn = true; // MINS_FUSED_KNN=0: the separate kernels (A/B)
   int fused_producers = 0;   // MINS_FUSED_PRODUCERS: 0 = by input kind
   bool fused_attr[ML_MAX_K + 1][2] = {};
-  // host -> device pipeline of the fused path: the scan crosses PCIe in chunks on the copy engine (stream_copy), each followed
-  // by a stream memory operation that stamps chunk_flag[c]; the producers of the fused kernel wait per chunk
-  cudaStream_t stream_copy = nullptr;
-  uint32_t *chunk_flag = nullptr;
-  int dma_chunks = 0; // MINS_DMA_CHUNKS > 0: chunked copy-engine transfer instead of zero-copy reads by the kernel. Measured
-                      // (G-64, 2.1 MB): zero-copy 132 us e2e, 2 chunks 136, 4 chunks 152, 8 chunks 191 - every (copy, flag) pair
-                      // costs the copy engine ~5 us, more than the overlap wins; kept as an A/B switch
-  int (*write_value32)(cudaStream_t, unsigned long long, unsigned int, unsigned int) = nullptr; // cuStreamWriteValue32
   bool rows_exported = false;
   bool rows_attr[ML_MAX_K + 1][8] = {};
   // debug timeline (ml_debug_timeline): per-CTA %globaltimer stamps of the kNN and rows kernels
@@ -353,8 +345,6 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     h->rows_block = atoi(e);
   if (const char *e = getenv("MINS_FUSED_KNN"))
     h->use_fused_knn = !(e[0] == '0');
-  if (const char *e = getenv("MINS_DMA_CHUNKS"))
-    h->dma_chunks = std::max(0, std::min(8, atoi(e)));
   if (const char *e = getenv("MINS_FUSED_PRODUCERS"))
     h->fused_producers = atoi(e);
   if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
@@ -443,17 +433,6 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
   CK(cudaMalloc(&h->knn_ok, cs));
   CK(cudaMalloc(&h->nbr, sizeof(float4) * cs * ML_MAX_K));
   CK(cudaMalloc(&h->d_T, sizeof(double) * ML_G * ML_MAX_HX));
-  CK(cudaStreamCreateWithFlags(&h->stream_copy, cudaStreamNonBlocking));
-  CK(cudaMalloc(&h->chunk_flag, sizeof(uint32_t) * 16));
-  CK(cudaMemset(h->chunk_flag, 0, sizeof(uint32_t) * 16));
-  {
-    void *fn = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess)
-      h->write_value32 = reinterpret_cast<int (*)(cudaStream_t, unsigned long long, unsigned int, unsigned int)>(fn);
-    else
-      cudaGetLastError();
-  }
   CK(cudaMalloc(&h->d_fctl, sizeof(FusedCtl)));
   CK(cudaMemset(h->d_fctl, 0, sizeof(FusedCtl)));
   CK(cudaMalloc(&h->units_tag, sizeof(uint32_t) * ((size_t)h->units_cap + 16384)));
@@ -470,17 +449,13 @@ void ml_destroy(ml_handle *h) {
     return;
   use_device(h);
   cudaStreamSynchronize(h->stream);
-  if (h->stream_copy) {
-    cudaStreamSynchronize(h->stream_copy);
-    cudaStreamDestroy(h->stream_copy);
-  }
   if (h->h_merge)
     cudaFreeHost(h->h_merge);
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
                  h->pt_rank, h->tile_sums, h->vox_tab, h->add_slot, h->contender, h->keep, h->pos, h->d_ints, h->add_pts, h->d_raw,
                  h->scan_pts, h->scan_orig, h->scan_map, h->scan_tmp, h->d_st, h->sort_keys[0], h->sort_keys[1], h->sort_vals[0],
                  h->sort_vals[1], h->radix_state, h->radix_ghist, h->d_vg, h->d_knots, h->qtab, h->q_slot, h->q_rank, h->q_sorted, h->units,
-                 h->knn_idx, h->knn_d2, h->knn_ok, h->nbr, h->d_T, h->d_fctl, h->units_tag, h->chunk_flag, h->rows,
+                 h->knn_idx, h->knn_d2, h->knn_ok, h->nbr, h->d_T, h->d_fctl, h->units_tag, h->rows,
                  h->sim_planes, h->sim_dirs, h->sim_dist, h->sim_n_out, h->icp_keep, h->icp_normals, h->icp_cell_pts, h->icp_read,
                  h->icp_q, h->d_icp, h->d_ist, h->icp_parts, h->d_hrows, h->tl_rows, h->lb_state, h->lb_ctr, h->radix_dbase, h->sim_knots, h->mg_done, h->d_bbox_vg};
   for (void *p : dev)
@@ -1425,29 +1400,27 @@ int ml_linsys(ml_handle *h, const ml_scan_consts *c, const double *P, double *Ht
 // The fused front end + kNN of the un-down-sampled one-call path (fused.cuh): one launch.
 template <int K, bool VEC4>
 static int launch_front_knn(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2,
-                            int producers, uint32_t epoch, int tiles_per_chunk) {
+                            int producers) {
   bool &attr_set = h->fused_attr[K][VEC4 ? 1 : 0];
   if (!attr_set) {
     CK(cudaFuncSetAttribute(k_front_knn<K, VEC4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FK_SMEM));
     attr_set = true;
   }
-  const int grid = h->n_sm * 3;
+  const int grid = h->n_sm * 2;
   launch_pdl(h, k_front_knn<K, VEC4>, grid, FK_BLOCK, FK_SMEM, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st, h->scan_pts,
-             h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, epoch, h->d_fctl, std::min(producers, grid),
+             h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, lb_next_epoch(h), h->d_fctl, std::min(producers, grid),
              (const GridDesc *)h->d_grid, h->q_sorted, h->units, h->units_tag, (const uint32_t *)h->cell_start,
              (const float4 *)h->cell_pts, max_d2, (int32_t *)nullptr, (float *)nullptr, (uint8_t *)nullptr,
-             (const float4 *)h->map_pts[h->cur], h->nbr, (const uint32_t *)(tiles_per_chunk > 0 ? h->chunk_flag : nullptr), tiles_per_chunk,
-             h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
+             (const float4 *)h->map_pts[h->cur], h->nbr, h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
   return check_launch(h);
 }
 template <int K>
 static int launch_front_knn_k(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2,
-                              int producers, uint32_t epoch, int tiles_per_chunk) {
+                              int producers) {
   const bool vec4 = stride == 4 && (((uintptr_t)raw_src) & 15u) == 0;
-  return vec4 ? launch_front_knn<K, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk)
-              : launch_front_knn<K, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
+  return vec4 ? launch_front_knn<K, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers)
+              : launch_front_knn<K, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
 }
-__global__ void k_set_u32(uint32_t *p, uint32_t v) { *p = v; }
 static int scan_front_knn_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM,
                                 int k, float max_d2) {
   if (n < 0 || (n > 0 && !xyz) || (stride != 3 && stride != 4))
@@ -1462,87 +1435,30 @@ static int scan_front_knn_async(ml_handle *h, const float *xyz, int stride, int 
     for (int c = 0; c < 4; c++)
       h->T_LtoM.m[4 * r + c] = T_LtoM[4 * r + c];
   h->have_T = true;
-  // Where the scan comes from decides how it reaches the kernel:
-  //  * device memory: read in place;
-  //  * host memory (pinned or pageable), dma_chunks > 0: the copy engine brings it across PCIe in chunks on its own stream
-  //    (pageable chunks pass through the handle's pinned staging buffer), a stream memory operation behind each chunk stamps its
-  //    flag, and the kernel - already running - hands each tile to its producer as soon as its chunk has landed: the transfer of
-  //    chunk c + 1 overlaps the grouping and the search of chunk c;
-  //  * MINS_DMA_CHUNKS=0: the kernel reads pinned, device-mapped memory itself (zero-copy), every tile at once.
-  const int ntiles = cdiv(n, RF_TILE);
-  const uint32_t epoch = lb_next_epoch(h);
   const float *raw_src = nullptr;
-  int tiles_per_chunk = 0;
-  cudaPointerAttributes at;
-  const bool known = cudaPointerGetAttributes(&at, xyz) == cudaSuccess;
-  cudaGetLastError();
-  const bool on_device = known && (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
-  const bool pinned = known && at.type == cudaMemoryTypeHost;
-  int rc_launch = ML_OK;
-  auto launch = [&](int producers) {
-    producers = std::max(1, std::min(h->fused_producers > 0 ? h->fused_producers : producers, ntiles));
-    switch (k) {
-    case 3: return launch_front_knn_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 4: return launch_front_knn_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 5: return launch_front_knn_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 6: return launch_front_knn_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 7: return launch_front_knn_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 8: return launch_front_knn_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    case 9: return launch_front_knn_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    default: return launch_front_knn_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers, epoch, tiles_per_chunk);
-    }
-  };
-  if (on_device) {
-    raw_src = xyz;
-    return launch(ntiles);
-  }
-  if (h->dma_chunks == 0 && pinned && h->zero_copy && at.devicePointer) {
-    raw_src = (const float *)at.devicePointer;
-    return launch(ntiles);
-  }
-  if (h->dma_chunks == 0) { // whole-scan copy on the main stream, then the kernel
-    bool dummy;
-    if (int rc = resolve_input(h, xyz, stride, n, &raw_src, &dummy))
-      return rc;
-    return launch(ntiles);
-  }
-  // chunked DMA. Chunk = a whole number of tiles; the first chunk is on its way before the kernel is launched.
-  const int chunks = std::max(1, std::min(h->dma_chunks, ntiles));
-  tiles_per_chunk = cdiv(ntiles, chunks);
-  raw_src = h->d_raw;
-  const size_t pt_bytes = sizeof(float) * (size_t)stride;
-  auto copy_chunk = [&](int c) -> int {
-    const size_t i0 = (size_t)c * tiles_per_chunk * RF_TILE, i1 = std::min((size_t)n, i0 + (size_t)tiles_per_chunk * RF_TILE);
-    if (i0 >= i1)
-      return ML_OK;
-    const char *src = (const char *)xyz + i0 * pt_bytes;
-    if (!pinned) { // pageable: through the pinned staging buffer, chunk by chunk (the DMA of chunk c runs beside the memcpy of c + 1)
-      memcpy((char *)h->h_raw + i0 * pt_bytes, src, (i1 - i0) * pt_bytes);
-      src = (const char *)h->h_raw + i0 * pt_bytes;
-    }
-    CK(cudaMemcpyAsync((char *)h->d_raw + i0 * pt_bytes, src, (i1 - i0) * pt_bytes, cudaMemcpyHostToDevice, h->stream_copy));
-    if (h->write_value32) {
-      if (h->write_value32(h->stream_copy, (unsigned long long)(uintptr_t)(h->chunk_flag + c), epoch, 0) != 0)
-        return fail(h, ML_ERR_CUDA, "cuStreamWriteValue32 failed");
-    } else {
-      k_set_u32<<<1, 1, 0, h->stream_copy>>>(h->chunk_flag + c, epoch);
-    }
-    return ML_OK;
-  };
-  if (int rc = copy_chunk(0))
+  bool over_pcie = false;
+  if (int rc = resolve_input(h, xyz, stride, n, &raw_src, &over_pcie))
     return rc;
-  rc_launch = launch(ntiles);
-  if (rc_launch)
-    return rc_launch;
-  for (int c = 1; c * tiles_per_chunk < ntiles; c++)
-    if (int rc = copy_chunk(c)) {
-      // the kernel is waiting for this chunk: let it run out (on whatever the buffer holds) before reporting the failure
-      for (int q = c; q * tiles_per_chunk < ntiles; q++)
-        k_set_u32<<<1, 1, 0, h->stream_copy>>>(h->chunk_flag + q, epoch);
-      cudaStreamSynchronize(h->stream);
-      return rc;
-    }
-  return ML_OK;
+  // Producers. From HBM every tile has its own producer and the front end is over in one wave. Over PCIe (the kernel reads
+  // pinned host memory itself) a few producers walk the tiles in order, each requesting its next tile while it groups the
+  // current one: 32 x 32 KB in flight keep the link full (bandwidth-delay product ~100 KB), the early tiles complete early and
+  // the search overlaps the transfer. (A chunked copy-engine transfer with a stream memory operation behind each chunk was
+  // measured instead: 2 / 4 / 8 chunks = 136 / 152 / 191 us e2e against 132 us zero-copy - ~5 us per (copy, flag) pair.)
+  const int ntiles = cdiv(n, RF_TILE);
+  int producers = over_pcie ? 32 : ntiles;
+  if (h->fused_producers > 0)
+    producers = h->fused_producers;
+  producers = std::max(1, std::min(producers, ntiles));
+  switch (k) {
+  case 3: return launch_front_knn_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 4: return launch_front_knn_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 5: return launch_front_knn_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 6: return launch_front_knn_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 7: return launch_front_knn_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 8: return launch_front_knn_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  case 9: return launch_front_knn_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  default: return launch_front_knn_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2, producers);
+  }
 }
 
 extern "C" {

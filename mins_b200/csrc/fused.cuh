@@ -39,9 +39,41 @@ struct FusedCtl {
   unsigned int pad1[30];
 };
 
-constexpr int FK_BLOCK = RF_BLOCK;        // 256
+constexpr int FK_BLOCK = 512;             // 16 warps; two CTAs per SM
+constexpr int FK_ROWS = RF_TILE / FK_BLOCK; // 4 rays per thread: warp w owns 128 consecutive rays, a row is 32 of them
 constexpr int FK_SLOTS = 2 * RF_TILE;     // 4096: shared-memory hash table, load factor <= 1/2
-constexpr size_t FK_SMEM = (size_t)FK_SLOTS * (sizeof(unsigned long long) + 2 * sizeof(uint32_t)); // 64 KB
+constexpr size_t FK_HASH_BYTES = (size_t)FK_SLOTS * (sizeof(unsigned long long) + 2 * sizeof(uint32_t)); // 64 KB
+constexpr size_t FK_STAGE_BYTES = (size_t)RF_TILE * sizeof(float4);                                          // 32 KB: the next tile's rays
+constexpr size_t FK_SMEM = FK_HASH_BYTES + FK_STAGE_BYTES;                                                   // 96 KB, two CTAs per SM
+
+// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (cp.async.bulk; SASS UBLKCP). One thread issues the copy
+// of a whole 32 KB tile; nobody's registers, load queue or memory fences are involved while it is in flight - which is the
+// point here: a __threadfence() waits for the issuing thread's outstanding LOADS too, so a register prefetch of the next tile
+// over PCIe (11 us) stalled the publication of the current one. ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "MBAR_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+               "@p bra MBAR_DONE;\n"
+               "bra MBAR_WAIT;\n"
+               "MBAR_DONE:\n"
+               "}" ::"r"(smem_u32(bar)),
+               "r"(parity)
+               : "memory");
+}
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p) {
   uint32_t v;
@@ -54,7 +86,7 @@ __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t *p) {
   return v;
 }
 
-// the raw scan is read once and may have been written by the copy engine while this kernel was already running: L2 loads
+// the raw scan is read exactly once: L2 loads (no L1 allocation)
 template <bool VEC4> __device__ __forceinline__ float4 load_raw_cg(const float *raw, int stride, int i) {
   if (VEC4)
     return __ldcg(reinterpret_cast<const float4 *>(raw) + i);
@@ -63,21 +95,22 @@ template <bool VEC4> __device__ __forceinline__ float4 load_raw_cg(const float *
 }
 
 template <int K, bool VEC4>
-__global__ void __launch_bounds__(FK_BLOCK, 3)
+__global__ void __launch_bounds__(FK_BLOCK, 2)
     k_front_knn(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax, ScanState *__restrict__ st,
                 float4 *__restrict__ cloud, float4 *__restrict__ orig, Tf32 T, float4 *__restrict__ in_map,
                 unsigned long long *tile_state, uint32_t epoch, FusedCtl *ctl, int producers, const GridDesc *__restrict__ gd,
                 float4 *__restrict__ q_sorted, KnnUnit *__restrict__ units, uint32_t *__restrict__ units_tag,
                 const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts, float max_d2,
                 int32_t *__restrict__ knn_idx, float *__restrict__ knn_d2, uint8_t *__restrict__ knn_ok,
-                const float4 *__restrict__ map_pts, float4 *__restrict__ nbr, const uint32_t *chunk_flag, int tiles_per_chunk,
-                unsigned long long *__restrict__ tl) {
+                const float4 *__restrict__ map_pts, float4 *__restrict__ nbr, unsigned long long *__restrict__ tl) {
   extern __shared__ __align__(16) unsigned char fk_smem[];
   unsigned long long *hkey = reinterpret_cast<unsigned long long *>(fk_smem); // [FK_SLOTS] 0 = empty
   uint32_t *hcnt = reinterpret_cast<uint32_t *>(hkey + FK_SLOTS);             // [FK_SLOTS] queries of the cell in this tile
   uint32_t *hpre = hcnt + FK_SLOTS;                                           // [FK_SLOTS] (query base) | (unit base) << 16
+  float4 *stage = reinterpret_cast<float4 *>(fk_smem + FK_HASH_BYTES);        // [RF_TILE] the next tile's rays (VEC4 input)
+  __shared__ __align__(8) unsigned long long s_bar;
   __shared__ uint32_t wsum[FK_BLOCK / 32];
-  __shared__ uint32_t s_tile, s_prefix, s_tq, s_gu, s_tu;
+  __shared__ uint32_t s_next, s_prefix, s_gu, s_tu;
   tl_mark(tl, 0);
   pdl_enter();
   tl_mark(tl, 1);
@@ -86,37 +119,39 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
   const GridDesc g = *gd;
 
   // ------------------------------------------------------------------------------------------ producer
-  if ((int)blockIdx.x < producers) {
-    // a producer's first tile is its block index (no ticket round trip on the way in); the ticket hands out the rest
-    for (uint32_t tile = blockIdx.x;;) {
-      if (tile >= ntiles)
-        break;
-      // the scan may still be on its way: the copy engine brings it in chunks and stamps chunk_flag[c] with the scan's epoch
-      // behind each (stream order); a tile waits for its chunk only
-      if (chunk_flag) {
-        if (threadIdx.x == 0) {
-          const uint32_t *f = chunk_flag + tile / (uint32_t)tiles_per_chunk;
-          while (ld_acquire_u32(f) != epoch)
-            __nanosleep(200);
-        }
-        __syncthreads();
-      }
-      const int wbase = (int)tile * RF_TILE + wid * (RF_TILE / (FK_BLOCK / 32));
-      float4 pt[8];
+  if ((int)blockIdx.x < producers && blockIdx.x < ntiles) {
+    // A producer's first tile is its block index (no ticket round trip on the way in); the ticket hands out the rest. The rays
+    // of the NEXT tile are requested as soon as the current ones have landed, so the transfer (PCIe, with the scan in pinned
+    // host memory) runs beside the grouping of the current tile: a few producers keep the link busy and finish their tiles one
+    // after the other, which is what lets the consumers start while most of the scan is still on the bus.
+    uint32_t tile = blockIdx.x;
+    uint32_t phase = 0;
+    if (VEC4 && threadIdx.x == 0) {
+      mbar_init(&s_bar, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    float4 pt[FK_ROWS];
+    {
+      const int wbase = (int)tile * RF_TILE + wid * (32 * FK_ROWS);
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         const int i = wbase + r * 32 + lane;
         pt[r] = i < n ? load_raw_cg<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
+    }
+    for (;;) {
+      if (threadIdx.x == 0)
+        s_next = (uint32_t)producers + atomicAdd(&ctl->tile_next, 1u); // the next tile's ticket, early
       // clear the table while the loads are in flight
       for (int s = threadIdx.x; s < FK_SLOTS; s += FK_BLOCK) {
         hkey[s] = 0ull;
         hcnt[s] = 0u;
       }
-      uint32_t bal[8];
+      const int wbase = (int)tile * RF_TILE + wid * (32 * FK_ROWS);
+      uint32_t bal[FK_ROWS];
       uint32_t cnt = 0;
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         const int i = wbase + r * 32 + lane;
         const bool k = i < n && range_keep(pt[r], rmin, rmax);
         bal[r] = __ballot_sync(0xffffffffu, k);
@@ -126,6 +161,12 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
         wsum[wid] = cnt;
       __syncthreads();
       tl_mark(tl, 4); // loads landed, range test done
+      const uint32_t next = s_next;
+      if (VEC4 && next < ntiles && threadIdx.x == 0) { // the next tile's rays start their journey now (one bulk copy)
+        const uint32_t bytes = (uint32_t)min(RF_TILE, n - (int)next * RF_TILE) * (uint32_t)sizeof(float4);
+        mbar_expect_tx(&s_bar, bytes);
+        bulk_g2s(stage, reinterpret_cast<const float4 *>(raw) + (size_t)next * RF_TILE, bytes, &s_bar);
+      }
       // warp 0: the tile's offset in the compacted clouds (decoupled look-back). The other warps go on to the hash fill, which
       // needs no offset: the look-back's L2 round trips hide behind it.
       if (wid == 0) {
@@ -136,7 +177,6 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
         const uint32_t excl = lb_exclusive_prefix(tile_state, tile, epoch, tot);
         if (lane == 0) {
           s_prefix = excl;
-          s_tq = tot;
           if (tile == 0) {
             st->n_raw = n;
             st->vox_n = 0;
@@ -148,15 +188,14 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
           }
         }
       }
-      // hash fill: cell of every kept query (its map-frame position is recomputed for the cloud stores below: cheaper than
-      // 24 more live registers), warp-aggregated insert; sr = slot | rank << 16
-      // In phases over the 8 rows, so that the long-latency steps of different rows overlap (a row at a time costs 8 dependent
-      // chains of match -> CAS -> atomicAdd -> shuffle: 6 us per tile measured): keys, peer sets, slot claims, counts, broadcast.
+      // hash fill: cell of every kept query (its map-frame position is recomputed for the stores below: cheaper than keeping it
+      // live), warp-aggregated insert; sr = slot | rank << 16. In phases over the rows, so that the long-latency steps of
+      // different rows overlap: keys, peer sets, slot claims, counts, broadcast.
       const uint32_t lt = (1u << lane) - 1u;
-      unsigned long long key[8];
-      uint32_t peers[8], sr[8];
+      unsigned long long key[FK_ROWS];
+      uint32_t peers[FK_ROWS], sr[FK_ROWS], base[FK_ROWS];
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         const float4 qm = tf_apply(T, pt[r]);
         const int lim = 1 << 19;
         const int cx = max(-lim, min(lim, cell_coord((double)qm.x, g.ox, g.inv_cell)));
@@ -165,13 +204,13 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
         key[r] = cell_key(cx, cy, cz);
       }
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         const bool kept = (bal[r] >> lane) & 1u;
-        // rays the range gate dropped get a key of their own (0 is no cell key): they match nobody
+        // rays the range gate dropped get a key of their own (a lane number is no cell key): they match nobody
         peers[r] = __match_any_sync(0xffffffffu, kept ? key[r] : (unsigned long long)lane) & bal[r];
       }
 #pragma unroll
-      for (int r = 0; r < 8; r++) { // leaders claim the slot of their cell
+      for (int r = 0; r < FK_ROWS; r++) { // leaders claim the slot of their cell
         sr[r] = 0u;
         const bool kept = (bal[r] >> lane) & 1u;
         if (kept && lane == __ffs(peers[r]) - 1) {
@@ -185,14 +224,13 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
           sr[r] = s;
         }
       }
-      uint32_t base[8];
 #pragma unroll
-      for (int r = 0; r < 8; r++) { // ... and reserve the ranks of all their peers with one atomicAdd
+      for (int r = 0; r < FK_ROWS; r++) { // ... and reserve the ranks of all their peers with one atomicAdd
         const bool kept = (bal[r] >> lane) & 1u;
         base[r] = (kept && lane == __ffs(peers[r]) - 1) ? atomicAdd(&hcnt[sr[r]], (uint32_t)__popc(peers[r])) : 0u;
       }
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         const bool kept = (bal[r] >> lane) & 1u;
         const int leader = kept ? __ffs(peers[r]) - 1 : lane;
         const uint32_t s = __shfl_sync(0xffffffffu, sr[r], leader);
@@ -201,10 +239,10 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
       }
       __syncthreads();
       tl_mark(tl, 5); // look-back done, hash filled
-      // exclusive scan over the slots: queries and units (ceil(cnt / 32)) of every occupied slot, 16 consecutive slots per thread
+      // exclusive scan over the slots: queries and units (ceil(cnt / 32)) of every occupied slot, 8 consecutive slots per thread
       uint32_t my_gu = 0, my_tu = 0;
       {
-        constexpr int SPT = FK_SLOTS / FK_BLOCK; // 16
+        constexpr int SPT = FK_SLOTS / FK_BLOCK; // 8
         uint32_t lq = 0, lu = 0;
 #pragma unroll
         for (int j = 0; j < SPT; j++) {
@@ -237,7 +275,7 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
       for (int w = 0; w < wid; w++)
         pos += wsum[w];
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         if ((bal[r] >> lane) & 1u) {
           const uint32_t o = pos + __popc(bal[r] & lt);
           const uint32_t s = sr[r] & 0xffffu, rank = sr[r] >> 16;
@@ -271,19 +309,18 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
       tl_mark(tl, 7); // queries and unit records visible
       for (uint32_t j = threadIdx.x; j < tu; j += FK_BLOCK)
         units_tag[gu + j] = epoch;
-      // next tile's ticket; the thread that reserved the units (thread 0) also counts the tile as done: its fence orders the
-      // reservation before the count, which is all a leaving consumer relies on (unit_reserve final once tiles_done == ntiles)
+      // the thread that reserved the units (thread 0) also counts the tile as done: its fence orders the reservation before
+      // the count, which is all a leaving consumer relies on (unit_reserve final once tiles_done == ntiles)
       if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(&ctl->tiles_done, 1u);
-        s_tile = (uint32_t)producers + atomicAdd(&ctl->tile_next, 1u);
       }
       // the clouds in scan order: pointcloud, pointcloud_original, pointcloud_in_map (nobody in this kernel reads them)
       pos = gq;
       for (int w = 0; w < wid; w++)
         pos += wsum[w];
 #pragma unroll
-      for (int r = 0; r < 8; r++) {
+      for (int r = 0; r < FK_ROWS; r++) {
         if ((bal[r] >> lane) & 1u) {
           const uint32_t o = pos + __popc(bal[r] & lt);
           const float4 q = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
@@ -293,8 +330,25 @@ __global__ void __launch_bounds__(FK_BLOCK, 3)
         }
         pos += __popc(bal[r]);
       }
-      __syncthreads(); // the ticket is in; this tile's shared state is dead
-      tile = s_tile;
+      if (next >= ntiles)
+        break;
+      tile = next;
+      {
+        const int nbase = (int)tile * RF_TILE + wid * (32 * FK_ROWS);
+        if (VEC4) {
+          mbar_wait(&s_bar, phase);
+          phase ^= 1u;
+        }
+#pragma unroll
+        for (int r = 0; r < FK_ROWS; r++) {
+          const int i = nbase + r * 32 + lane;
+          if (VEC4)
+            pt[r] = i < n ? stage[wid * (32 * FK_ROWS) + r * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f);
+          else
+            pt[r] = i < n ? load_raw_cg<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+      __syncthreads(); // this tile's shared state is dead; the staged rays are in registers
     }
   }
   tl_mark(tl, 2);
