@@ -71,6 +71,25 @@ public:
     erase_invalid_dataset();
   }
 
+  // Initializer::init_lidar_sim (mins/src/init/Initializer.cpp:308-340; the Initializer is a friend of the reference's
+  // UpdaterLidar): the dense ground-truth scan becomes the map as it is - LiDARData ctor (range filter) + init_map_local, no
+  // down-sampling - and sets the reference time FT.
+  void init_map_gt(int id, double stamp, const float *xyz, int n) {
+    if (FT < 0)
+      FT = stamp;
+    auto scan = std::make_shared<LiDARData>();
+    scan->time = stamp, scan->id = id;
+    scan->xyz.assign(xyz, xyz + 3 * (size_t)n);
+    auto &ikd = ikd_data.at(id);
+    ck(api.scan_upload(ikd->tree, scan->xyz.data(), 3, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
+                       nullptr),
+       "ml_scan_upload", ikd->tree);
+    resident[ikd->id] = nullptr;
+    ck(api.map_build_from_scan(ikd->tree), "ml_map_build_from_scan", ikd->tree);
+    ikd->time = stamp;
+    ikd->last_up_time = stamp;
+  }
+
   // UpdaterLidar::try_update (UpdaterLidar.cpp:106-125)
   void try_update() {
     for (auto it = stack_lidar_new.begin(); it != stack_lidar_new.end();) {
@@ -105,6 +124,7 @@ public:
   double FT = -1;
   std::vector<std::shared_ptr<LiDARData>> stack_lidar_raw, stack_lidar_new, stack_lidar_used; // friend Initializer touches these
   ml_counters last_counters{};
+  int n_updates = 0; // successful EKF updates so far
   bool last_icp_success = true; // LiDARData::icp_success of the last update (LidarTypes.h)
   OptionsLidar op;              // the reference reads state->op->lidar; here the updater holds its copy
 
@@ -427,6 +447,7 @@ private:
       return false;
     state->EKFUpdate(H_order, widths, Rc.data(), rc_.data(), rank, total_hx);
     pending[lidar.get()] = pend;
+    n_updates++;
     return true;
   }
 

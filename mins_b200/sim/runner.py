@@ -44,6 +44,7 @@ class SimConfig:
     scan_source: str = "numpy"       # "numpy": host ray-caster (world.py); "cuda": ml_sim_raycast (Philox noise keyed by seed, scan index)
     bspline_path: str = ""           # BSplineDataset file ("" = the synthetic loop); UD_WAREHOUSE[0] for the reference's
     floorplan_path: str = ""         # FloorPlans file ("" = the synthetic hall); UD_WAREHOUSE[1]
+    remove_noise: bool = False       # config_simulation.yaml remove_noise: noise-free IMU, scans and initial state (P0 unchanged)
     use_gt_lidar: bool = False       # config_init.yaml use_gt_lidar: seed the map from a dense scan at the true pose
                                      # (Initializer::init_lidar_sim, mins/src/init/Initializer.cpp:308-340)
     op: OptionsLidar = field(default_factory=lambda: OptionsLidar(raw_do_downsample=True, map_use_icp=False))
@@ -94,8 +95,9 @@ def run(cfg, backend):
     dt_imu = 1.0 / cfg.freq_imu
     t0 = np.ceil((spline.t_start + 0.1) * cfg.clone_freq) / cfg.clone_freq
     k0 = spline.get_kinematics(t0)
-    R0 = exp_so3(rng_init.normal(0, cfg.init_ori_err, 3)) @ k0[0]
-    p0 = k0[1] + rng_init.normal(0, cfg.init_pos_err, 3)
+    nz = 0.0 if cfg.remove_noise else 1.0
+    R0 = exp_so3(nz * rng_init.normal(0, cfg.init_ori_err, 3)) @ k0[0]
+    p0 = k0[1] + nz * rng_init.normal(0, cfg.init_pos_err, 3)
     P0 = np.diag(np.r_[np.full(3, cfg.init_ori_err**2), np.full(3, cfg.init_pos_err**2), np.full(3, 0.01**2), np.full(3, 1e-4**2 + 1e-8),
                        np.full(3, 0.02**2)])
     st = State(R0, p0, k0[3].copy(), np.zeros(3), np.zeros(3), P0, intr_order=cfg.intr_order, R_ItoL=R_ItoL, p_IinL=p_IinL)
@@ -108,16 +110,16 @@ def run(cfg, backend):
         nonlocal bg_true, ba_true
         R, _, w, _, a = spline.get_kinematics(t)
         sd = 1.0 / np.sqrt(dt_imu)
-        wm = w + bg_true + cfg.gyro_noise * sd * rng_imu.standard_normal(3)
-        am = R @ (a + st.g) + ba_true + cfg.accel_noise * sd * rng_imu.standard_normal(3)
-        bg_true = bg_true + cfg.gyro_walk * np.sqrt(dt_imu) * rng_imu.standard_normal(3)
-        ba_true = ba_true + cfg.accel_walk * np.sqrt(dt_imu) * rng_imu.standard_normal(3)
+        wm = w + bg_true + nz * cfg.gyro_noise * sd * rng_imu.standard_normal(3)
+        am = R @ (a + st.g) + ba_true + nz * cfg.accel_noise * sd * rng_imu.standard_normal(3)
+        bg_true = bg_true + nz * cfg.gyro_walk * np.sqrt(dt_imu) * rng_imu.standard_normal(3)
+        ba_true = ba_true + nz * cfg.accel_walk * np.sqrt(dt_imu) * rng_imu.standard_normal(3)
         return wm, am
 
     caster = None
     if cfg.use_lidar and cfg.scan_source == "cuda":
         from ..lidar import LidarMap
-        caster = LidarMap(max_scan_points=max(1024, len(dirs_L)), max_map_points=1024, device=getattr(backend, "device", 0))
+        caster = LidarMap(max_scan_points=max(1 << 17, len(dirs_L)), max_map_points=1024, device=getattr(backend, "device", 0))
         caster.sim_set_world(world.packed())
         caster.sim_set_rays(dirs_L)
     p_LinI = -R_ItoL.T @ p_IinL
@@ -129,7 +131,14 @@ def run(cfg, backend):
         V, Hh = np.meshgrid(np.arange(-90.0, 90.0), h_ang, indexing="ij")
         ph, th = np.deg2rad(90.0 - V).ravel(), np.deg2rad(Hh).ravel()
         dense = np.stack([np.sin(ph) * np.cos(th), np.sin(ph) * np.sin(th), np.cos(ph)], 1)
-        upd.init_map_gt(t0, simulate_scan(world, k0[0], k0[1], R_ItoL, p_IinL, dense, op.min_range, op.max_range, op.raw_noise, rng_ldr))
+        if caster is not None:  # same generator as the C++ harness: Philox keyed by (seed, 0xffffffff)
+            caster.sim_set_rays(dense)
+            xyz0 = caster.sim_raycast(k0[1] + k0[0].T @ p_LinI, k0[0].T @ R_ItoL.T, op.min_range, op.max_range, noise=nz * op.raw_noise,
+                                      seed=(int(cfg.seed) << 32) | 0xffffffff)[:, :3]
+            caster.sim_set_rays(dirs_L)
+        else:
+            xyz0 = simulate_scan(world, k0[0], k0[1], R_ItoL, p_IinL, dense, op.min_range, op.max_range, nz * op.raw_noise, rng_ldr)
+        upd.init_map_gt(t0, xyz0)
     n_steps = int(round(min(cfg.duration, spline.t_end - 0.05 - t0) * cfg.freq_imu))
     imu_per_clone = int(round(cfg.freq_imu / cfg.clone_freq))
     imu_per_scan = int(round(cfg.freq_imu / cfg.freq_lidar))
@@ -157,10 +166,10 @@ def run(cfg, backend):
         if cfg.use_lidar and k % imu_per_scan == 0:  # SystemManager::feed_measurement_lidar (:177-185)
             R_gt, p_gt = spline.get_pose(t)
             if caster is not None:
-                xyz = caster.sim_raycast(p_gt + R_gt.T @ p_LinI, R_gt.T @ R_ItoL.T, op.min_range, op.max_range, noise=op.raw_noise,
+                xyz = caster.sim_raycast(p_gt + R_gt.T @ p_LinI, R_gt.T @ R_ItoL.T, op.min_range, op.max_range, noise=nz * op.raw_noise,
                                          seed=(int(cfg.seed) << 32) | (k // imu_per_scan))[:, :3]
             else:
-                xyz = simulate_scan(world, R_gt, p_gt, R_ItoL, p_IinL, dirs_L, op.min_range, op.max_range, op.raw_noise, rng_ldr)
+                xyz = simulate_scan(world, R_gt, p_gt, R_ItoL, p_IinL, dirs_L, op.min_range, op.max_range, nz * op.raw_noise, rng_ldr)
             c0 = time.perf_counter()
             upd.feed_measurement(t, xyz)
             upd.try_update()

@@ -1,0 +1,72 @@
+#!/usr/bin/env python
+"""Monte-Carlo job (BASELINE.json configs[4]) with the host-C++ harness: independent closed-loop runs
+(mins_b200/host/mins_sim_run: minimal EKF core + mins_gpu::UpdaterLidar over the C ABI, scans ray-cast on the device), one
+process per run, `--per-gpu` processes at a time on each of `--gpus` GPUs. No collective: the unit of work is a seed.
+
+  python scripts/mc_sim_cpp.py --gpus 1 --runs 64 --per-gpu 8 --duration 50 [--icp 1]
+
+Prints the per-run JSON lines (stderr) and one summary line (stdout): ATE mean +- std, NEES, wall time of the job, aggregate
+simulated scans per second, and the share of a run's wall time spent inside the LiDAR updater (the device-facing part)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "mins_b200", "host", "mins_sim_run")
+G = os.path.join(ROOT, "tests", "golden")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--runs", type=int, default=8)
+    ap.add_argument("--per-gpu", type=int, default=4)
+    ap.add_argument("--duration", type=float, default=50.0)
+    ap.add_argument("--icp", type=int, default=0)
+    ap.add_argument("--seed0", type=int, default=0)
+    args = ap.parse_args()
+    pending = list(range(args.seed0, args.seed0 + args.runs))
+    slots = [(g, s) for g in range(args.gpus) for s in range(args.per_gpu)]
+    running, results = {}, []
+    t0 = time.perf_counter()
+    while pending or running:
+        for slot in slots:
+            if slot not in running and pending:
+                seed = pending.pop(0)
+                cmd = [BIN, "--bspline", os.path.join(G, "UD_Warehouse_bspline.txt"), "--floorplan", os.path.join(G, "UD_Warehouse_floorplan.txt"),
+                       "--seed", str(seed), "--duration", str(args.duration), "--icp", str(args.icp), "--device", str(slot[0])]
+                running[slot] = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        for slot, p in list(running.items()):
+            if p.poll() is not None:
+                out, err = p.communicate()
+                del running[slot]
+                if p.returncode != 0:
+                    print(f"run failed on gpu {slot[0]}: {err[-500:]}", file=sys.stderr)
+                    continue
+                r = json.loads(out.strip().splitlines()[-1])
+                r["gpu"] = slot[0]
+                results.append(r)
+                print(json.dumps(r), file=sys.stderr)
+        time.sleep(0.002)
+    wall = time.perf_counter() - t0
+    a = lambda k: np.array([r[k] for r in results], float)
+    out = {"job": "monte-carlo, host C++ harness, UD_Warehouse", "gpus": args.gpus, "runs": len(results), "per_gpu": args.per_gpu,
+           "duration_s": args.duration, "icp": args.icp, "wall_s": wall,
+           "sim_scans_per_s": float(a("n_scans").sum() / wall), "sim_seconds_per_s": float(len(results) * args.duration / wall),
+           "rmse_ori_deg": [float(a("rmse_ori_deg").mean()), float(a("rmse_ori_deg").std())],
+           "rmse_pos_m": [float(a("rmse_pos_m").mean()), float(a("rmse_pos_m").std())],
+           "nees_pos": [float(a("nees_pos").mean()), float(a("nees_pos").std())],
+           "updates_per_scan": float(a("n_updates").sum() / max(a("n_scans").sum(), 1)),
+           "lidar_share_of_run_wall": float((a("ldr_wall_s") / a("wall_s")).mean()),
+           "raycast_share_of_run_wall": float((a("raycast_wall_s") / a("wall_s")).mean()),
+           "run_wall_s_mean": float(a("wall_s").mean())}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
