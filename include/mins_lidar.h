@@ -21,6 +21,7 @@
 #ifndef MINS_LIDAR_H
 #define MINS_LIDAR_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -165,6 +166,12 @@ int ml_scan_downsample(ml_handle *h, float leaf, int *n_ds);
 int ml_scan_transform(ml_handle *h, const float T_LtoM[16]);
 /* which: 0 = pointcloud, 1 = pointcloud_in_map, 2 = pointcloud_original */
 int ml_scan_download(ml_handle *h, int which, float *xyzi_out, int cap, int *n);
+/* Storage for queued scans (the role of LiDARData's pcl::PointCloud buffers, LidarTypes.h:37-66): pinned, device-mapped host
+ * memory. A scan handed to ml_scan_upload / ml_scan_update from such a buffer (stride 4, 16-byte aligned) is read by the kernels
+ * straight over PCIe - no staging memcpy, no DMA copy node; pageable memory works too but pays a host memcpy per scan.
+ * Allocation is slow (a driver call): pool the buffers (the C++ shim does). NULL on failure. */
+void *ml_host_alloc(size_t bytes);
+void ml_host_free(void *p);
 /* test hook: replace `pointcloud` (and `pointcloud_original`) verbatim, no filtering */
 int ml_scan_set(ml_handle *h, const float *xyzi, int n);
 

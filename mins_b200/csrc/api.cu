@@ -771,6 +771,19 @@ int ml_scan_upload(ml_handle *h, const float *xyz, int stride, int n, float t_re
   return ML_OK;
 }
 
+void *ml_host_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return p;
+}
+void ml_host_free(void *p) {
+  if (p)
+    cudaFreeHost(p);
+}
+
 int ml_scan_set(ml_handle *h, const float *xyzi, int n) {
   if (!h || n < 0 || (n > 0 && !xyzi))
     return fail(h, ML_ERR_ARG, "ml_scan_set: bad argument");

@@ -47,12 +47,14 @@ struct ml_api {
   decltype(&ml_linsys) linsys;
   decltype(&ml_icp_default_options) icp_default_options;
   decltype(&ml_scan_icp) scan_icp;
+  decltype(&ml_host_alloc) host_alloc;
+  decltype(&ml_host_free) host_free;
 #ifndef MINS_GPU_NO_LINK
   static ml_api real() {
     return ml_api{&ml_create,      &ml_destroy,         &ml_last_error,  &ml_map_reset,   &ml_map_initialized, &ml_map_build_from_scan,
                   &ml_map_add_scan, &ml_map_reanchor,   &ml_map_flatten, &ml_map_size,    &ml_scan_upload,     &ml_scan_deskew,
                   &ml_scan_downsample, &ml_scan_transform, &ml_scan_update, &ml_info_to_sqrt, &ml_linsys, &ml_icp_default_options,
-                  &ml_scan_icp};
+                  &ml_scan_icp, &ml_host_alloc, &ml_host_free};
   }
 #endif
 };
@@ -129,11 +131,14 @@ inline void mv3(const double *A, const double *v, double *o) {
 
 // ---- LiDARData (LidarTypes.h:37-66): a queued scan. The clouds live on the device once the scan is being processed;
 // while queued only the raw host copy is kept (the range filter of the constructor runs on the device at upload). ----
+// The raw points sit in a pinned, device-mapped buffer from the updater's pool, PointXYZ layout (x, y, z, pad: stride 4, the
+// reference's own 16-byte points), so that the device reads them in place when the scan's turn comes.
 struct LiDARData {
   double time = -1;
   int id = -1;
-  std::vector<float> xyz; // n x 3, sensor frame
-  int size() const { return (int)(xyz.size() / 3); }
+  float *xyz = nullptr; // n x 4, sensor frame (owned by the updater's pool)
+  int n = 0;
+  int size() const { return n; }
 };
 
 // ---- iKDDATA (LidarTypes.h:71-81): one local map = one ml_handle ---------------------------------------------------

@@ -119,6 +119,12 @@ static int m_icp(ml_handle *h, const float T[16], const ml_icp_options *o, ml_ic
   r->success = 1;
   return ML_OK;
 }
+static int g_host_allocs = 0;
+static void *m_host_alloc(size_t bytes) {
+  g_host_allocs++;
+  return std::malloc(bytes);
+}
+static void m_host_free(void *p) { std::free(p); }
 static int m_sqrt(const double *HtH, const double *Htr, int n, double *Rc, double *rc) {
   for (int i = 0; i < n * n; i++)
     Rc[i] = 0;
@@ -215,7 +221,7 @@ struct MockState : StateView {
 int main() {
   ml_api api{m_create, m_destroy, m_err,    m_reset, m_inited, m_build,     m_add_scan, m_reanchor,
              m_flatten, m_size,   m_upload, m_deskew, m_down,  m_transform, m_update,   m_sqrt,
-             m_linsys,  m_icp_defaults, m_icp};
+             m_linsys,  m_icp_defaults, m_icp, m_host_alloc, m_host_free};
   OptionsLidar op;
   op.max_n = 1, op.raw_do_downsample = true, op.raw_downsample_size = 0.3, op.map_downsample_size = 0.3, op.min_range = 1.0;
   op.do_calib_ext = true;
@@ -287,5 +293,6 @@ int main() {
   up.feed_measurement(0, 11.70, pts.data(), 10);
   up.try_update();
   state_of();
+  std::printf("host_allocs=%d\n", g_host_allocs);
   return 0;
 }

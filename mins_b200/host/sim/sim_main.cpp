@@ -100,13 +100,6 @@ static SimResult run(const SimConfig &cfg) {
                        scan4.data(), n_rays, n_out) != ML_OK)
       throw std::runtime_error(std::string("ml_sim_raycast: ") + ml_last_error(caster));
   };
-  std::vector<float> scan3;
-  auto to_xyz3 = [&](int n) {
-    scan3.resize((size_t)3 * n);
-    for (int i = 0; i < n; i++)
-      for (int a = 0; a < 3; a++)
-        scan3[3 * i + a] = scan4[4 * i + a];
-  };
   if (cfg.use_lidar) {
     upd.reset(new mins_gpu::UpdaterLidar(&view, cfg.op, api, 1 << 17, 1 << 19, cfg.device));
     ml_config cc{cfg.device, 1 << 17, 1024, 0, 0.f};
@@ -126,8 +119,7 @@ static SimResult run(const SimConfig &cfg) {
       }
       int n = 0;
       raycast(t0, ray_dirs(vd, hd), (cfg.seed << 32) | 0xffffffffull, &n);
-      to_xyz3(n);
-      upd->init_map_gt(0, t0, scan3.data(), n);
+      upd->init_map_gt(0, t0, scan4.data(), n, 4);
     }
   }
 
@@ -176,10 +168,9 @@ static SimResult run(const SimConfig &cfg) {
       int n = 0;
       const auto r0 = clk::now();
       raycast(t, dirs_L, (cfg.seed << 32) | (unsigned long long)(k / imu_per_scan), &n);
-      to_xyz3(n);
       const auto c0 = clk::now();
       res.raycast_wall_s += std::chrono::duration<double>(c0 - r0).count();
-      upd->feed_measurement(0, t, scan3.data(), n);
+      upd->feed_measurement(0, t, scan4.data(), n, 4);
       upd->try_update();
       res.ldr_wall_s += std::chrono::duration<double>(clk::now() - c0).count();
       res.n_scans++;

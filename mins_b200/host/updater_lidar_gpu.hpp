@@ -9,7 +9,7 @@ public:
   // history per LiDAR id. Capacities size the device buffers once (nothing is allocated on the per-scan path).
   UpdaterLidar(StateView *state, const OptionsLidar &op, const ml_api &api, int max_scan_points = 1 << 18, int max_map_points = 1 << 21,
                int device = 0)
-      : op(op), state(state), api(api) {
+      : op(op), state(state), api(api), cap_scan(max_scan_points) {
     for (int i = 0; i < op.max_n; i++) {
       Chi.emplace_back();
       t_hist[i] = std::deque<double>();
@@ -24,24 +24,51 @@ public:
     }
   }
   ~UpdaterLidar() {
+    stack_lidar_raw.clear(), stack_lidar_new.clear(), stack_lidar_used.clear(); // scans return their buffers to the pool
+    for (float *b : pool)
+      api.host_free(b);
     for (auto &ikd : ikd_data)
       api.destroy(ikd->tree);
   }
   UpdaterLidar(const UpdaterLidar &) = delete;
   UpdaterLidar &operator=(const UpdaterLidar &) = delete;
 
-  // UpdaterLidar::feed_measurement (UpdaterLidar.cpp:50-104). `stamp` in seconds, xyz = n x 3 floats (sensor frame).
-  void feed_measurement(int id, double stamp, const float *xyz, int n) {
+  // LiDARData::LiDARData's storage: a pooled pinned buffer of max_scan_points PointXYZ; the incoming points (n x stride floats)
+  // are copied once, here, off the update's critical path. The range filter of the constructor runs on the device later.
+  std::shared_ptr<LiDARData> make_scan(int id, double stamp, const float *xyz, int n, int stride) {
+    if (n > cap_scan)
+      die("feed_measurement: more points than max_scan_points", nullptr);
+    float *buf = nullptr;
+    if (!pool.empty()) {
+      buf = pool.back();
+      pool.pop_back();
+    } else {
+      buf = (float *)api.host_alloc(sizeof(float) * 4 * (size_t)cap_scan);
+      if (!buf)
+        die("ml_host_alloc", nullptr);
+    }
+    for (int i = 0; i < n; i++) {
+      buf[4 * i + 0] = xyz[(size_t)stride * i + 0], buf[4 * i + 1] = xyz[(size_t)stride * i + 1], buf[4 * i + 2] = xyz[(size_t)stride * i + 2];
+      buf[4 * i + 3] = 1.f;
+    }
+    std::shared_ptr<LiDARData> scan(new LiDARData(), [this](LiDARData *d) {
+      if (d->xyz)
+        pool.push_back(d->xyz);
+      delete d;
+    });
+    scan->time = stamp, scan->id = id, scan->xyz = buf, scan->n = n;
+    return scan;
+  }
+
+  // UpdaterLidar::feed_measurement (UpdaterLidar.cpp:50-104). `stamp` in seconds, xyz = n x stride floats (sensor frame).
+  void feed_measurement(int id, double stamp, const float *xyz, int n, int stride = 3) {
     if (FT < 0)
       FT = stamp; // first ever measurement time = reference time of the intensity stamps (LidarTypes.h)
     auto &th = t_hist.at(id);
     if (th.size() > 100)
       th.pop_front();
     th.push_back(stamp);
-    auto scan = std::make_shared<LiDARData>();
-    scan->time = stamp, scan->id = id;
-    scan->xyz.assign(xyz, xyz + 3 * (size_t)n);
-    stack_lidar_raw.push_back(scan);
+    stack_lidar_raw.push_back(make_scan(id, stamp, xyz, n, stride));
 
     for (auto it = stack_lidar_raw.begin(); it != stack_lidar_raw.end();) {
       if (state->clones_empty())
@@ -74,14 +101,12 @@ public:
   // Initializer::init_lidar_sim (mins/src/init/Initializer.cpp:308-340; the Initializer is a friend of the reference's
   // UpdaterLidar): the dense ground-truth scan becomes the map as it is - LiDARData ctor (range filter) + init_map_local, no
   // down-sampling - and sets the reference time FT.
-  void init_map_gt(int id, double stamp, const float *xyz, int n) {
+  void init_map_gt(int id, double stamp, const float *xyz, int n, int stride = 3) {
     if (FT < 0)
       FT = stamp;
-    auto scan = std::make_shared<LiDARData>();
-    scan->time = stamp, scan->id = id;
-    scan->xyz.assign(xyz, xyz + 3 * (size_t)n);
+    auto scan = make_scan(id, stamp, xyz, n, stride);
     auto &ikd = ikd_data.at(id);
-    ck(api.scan_upload(ikd->tree, scan->xyz.data(), 3, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
+    ck(api.scan_upload(ikd->tree, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
                        nullptr),
        "ml_scan_upload", ikd->tree);
     resident[ikd->id] = nullptr;
@@ -162,7 +187,7 @@ private:
     std::vector<float> knots;
     if (op.raw_remove_motion_blur && !deskew_knots(scan, knots))
       return false;
-    ck(api.scan_upload(ikd->tree, scan->xyz.data(), 3, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
+    ck(api.scan_upload(ikd->tree, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
                        nullptr),
        "ml_scan_upload", ikd->tree);
     if (!knots.empty())
@@ -417,7 +442,7 @@ private:
     std::memset(&cnt, 0, sizeof(cnt));
     int rc;
     if (!op.map_use_icp && !op.raw_remove_motion_blur) {
-      rc = api.scan_update(ikd->tree, lidar->xyz.data(), 3, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
+      rc = api.scan_update(ikd->tree, lidar->xyz, 4, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
                            (float)op.max_range, op.raw_do_downsample ? (float)op.raw_downsample_size : 0.f, pend.T_LtoM, &c,
                            P.data(), HtH.data(), Htr.data(), &cnt);
     } else {
@@ -453,6 +478,8 @@ private:
 
   StateView *state;
   ml_api api;
+  int cap_scan;
+  std::vector<float *> pool; // free pinned scan buffers (ml_host_alloc), each max_scan_points PointXYZ
 };
 
 } // namespace mins_gpu

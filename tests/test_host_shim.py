@@ -14,7 +14,7 @@ def run(name, *args):
 
 
 def test_shim_links_against_the_real_abi():
-    assert "ml_api bound: 19 entries" in run("shim_link_check")
+    assert "ml_api bound: 21 entries" in run("shim_link_check")
 
 
 def test_queueing_policy_trace():
@@ -93,3 +93,6 @@ def test_queueing_policy_trace():
     expect("h0 scan_transform")
     expect("h0 linsys")
     expect("h0 map_add_scan")
+    # queued scans live in pooled pinned buffers, PointXYZ layout: few allocations for the ten scans fed, and the device is
+    # handed stride-4 points
+    assert int(expect("host_allocs=").split("=")[1]) <= 3 and "stride=3" not in out and "stride=4" in out
