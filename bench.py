@@ -261,6 +261,61 @@ def aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx, reps=10):
     return aux
 
 
+def aux_config1(device, reps=20):
+    """BASELINE.json configs[1]: 2 x VLP-16 (32 000 rays) against the KAIST-shaped map, for the simulation option set and the
+    KAIST option set (mins/config/kaist/config_lidar.yaml:11-29: leaf 2.0, map voxel 0.5, map_ngbr_max_d 10 -> the cube walk
+    reaches 7 cells), each with and without raw down-sampling. e2e = wall clock of ml_scan_update from pinned host memory,
+    device = CUDA events around the whole step. knn_fail_share = queries get_neighbors rejects (for the KAIST radius these are
+    the ones that walked to the last level)."""
+    import torch
+    from mins_b200 import capi, synth
+    from mins_b200.lidar import LidarMap, OptionsLidar, kaist_options
+    res = {}
+    for name, mk, radius in (("sim_options", lambda ds: OptionsLidar(raw_do_downsample=ds), None),
+                             ("kaist_options", lambda ds: kaist_options(raw_do_downsample=ds), 30.0)):
+        for ds in (True, False):
+            op = mk(ds)
+            w = synth.make_workload("G-vlp", op=op, map_radius=radius)
+            if name == "kaist_options":  # sparse map ahead of the sensor: part of the scan searches to the last level
+                mp = w["map"]
+                w["map"] = np.ascontiguousarray(mp[(mp[:, 0] < 3.0) | (np.arange(len(mp)) % 40 == 0)])
+            n, hx = int(w["n_rays"]), w["total_hx"]
+            m = LidarMap(max_scan_points=n, max_map_points=len(w["map"]) + 2 * n, device=device)
+            m.Build(w["map"])
+            pinned = torch.from_numpy(w["raw"]).pin_memory()
+            out = (np.zeros((hx, hx)), np.zeros(hx), capi.ml_counters())
+            T = np.ascontiguousarray(w["T_LtoM"], np.float32)
+            P = np.ascontiguousarray(w["P"], np.float64)
+            leaf = op.raw_downsample_size if ds else 0.0
+            m.set_timing(2)
+            tw, td = [], []
+            for it in range(5 + reps):
+                t0 = time.perf_counter()
+                rc = m.lib.ml_scan_update(m.h, pinned.data_ptr(), 4, n, w["t_rel"], op.min_range, op.max_range, leaf, T.ctypes.data,
+                                          C.byref(w["consts"]), P.ctypes.data, out[0].ctypes.data, out[1].ctypes.data, C.byref(out[2]))
+                dt_ = time.perf_counter() - t0
+                assert rc in (0, 1)
+                if it >= 5:
+                    tw.append(dt_)
+                    td.append(m.timing()["total"])
+            c = out[2]
+            res[f"{name}_{'mode_B_leaf_%.1f' % leaf if ds else 'mode_A'}"] = {
+                "e2e_ms_per_scan": float(np.median(tw) * 1e3), "device_ms_per_scan": float(np.median(td)), "rays": n,
+                "map_points": int(len(w["map"])), "queries": int(c.n_points), "accepted": int(c.n_acc),
+                "knn_fail_share": float(c.n_knn_fail / max(c.n_points, 1)), "raw_points_per_s_e2e": float(n / np.median(tw))}
+            m.close()
+    return res
+
+
+def aux_monte_carlo(runs=8, per_gpu=8, duration=20.0):
+    """BASELINE.json configs[4] in small: independent closed-loop runs of the host-C++ harness on this GPU (scripts/mc_sim_cpp.py)"""
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "mc_sim_cpp.py"), "--gpus", "1", "--runs", str(runs), "--per-gpu",
+                        str(per_gpu), "--duration", str(duration)], capture_output=True, text=True, timeout=600)
+    if p.returncode != 0:
+        return {"error": p.stderr[-300:]}
+    return json.loads(p.stdout.strip().splitlines()[-1])
+
+
 def emit(line):
     """the one JSON line, on the process's ORIGINAL stdout (see main: fd 1 is pointed at stderr while the run lasts)"""
     os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
@@ -412,6 +467,29 @@ def main():
         e2e_s += dt_
         e2e_steps.append(dt_)
         sampler.sample()
+    # ---- the same call for the other kinds of input an integrator may hand over (median of `steps` calls each; informational,
+    #      in e2e.by_input): pageable packed xyz (stride 3: one host memcpy into the handle's pinned staging buffer, then the
+    #      kernel reads that) and device-resident input as wall clock ------------------------------------------------------------
+    by_input = {"pinned_stride4_ms": float(np.median(e2e_steps) * 1e3)}
+    xyz3 = np.ascontiguousarray(w["raw"][:, :3])
+
+    def step3():
+        rc = lib.ml_scan_update(h, xyz3.ctypes.data, 3, n, w["t_rel"], op.min_range, op.max_range, 0.0, T.ctypes.data, C.byref(cns),
+                                P.ctypes.data, out[0].ctypes.data, out[1].ctypes.data, C.byref(out[2]))
+        if rc != 0:
+            raise RuntimeError(f"ml_scan_update -> {rc}: {lib.ml_last_error(h).decode()}")
+
+    for name, fn in (("pageable_stride3_ms", step3), ("device_resident_ms", lambda: step(dev_ptr))):
+        ts_ = []
+        for it in range(3 + args.steps):
+            flush_l2()
+            t0 = time.perf_counter()
+            fn()
+            if it >= 3:
+                ts_.append(time.perf_counter() - t0)
+        by_input[name] = float(np.median(ts_) * 1e3)
+    by_input["note"] = ("wall clock of the blocking ml_scan_update call; the C++ shim (mins_gpu::UpdaterLidar) queues scans in pooled "
+                        "pinned PointXYZ buffers (ml_host_alloc), so its update() call is the pinned_stride4 case")
     if gc_off:
         gc.enable()
     barrier()
@@ -460,10 +538,12 @@ def main():
             "config": workload_desc(w, world, n, n_acc),
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(n * 16 + C.sizeof(capi.ml_scan_consts) + hx * hx * 8 + 32),
-                    "d2h_bytes_per_step": int(8 * (hx * hx + hx) + C.sizeof(capi.ml_counters) + 40), "ms_per_step": e2e_ms_max / args.steps,
+                    "d2h_bytes_per_step": int(148 * (8 * 57 + 24)), "ms_per_step": e2e_ms_max / args.steps,
                     "step_ms_min_median_max": [float(np.min(e2e_steps) * 1e3), float(np.median(e2e_steps) * 1e3), float(np.max(e2e_steps) * 1e3)],
-                    "ms_mean_max_argmax_by_rank": by_rank, "host_cpu_affinity_rank0": affinity,
-                    "d2h": "none as a copy: the kernel's last CTA writes the result block into pinned host memory over PCIe"},
+                    "ms_mean_max_argmax_by_rank": by_rank, "host_cpu_affinity_rank0": affinity, "by_input": by_input,
+                    "h2d": "none as a copy: the fused front kernel reads the pinned scan over PCIe itself (TMA bulk copies, tile by tile)",
+                    "d2h": "none as a copy: every CTA of the rows kernel writes its reduced system into pinned host memory over PCIe; "
+                           "the library's host tail adds them in CTA order and applies the chain rule T^T G T"},
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k_: v / args.steps for k_, v in stage.items()},
             "wall_ms_total_incl_l2_flush": wall_total * 1e3,
@@ -477,6 +557,14 @@ def main():
                 line["aux"] = aux_measurements(m, w, op, step, host_ptr, out, flush_l2, hx)
             except Exception as e:  # informational block, never required for the headline
                 line["aux"] = {"error": repr(e)}
+            try:
+                line["aux"]["config1_2xVLP16_200k_map"] = aux_config1(local_rank)
+            except Exception as e:
+                line["aux"]["config1_2xVLP16_200k_map"] = {"error": repr(e)}
+            try:
+                line["aux"]["monte_carlo_cpp_harness"] = aux_monte_carlo()
+            except Exception as e:
+                line["aux"]["monte_carlo_cpp_harness"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
             try:
                 val, ms, _, sample, n_acc_cpu = cpu_reference_run(w, 3, 1, threads)

@@ -99,7 +99,9 @@ typedef struct ml_counters {
   int n_chi_rej;    /* Chi2Check false (incl. NaN) */
   int n_acc;        /* accepted points (3 rows each in the reference's H_big) */
   double sum_chi, sum_chi2; /* over all points that reached the chi2 test */
-  double sum_res, sum_res2; /* over the 3 projected residuals of those points (sum of r', sum of r'^2) */
+  double sum_res, sum_res2; /* over the k - 2 projected residuals of those points: sum of r' (filled only with residual statistics on,
+                               ml_set_stats: it depends on the reference's Givens basis, which costs a third of the rows kernel on
+                               top; 0 otherwise) and sum of r'^2 (always) */
 } ml_counters;
 
 /* per-point debug/parity export (ml_point_rows) */
@@ -274,6 +276,10 @@ int ml_set_timing(ml_handle *h, int on);
  * that follow (on = 1 arms, 0 disarms); out (may be NULL) receives the stamps of the last scan as [kernel: 0 kNN, 1 rows][cta <
  * 2048][slot < 8] and clears them. Returns the number of values written. Costs one predicated store per mark when disarmed. */
 int ml_debug_timeline(ml_handle *h, int on, unsigned long long *out, int cap);
+/* Residual statistics of UpdaterStatistics::Chi2Check (res_stat->add_stat(res), UpdaterStatistics.cpp:54-57): on = 1 makes
+ * ml_linsys / ml_scan_update also return ml_counters.sum_res - the first moment of the projected residuals in the reference's own
+ * nullspace basis (StateHelper::Givens_Rotation, StateHelper.cpp:660-680), run per point on the device. Default off. */
+int ml_set_stats(ml_handle *h, int on);
 /* sizeof of {ml_scan_consts, ml_point_row, ml_counters, ml_config} as compiled, for FFI layout checks */
 void ml_abi_sizes(int out[4]);
 /* number of kernel launches issued by this handle so far */

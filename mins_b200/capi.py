@@ -79,7 +79,7 @@ SYMBOLS = [
     "ml_scan_upload", "ml_scan_deskew", "ml_scan_downsample", "ml_scan_transform", "ml_scan_download", "ml_scan_set",
     "ml_knn", "ml_linsys", "ml_scan_update", "ml_point_rows", "ml_info_to_sqrt", "ml_last_timing", "ml_set_timing",
     "ml_abi_sizes", "ml_launch_count", "ml_sim_set_world", "ml_sim_set_rays", "ml_sim_raycast", "ml_sim_raycast_sweep", "ml_sim_scan_device",
-    "ml_icp_default_options", "ml_scan_icp", "ml_debug_timeline", "ml_host_alloc", "ml_host_free",
+    "ml_icp_default_options", "ml_scan_icp", "ml_debug_timeline", "ml_host_alloc", "ml_host_free", "ml_set_stats",
 ]
 
 _lib = None
@@ -133,6 +133,7 @@ def load():
     lib.ml_icp_default_options.restype = None
     lib.ml_scan_icp.argtypes = [vp, vp, C.POINTER(ml_icp_options), C.POINTER(ml_icp_result)]
     lib.ml_debug_timeline.argtypes = [vp, C.c_int, vp, C.c_int]
+    lib.ml_set_stats.argtypes = [vp, C.c_int]
     lib.ml_host_alloc.argtypes = [C.c_size_t]
     lib.ml_host_alloc.restype = vp
     lib.ml_host_free.argtypes = [vp]

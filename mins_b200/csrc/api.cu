@@ -119,6 +119,7 @@ struct ml_handle {
   bool rows_exported = false;
   bool rows_attr[ML_MAX_K + 1][8] = {};
   // debug timeline (ml_debug_timeline): per-CTA %globaltimer stamps of the kNN and rows kernels
+  bool stats_on = false; // ml_set_stats
   bool tl_on = false;
   unsigned long long *tl_rows = nullptr, *tl_knn = nullptr;
   int rows_block = 0; // 0 = chosen per scan size; MINS_ROWS_BLOCK=512|1024 pins it (profiling) // cudaFuncAttributeMaxDynamicSharedMemorySize set for k_rows_reduce<K, NB> on THIS handle's device
@@ -1274,7 +1275,7 @@ static int consts_host(ml_handle *h, const ml_scan_consts *c, const double *P) {
 static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
   const ml_scan_consts &c = h->consts;
   const int hx = c.total_hx, nb = h->rows_nb;
-  const int NG = c.calib_col >= 0 ? ML_G : 9, NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 3;
+  const int NG = c.calib_col >= 0 ? ML_G : 9, NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 4;
   double sum[ML_NRED];
   int cs[5] = {0, 0, 0, 0, 0};
   for (int e = 0; e < NRED; e++)
@@ -1290,7 +1291,7 @@ static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *c
   if (cnt) {
     cnt->n_points = h->last_n_scan;
     cnt->n_acc = cs[0], cnt->n_knn_fail = cs[1], cnt->n_plane_fail = cs[2], cnt->n_badmatch = cs[3], cnt->n_chi_rej = cs[4];
-    cnt->sum_chi = sum[NE + 0], cnt->sum_chi2 = sum[NE + 1], cnt->sum_res = 0.0, cnt->sum_res2 = sum[NE + 2];
+    cnt->sum_chi = sum[NE + 0], cnt->sum_chi2 = sum[NE + 1], cnt->sum_res = sum[NE + 3], cnt->sum_res2 = sum[NE + 2];
   }
   if (HtH || Htr) {
     double G[ML_G][ML_G], GT[ML_G][ML_MAX_HX];
@@ -1343,10 +1344,12 @@ static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *c
 // rows kernel + the wait + the host tail; the kNN results of the resident scan must be in flight on the stream
 static int rows_and_wait(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
   const int k = h->consts.map_ngbr_num;
-  int rc = launch_rows_k(h, k, nullptr);
+  // residual statistics on (ml_set_stats): the variant that also runs the reference's Givens sequence per point and keeps the
+  // per-point rows; otherwise the lean one
+  int rc = launch_rows_k(h, k, h->stats_on ? h->rows : nullptr);
   if (rc)
     return rc;
-  h->rows_exported = false;
+  h->rows_exported = h->stats_on;
   if (h->timing == 1)
     cudaEventRecord(h->ev[6], h->stream);
   // no D2H copy: every CTA wrote its reduced system straight into the pinned result area
@@ -1647,6 +1650,13 @@ void ml_abi_sizes(int out[4]) {
   out[1] = (int)sizeof(ml_point_row);
   out[2] = (int)sizeof(ml_counters);
   out[3] = (int)sizeof(ml_config);
+}
+
+int ml_set_stats(ml_handle *h, int on) {
+  if (!h)
+    return ML_ERR_ARG;
+  h->stats_on = on != 0;
+  return ML_OK;
 }
 
 int ml_set_timing(ml_handle *h, int on) {

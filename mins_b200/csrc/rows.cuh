@@ -131,8 +131,31 @@ struct RowConsts {
 struct RowOut {
   double W, V, chi2, rss, raw_n, res5;
   double n[3], d;
+  double sum_rp; // STATS: sum of the K - 2 projected residuals r' in the reference's own nullspace basis
 };
-template <int K, int NB>
+// Eigen::JacobiRotation<double>::makeGivens(p, q), real case: G = [c s; -s c] with G^* [p; q] = [r; 0]
+__device__ __forceinline__ void make_givens(double p, double q, double &c, double &s) {
+  if (q == 0.0) {
+    c = p < 0 ? -1.0 : 1.0, s = 0.0;
+  } else if (p == 0.0) {
+    c = 0.0, s = q < 0 ? 1.0 : -1.0;
+  } else if (fabs(p) > fabs(q)) {
+    const double t = q / p;
+    double u = sqrt(1.0 + t * t);
+    u = p < 0 ? -u : u;
+    c = 1.0 / u, s = -t * c;
+  } else {
+    const double t = p / q;
+    double u = sqrt(1.0 + t * t);
+    u = q < 0 ? -u : u;
+    s = -1.0 / u, c = -t * s;
+  }
+}
+// STATS (residual statistics switched on, ml_set_stats): also the FIRST moment of the projected residuals, which - unlike
+// ||r'||^2 and chi2 - depends on the basis of the left nullspace, so the reference's own Givens sequence
+// (StateHelper::Givens_Rotation, StateHelper.cpp:660-680: columns left to right, rows bottom up) is run on the whitened
+// (K + 1) x 3 H_f and the residual; costs about a third of the point on top.
+template <int K, int NB, bool STATS>
 __device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, const float4 (&nb)[K], double *__restrict__ g,
                                          RowOut &o) {
   // ---- neighbours: Gram matrix, column sums, mean range (LidarHelper.cpp:293-302) ----
@@ -201,7 +224,7 @@ __device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, 
   if (res5 > rc.badmatch)
     return 3;
   // ---- leverage of the scan-point row: || L^-1 pfinM_fej ||^2 ----
-  double zz;
+  double zz, fej[3];
   {
     const double fx = fma(rc.RLtoM_fej[0], qx, fma(rc.RLtoM_fej[1], qy, fma(rc.RLtoM_fej[2], qz, rc.pLinM_fej[0])));
     const double fy = fma(rc.RLtoM_fej[3], qx, fma(rc.RLtoM_fej[4], qy, fma(rc.RLtoM_fej[5], qz, rc.pLinM_fej[1])));
@@ -210,6 +233,7 @@ __device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, 
     const double y1 = fma(-l10, y0, fy) * i1;
     const double y2 = fma(-l21, y1, fma(-l20, y0, fz)) * i2;
     zz = fma(y0, y0, fma(y1, y1, y2 * y2));
+    fej[0] = fx, fej[1] = fy, fej[2] = fz;
   }
   // ---- g = n [dpfinM_dI | dpfinM_dA | dpfinM_dcalib], folded (UpdaterLidar.cpp:320-329; ML_G in common.cuh) ----
   {
@@ -272,6 +296,41 @@ __device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, 
   }
   s *= ir * ir;
   const double chi2 = rss - s * vr * vr / fma(s, wv, 1.0);
+  if (STATS) {
+    double A[K + 1][3], r[K + 1];
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+      A[j][0] = (double)px[j] * im, A[j][1] = (double)py[j] * im, A[j][2] = (double)pz[j] * im;
+      r[j] = -fma(n0, (double)px[j], fma(n1, (double)py[j], fma(n2, (double)pz[j], d))) * im;
+    }
+    A[K][0] = fej[0] * ir, A[K][1] = fej[1] * ir, A[K][2] = fej[2] * ir;
+    r[K] = res5 * ir;
+#pragma unroll
+    for (int cn = 0; cn < 3; cn++) {
+#pragma unroll
+      for (int m = K; m > cn; m--) {
+        if (A[m][cn] == 0.0)
+          continue;
+        double c, s;
+        make_givens(A[m - 1][cn], A[m][cn], c, s);
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+          if (q < cn)
+            continue;
+          const double x = A[m - 1][q], y = A[m][q];
+          A[m - 1][q] = c * x - s * y, A[m][q] = s * x + c * y;
+        }
+        A[m][cn] = 0.0;
+        const double x = r[m - 1], y = r[m];
+        r[m - 1] = c * x - s * y, r[m] = s * x + c * y;
+      }
+    }
+    double sr = 0.0;
+#pragma unroll
+    for (int m = 3; m <= K; m++)
+      sr += r[m];
+    o.sum_rp = sr;
+  }
   o.W = wv * ir * ir;
   o.V = vr * ir;
   o.chi2 = chi2;
@@ -299,8 +358,8 @@ __device__ __forceinline__ int point_row(const RowConsts &rc, const float4 pl4, 
 // ------------------------------------------------------------------------------------------------
 constexpr int RR_BLOCK = 512, RR_BLOCK_MID = 896, RR_BLOCK_BIG = 1024; // 16, 28 or 32 warps per SM (one CTA per SM either way)
 constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diagonal blocks)
-// reduced entries for NB block rows: upper triangle of G (NG (NG + 1) / 2), b (NG), sum_chi, sum_chi2, sum_res2
-#define ML_NRED (ML_GSYM + ML_G + 3)
+// reduced entries for NB block rows: upper triangle of G (NG (NG + 1) / 2), b (NG), sum_chi, sum_chi2, sum_res2, sum_res
+#define ML_NRED (ML_GSYM + ML_G + 4)
 // What one CTA returns: its reduced system in the folded pose space (G = sum W g g^T upper triangle by rows, b = sum g V),
 // the chi2 statistics and the status counters. Lives in PINNED HOST memory: the CTA's last act is ~0.5 KB of posted PCIe
 // writes; no ticket, no fence, no serial tail on the device. The library's host tail (rows_host_tail, api.cu) adds the
@@ -313,7 +372,7 @@ struct RRPart {
 // per-warp slab: g rows (odd stride: conflict-free stores) | W | V | running sums (one slot per lane) | statistics
 template <int NB> struct RRLayout {
   static constexpr int NG = 3 * NB;
-  static constexpr int NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 3;
+  static constexpr int NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 4;
   static constexpr int ROW = NG + 2;
   static constexpr int SLAB = 32 * ROW + 32 + 32 + 32 * RR_RACC + 8; // + chi, chi^2, rss | 5 status counters (as int)
   static constexpr size_t smem(int warps) { return sizeof(double) * (size_t)(warps * SLAB); }
@@ -402,14 +461,14 @@ __global__ void __launch_bounds__(BLOCK, 1)
     int status = 1;
     double g[NG];
     RowOut ro;
-    ro.W = ro.V = ro.chi2 = ro.rss = ro.raw_n = ro.res5 = ro.d = 0.0;
+    ro.W = ro.V = ro.chi2 = ro.rss = ro.raw_n = ro.res5 = ro.d = ro.sum_rp = 0.0;
     ro.n[0] = ro.n[1] = ro.n[2] = 0.0;
 #pragma unroll
     for (int a = 0; a < NG; a++)
       g[a] = 0.0;
     // the kNN kernel marks a query get_neighbors rejects (LidarHelper.cpp:280-285) with a NaN first coordinate
     if (i < n && nb0[0].x == nb0[0].x)
-      status = point_row<K, NB>(rc, pl0, nb0, g, ro);
+      status = point_row<K, NB, EXPORT>(rc, pl0, nb0, g, ro);
     const bool okp = status == 0;
     if (EXPORT && i < n) { // parity export only: whitened g like the reference's H row
       PointRow pr;
@@ -438,18 +497,22 @@ __global__ void __launch_bounds__(BLOCK, 1)
     sv[lane] = okp ? ro.V : 0.0;
     {
       const bool tested = (status == 0 || status == 4) && (ro.chi2 == ro.chi2);
-      double vchi = tested ? ro.chi2 : 0.0, vrss = tested ? ro.rss : 0.0;
+      double vchi = tested ? ro.chi2 : 0.0, vrss = tested ? ro.rss : 0.0, vsr = (EXPORT && tested) ? ro.sum_rp : 0.0;
       double vchi2 = vchi * vchi;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         vchi += __shfl_xor_sync(0xffffffffu, vchi, o);
         vchi2 += __shfl_xor_sync(0xffffffffu, vchi2, o);
         vrss += __shfl_xor_sync(0xffffffffu, vrss, o);
+        if (EXPORT)
+          vsr += __shfl_xor_sync(0xffffffffu, vsr, o);
       }
       if (lane == 0) {
         sstat[0] += vchi;
         sstat[1] += vchi2;
         sstat[2] += vrss;
+        if (EXPORT)
+          sstat[6] += vsr; // slots 3-5 hold the integer status counters
       }
       // status counters: lane q < 5 counts status q
       int mine = 0;
@@ -537,7 +600,7 @@ __global__ void __launch_bounds__(BLOCK, 1)
         v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + (gq * ROLES + erole) * RR_RACC + q];
     mine->v[t] = v;
   } else if (t < NRED) {
-    const int q = t - NE;
+    const int q = t - NE == 3 ? 6 : t - NE; // the fourth statistic (sum_res) sits behind the integer counters in the slab
     double v = 0.0;
     for (int w = 0; w < WARPS; w++)
       v += slabs[(size_t)w * SLAB + 32 * ROW + 64 + 32 * RR_RACC + q];

@@ -337,6 +337,10 @@ class LidarMap:
         self.lib.ml_last_timing(self.h, ms)
         return dict(zip(["upload_filter", "downsample", "transform", "bin", "knn", "rows_reduce", "d2h", "total"], list(ms)))
 
+    def set_stats(self, on):
+        """residual statistics of UpdaterStatistics::Chi2Check (ml_counters.sum_res) on/off"""
+        self.lib.ml_set_stats(self.h, int(on))
+
     def set_timing(self, on):
         self.lib.ml_set_timing(self.h, int(on))
 

@@ -242,3 +242,26 @@ def test_chi2_gate_uses_the_projected_row_count(make_map, po, workload, k):
     assert cnt.n_chi_rej > 0.3 * tested.sum() and cnt.n_acc > 0.3 * tested.sum()
     assert np.array_equal(rows["status"][tested] == 0, rows["chi2"][tested] < c2.chi2_mult * q)
     assert rel(HtH, ref["HtH"]) <= TOL and rel(Htr, ref["Htr"]) <= TOL
+
+
+@pytest.mark.parametrize("variant,k", [("plain", 5), ("calib", 5), ("overlap", 7), ("plain", 3)])
+def test_residual_statistics_first_moment(make_map, po, workload, variant, k):
+    """ml_counters.sum_res: res_stat->add_stat(res) of UpdaterStatistics::Chi2Check (UpdaterStatistics.cpp:54-57) sums the
+    projected residuals r' themselves - a number that depends on the basis StateHelper::Givens_Rotation (StateHelper.cpp:660-680)
+    leaves, so the device runs that very rotation sequence (statistics on); off, the field stays 0 and nothing else changes."""
+    w = workload("G-small", variant=variant, k=k)
+    m = make_map(max_scan_points=1 << 14, max_map_points=1 << 16)
+    m.Build(w["map"])
+    rc, HtH0, Htr0, cnt0 = m.scan_update(w["raw"], w["t_rel"], w["op"], w["T_LtoM"], w["consts"], w["P"])
+    assert rc == 0 and cnt0.sum_res == 0.0
+    m.set_stats(True)
+    rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], w["op"], w["T_LtoM"], w["consts"], w["P"])
+    ref = po.scan_linsys(w["consts"], w["P"], w["map"], m.scan(0), m.scan(1))
+    oc = ref["cnt"]
+    assert cnt.n_acc == oc.n_acc == cnt0.n_acc
+    scale = np.sqrt(oc.sum_res2 * (cnt.n_acc + cnt.n_chi_rej) * (k - 2))       # Cauchy-Schwarz bound of |sum r'|
+    assert abs(cnt.sum_res - oc.sum_res) <= 1e-9 * scale and abs(oc.sum_res) > 1e-6 * scale
+    assert cnt.sum_res2 == pytest.approx(oc.sum_res2, rel=TOL) and cnt.sum_chi == pytest.approx(oc.sum_chi, rel=TOL)
+    assert rel(HtH, ref["HtH"]) <= TOL and rel(HtH, HtH0) <= 1e-12 and rel(Htr, Htr0) <= 1e-11
+    rows, h = m.point_rows()                                                       # the rows are already there
+    assert np.array_equal(rows["status"], ref["rows"]["status"])
