@@ -22,6 +22,8 @@ WANT = {
     "dram__bytes_read.sum": "dram_read",
     "dram__bytes_write.sum": "dram_write",
     "lts__t_bytes.sum": "l2_bytes",
+    "lts__t_sectors.sum": "l2_sectors",
+    "lts__t_sector_hit_rate.pct": "l2_hit_pct",
     "launch__registers_per_thread": "regs",
     "sm__warps_active.avg.pct_of_peak_sustained_active": "occ",
     "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue",
@@ -59,6 +61,8 @@ def main():
             if k != "launches":
                 d[k] /= n
         d["dram_bytes_per_launch"] = d.get("dram_read", 0.0) + d.get("dram_write", 0.0)
+        if "l2_bytes" not in d and "l2_sectors" in d:  # `--set full` carries the sector count, not lts__t_bytes: 32 B per sector
+            d["l2_bytes"] = 32.0 * d["l2_sectors"]
     out = {"all": acc, "source": os.path.basename(rep)}
     for alias, pat in (("knn", "k_knn<5>"), ("knn", "k_front_knn<5"), ("rows_reduce", "k_rows_reduce<5"), ("front", "k_range_filter_bin")):
         for name, d in acc.items():
@@ -66,7 +70,7 @@ def main():
                 out[alias] = d
     json.dump(out, open(out_path, "w"), indent=1)
     for name, d in acc.items():
-        print(f"{name:40s} x{d['launches']} {d.get('time_us', 0):8.1f} us  dram {d['dram_bytes_per_launch'] / 1e6:7.2f} MB  regs {d.get('regs', 0):4.0f} "
+        print(f"{name:40s} x{d['launches']} {d.get('time_us', 0):8.1f} us  dram {d['dram_bytes_per_launch'] / 1e6:7.2f} MB  l2 {d.get('l2_bytes', 0) / 1e6:7.2f} MB  regs {d.get('regs', 0):4.0f} "
               f"occ {d.get('occ', 0):5.1f}% issue {d.get('issue', 0):5.1f}% fp64 {d.get('fp64', 0):5.1f}% lanes {d.get('lanes', 0):5.1f}")
 
 

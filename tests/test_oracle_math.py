@@ -249,3 +249,61 @@ def test_oracle_plane_gate_on_rank_deficient_neighbours(po):
         mp[:, :3] = nbp
         ok, plane, cond = po.compute_plane(mp)
         assert not ok and cond > 1e12
+
+
+def _newton_eig_minmax(G):
+    """numpy restatement of rows.cuh sym3_eig_minmax: roots of 4c^3 - 3c = r by Newton instead of cos(acos(r)/3)."""
+    a00, a01, a02, a11, a12, a22 = G[0, 0], G[0, 1], G[0, 2], G[1, 1], G[1, 2], G[2, 2]
+    p1 = a01 * a01 + a02 * a02 + a12 * a12
+    q = (a00 + a11 + a22) / 3.0
+    b00, b11, b22 = a00 - q, a11 - q, a22 - q
+    p2 = b00 * b00 + b11 * b11 + b22 * b22 + 2.0 * p1
+    if not p2 > 0.0:
+        return q, q
+    p = np.sqrt(p2 / 6.0)
+    det = b00 * (b11 * b22 - a12 * a12) - a01 * (a01 * b22 - a12 * a02) + a02 * (a01 * a12 - b11 * a02)
+    r = min(1.0, max(-1.0, 0.5 * det / p**3))
+    c = np.float32(0.5) + np.sqrt((np.float32(1.0) + np.float32(r)) / np.float32(6.0))
+    rf = np.float32(r)
+    for _ in range(3):
+        c2 = c * c
+        c = np.float32(c - ((np.float32(4) * c2 - np.float32(3)) * c - rf) / (np.float32(12) * c2 - np.float32(3) + np.float32(1e-30)))
+    c = max(0.5, float(c))
+    for _ in range(2):
+        fp = 12.0 * c * c - 3.0
+        if fp > 1e-300:
+            c = c - ((4.0 * c * c - 3.0) * c - r) / fp
+    c = min(1.0, max(0.5, c))
+    return q - p * (np.sqrt(3.0) * np.sqrt(max(0.0, 1.0 - c * c)) + c), q + 2.0 * p * c
+
+
+@pytest.mark.parametrize("k", [3, 5, 10])
+def test_gram_route_matches_qr_route(po, k):
+    """The r2 device route of compute_plane (rows.cuh point_row): G = A^T A, condition gate from the extreme eigenvalues of G found by
+    Newton on 4c^3 - 3c = r, abc = -d G^-1 A^T 1 by a 3x3 Cholesky - against the oracle's SVD + column-pivoted QR restatement of
+    LidarHelper.cpp:291-328 on neighbour sets that pass the reference's gate (cond <= plane_max_condi)."""
+    rng = np.random.default_rng(100 + k)
+    n = 0
+    for trial in range(400):
+        off = rng.uniform(-6, 6, 3)
+        nb = plane_neighbours(rng, k, noise=rng.choice([0.0, 0.005, 0.02, 0.1]), offset=off)
+        max_condi = 100.0
+        ok, plane, cond = po.compute_plane(nb, max_condi, 1e9)
+        A = nb[:, :3].astype(np.float64)
+        G = A.T @ A
+        lmin, lmax = _newton_eig_minmax(G)
+        ev = np.linalg.eigvalsh(G)
+        assert lmax == pytest.approx(ev[-1], rel=1e-13)
+        assert lmin == pytest.approx(ev[0], rel=1e-9 * cond * cond, abs=1e-13 * ev[-1])
+        gate = lmin > 0.0 and not (lmax > max_condi**2 * lmin)
+        if abs(cond - max_condi) > 1e-6 * max_condi:
+            assert gate == (cond <= max_condi)
+        if not (gate and ok):
+            continue
+        d = np.linalg.norm(A, axis=1).mean()
+        L = np.linalg.cholesky(G)
+        abc = -d * np.linalg.solve(L.T, np.linalg.solve(L, A.sum(0)))
+        assert np.abs(abc - plane[:3]).max() <= 1e-15 * cond**2 * np.abs(plane[:3]).max() + 1e-300
+        assert np.abs(abc - plane[:3]).max() <= 3e-11 * np.abs(plane[:3]).max()
+        n += 1
+    assert n > 25
