@@ -24,7 +24,11 @@
 using namespace ml;
 
 static std::string g_global_error;
+#if defined(ML_KNN_PROF) && ML_KNN_PROF
+#define ML_TL_MAX_CTAS 8192
+#else
 #define ML_TL_MAX_CTAS 2048
+#endif
 
 struct ml_handle {
   ml_config cfg;

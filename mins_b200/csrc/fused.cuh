@@ -45,35 +45,25 @@ constexpr int FK_SLOTS = 2 * RF_TILE;     // 4096: shared-memory hash table, loa
 constexpr size_t FK_HASH_BYTES = (size_t)FK_SLOTS * (sizeof(unsigned long long) + 2 * sizeof(uint32_t)); // 64 KB
 constexpr size_t FK_STAGE_BYTES = (size_t)RF_TILE * sizeof(float4);                                          // 32 KB: the next tile's rays
 constexpr size_t FK_SMEM = FK_HASH_BYTES + FK_STAGE_BYTES;                                                   // 96 KB, two CTAs per SM
-
-// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (cp.async.bulk; SASS UBLKCP). One thread issues the copy
-// of a whole 32 KB tile; nobody's registers, load queue or memory fences are involved while it is in flight - which is the
-// point here: a __threadfence() waits for the issuing thread's outstanding LOADS too, so a register prefetch of the next tile
-// over PCIe (11 us) stalled the publication of the current one. ----
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+#ifndef ML_KNN_STAGED
+#define ML_KNN_STAGED 1
+#endif
+// -DML_KNN_PROF=1 (scripts/knn_warp_profile.py): instead of the per-CTA marks every consumer warp records, in the timeline buffer,
+// [ns waiting for tickets and tags, ns in the walk, ns emitting, units, candidates offered, first unit start, last unit end, 0]
+#ifndef ML_KNN_PROF
+#define ML_KNN_PROF 0
+#endif
+#if ML_KNN_PROF
+#define FK_MARK(tl, s) ((void)0)
+#else
+#define FK_MARK(tl, s) tl_mark(tl, s)
+#endif
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
-               "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
-  asm volatile("{\n"
-               ".reg .pred p;\n"
-               "MBAR_WAIT:\n"
-               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-               "@p bra MBAR_DONE;\n"
-               "bra MBAR_WAIT;\n"
-               "MBAR_DONE:\n"
-               "}" ::"r"(smem_u32(bar)),
-               "r"(parity)
-               : "memory");
-}
+static_assert((FK_BLOCK / 32) * KW_WARP_BYTES <= FK_SMEM, "the consumers' candidate buffers reuse the producer's shared memory");
 
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p) {
   uint32_t v;
@@ -109,11 +99,12 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
   uint32_t *hpre = hcnt + FK_SLOTS;                                           // [FK_SLOTS] (query base) | (unit base) << 16
   float4 *stage = reinterpret_cast<float4 *>(fk_smem + FK_HASH_BYTES);        // [RF_TILE] the next tile's rays (VEC4 input)
   __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ __align__(8) unsigned long long s_kbar[FK_BLOCK / 32][2]; // consumers: one mbarrier per half of a warp's candidate buffer
   __shared__ uint32_t wsum[FK_BLOCK / 32];
   __shared__ uint32_t s_next, s_prefix, s_gu, s_tu;
-  tl_mark(tl, 0);
+  FK_MARK(tl, 0);
   pdl_enter();
-  tl_mark(tl, 1);
+  FK_MARK(tl, 1);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const uint32_t ntiles = (uint32_t)((n + RF_TILE - 1) / RF_TILE);
   const GridDesc g = *gd;
@@ -160,7 +151,7 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
       if (lane == 0)
         wsum[wid] = cnt;
       __syncthreads();
-      tl_mark(tl, 4); // loads landed, range test done
+      FK_MARK(tl, 4); // loads landed, range test done
       const uint32_t next = s_next;
       if (VEC4 && next < ntiles && threadIdx.x == 0) { // the next tile's rays start their journey now (one bulk copy)
         const uint32_t bytes = (uint32_t)min(RF_TILE, n - (int)next * RF_TILE) * (uint32_t)sizeof(float4);
@@ -238,7 +229,7 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
         sr[r] = kept ? (s | ((b + (uint32_t)__popc(peers[r] & lt)) << 16)) : 0u;
       }
       __syncthreads();
-      tl_mark(tl, 5); // look-back done, hash filled
+      FK_MARK(tl, 5); // look-back done, hash filled
       // exclusive scan over the slots: queries and units (ceil(cnt / 32)) of every occupied slot, 8 consecutive slots per thread
       uint32_t my_gu = 0, my_tu = 0;
       {
@@ -267,7 +258,7 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
         }
       }
       __syncthreads();
-      tl_mark(tl, 6); // slots scanned
+      FK_MARK(tl, 6); // slots scanned
       // The tile's queries in cell order: its range of the cell-ordered array IS its range of the compacted clouds (same
       // count, unique by the look-back), so only the unit list needs a reservation. One unit record per 32 queries of a slot.
       const uint32_t gq = s_prefix;
@@ -306,7 +297,7 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
       // publish: only the query and unit stores are outstanding at this fence (the clouds are written after it)
       __threadfence();
       __syncthreads();
-      tl_mark(tl, 7); // queries and unit records visible
+      FK_MARK(tl, 7); // queries and unit records visible
       for (uint32_t j = threadIdx.x; j < tu; j += FK_BLOCK)
         units_tag[gu + j] = epoch;
       // the thread that reserved the units (thread 0) also counts the tile as done: its fence orders the reservation before
@@ -351,10 +342,26 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
       __syncthreads(); // this tile's shared state is dead; the staged rays are in registers
     }
   }
-  tl_mark(tl, 2);
+  FK_MARK(tl, 2);
 
   // ------------------------------------------------------------------------------------------ consumer
   const int R = max(1, (int)ceil(sqrt((double)max_d2) * (1.0 + 1e-5) * g.inv_cell));
+#if ML_KNN_STAGED
+  // The candidate buffers of the 16 warps (6 KB each) take over the producer's dynamic shared memory: the hash table and the
+  // stage are dead after a producer's last publication barrier, and a consumer-only CTA never used them.
+  float4 *kbuf = reinterpret_cast<float4 *>(fk_smem) + (size_t)wid * (2 * KW_CH);
+  uint32_t kpar = 0;
+  if (lane == 0) {
+    mbar_init(&s_kbar[wid][0], 1);
+    mbar_init(&s_kbar[wid][1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+#endif
+#if ML_KNN_PROF
+  unsigned long long pw_wait = 0, pw_walk = 0, pw_emit = 0, pw_units = 0, pw_first = 0, pw_last = 0, pw_t = gtimer(), pw_rec = 0;
+  unsigned long long pw_in[3] = {0, 0, 0};
+#endif
   for (;;) {
     // A ticket is taken only when an unclaimed unit has been reserved (two relaxed loads, backing off up to 2 us while the
     // producers are still at work): thousands of warps spinning on tags and tickets cost the producers their L2 round trips
@@ -392,6 +399,14 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
     __syncwarp();
     if (!have)
       break;
+#if ML_KNN_PROF
+    {
+      const unsigned long long t = gtimer();
+      pw_wait += t - pw_t, pw_t = t;
+      if (!pw_first)
+        pw_first = t;
+    }
+#endif
     // the unit record and its queries were written by another SM during this kernel: read them from L2 (an L1 line fetched for
     // an earlier unit may hold the bytes of this one from before they were written)
     KnnUnit un;
@@ -402,11 +417,40 @@ __global__ void __launch_bounds__(FK_BLOCK, 2)
     const bool active = lane < un.cnt;
     const float4 q = __ldcg(&q_sorted[un.qbase + (active ? lane : 0)]);
     TopK<K> best;
+#if ML_KNN_PROF
+    {
+      const unsigned long long t = gtimer() + (__float_as_int(q.x) == 0x7fffffff ? 1 : 0); // after the query has landed
+      pw_rec += t - pw_t, pw_t = t;
+    }
+    knn_walk_staged<K>(un, q, active, g, R, cell_start, cell_pts, best, kbuf, s_kbar[wid], kpar, pw_in);
+#elif ML_KNN_STAGED
+    knn_walk_staged<K>(un, q, active, g, R, cell_start, cell_pts, best, kbuf, s_kbar[wid], kpar);
+#else
     knn_walk<K>(un, q, active, g, R, cell_start, cell_pts, best);
+#endif
+#if ML_KNN_PROF
+    {
+      const unsigned long long t = gtimer();
+      pw_walk += t - pw_t, pw_t = t;
+    }
+#endif
     if (active)
       knn_emit<K>(best, __float_as_int(q.w), max_d2, knn_idx, knn_d2, knn_ok, map_pts, nbr);
+#if ML_KNN_PROF
+    {
+      __syncwarp();
+      const unsigned long long t = gtimer();
+      pw_emit += t - pw_t, pw_t = t, pw_last = t, pw_units++;
+    }
+#endif
   }
-  tl_mark(tl, 3);
+#if ML_KNN_PROF
+  if (tl && lane == 0) {
+    unsigned long long *o = tl + ((size_t)blockIdx.x * (FK_BLOCK / 32) + wid) * 8;
+    o[0] = pw_wait, o[1] = pw_walk, o[2] = pw_emit, o[3] = pw_units | (pw_rec << 16), o[4] = pw_in[0] | (pw_in[1] << 20) | (pw_in[2] << 40), o[5] = pw_first, o[6] = pw_last, o[7] = (unsigned long long)((int)blockIdx.x < producers);
+  }
+#endif
+  FK_MARK(tl, 3);
   // the last CTA to leave resets the control block for the next scan (every ticket has been taken by then)
   __syncthreads();
   if (threadIdx.x == 0) {

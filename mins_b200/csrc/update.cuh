@@ -606,6 +606,183 @@ __device__ __forceinline__ void knn_walk(const KnnUnit &un, const float4 q, cons
   }
 }
 
+// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier (cp.async.bulk; SASS UBLKCP). One thread issues the copy
+// of a whole 32 KB tile; nobody's registers, load queue or memory fences are involved while it is in flight - which is the
+// point here: a __threadfence() waits for the issuing thread's outstanding LOADS too, so a register prefetch of the next tile
+// over PCIe (11 us) stalled the publication of the current one. ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t parity) {
+  asm volatile("{\n"
+               ".reg .pred p;\n"
+               "MBAR_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+               "@p bra MBAR_DONE;\n"
+               "bra MBAR_WAIT;\n"
+               "MBAR_DONE:\n"
+               "}" ::"r"(smem_u32(bar)),
+               "r"(parity)
+               : "memory");
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// The same cube walk with the candidates STAGED IN SHARED MEMORY by TMA bulk copies (north_star's design for the search).
+// Why: knn_walk loads every candidate from a warp-uniform global address, so a warp has at most 4 x 16 bytes in flight and a
+// unit's walk is a chain of ~45 dependent L2 round trips (9 rows x ~5 groups of 4): at one unit per warp the search phase of a
+// 131 072-ray scan lasted 25-30 us although its instructions need 13 us of issue (profiles/r2_ncu.md). Here the lanes compute
+// the cube's rows (x-runs of cells = contiguous ranges of cell_pts), every lane hands its range(s) to the copy engine
+// (cp.async.bulk -> the warp's own buffer, completion on the warp's mbarrier), and the warp then tests the flat candidate list
+// from shared memory (one broadcast LDS.128 per candidate): one round trip per level instead of ~45.
+// The buffer is two halves of KW_CH candidates with one mbarrier each: chunk c + 2 is requested as soon as chunk c has been
+// tested. Arithmetic, completeness rule and (d2, index) order are those of knn_walk: results are bit-identical.
+// The unit's own cell is no special case here: at the first level the whole cube is staged, the row through the own cell first
+// (it holds the likeliest neighbours, so the k-th best is tight when the other rows are tested).
+// ------------------------------------------------------------------------------------------------
+constexpr int KW_CH = 192;                                     // candidates per half buffer
+constexpr size_t KW_WARP_BYTES = 2 * KW_CH * sizeof(float4);   // 6 KB per warp
+
+template <int K>
+__device__ __forceinline__ void knn_walk_staged(const KnnUnit &un, const float4 q, const bool active, const GridDesc &g, const int R,
+                                                const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts,
+                                                TopK<K> &best, float4 *buf, unsigned long long *bar, uint32_t &par,
+                                                unsigned long long *prof = nullptr) {
+  const int lane = threadIdx.x & 31;
+#if defined(ML_KNN_PROF) && ML_KNN_PROF
+#define KW_T(i)                                                                                                                       \
+  {                                                                                                                                   \
+    unsigned long long t_;                                                                                                            \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                                            \
+    if (prof)                                                                                                                         \
+      prof[i] += t_ - kw_t;                                                                                                           \
+    kw_t = t_;                                                                                                                        \
+  }
+  unsigned long long kw_t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(kw_t));
+#else
+#define KW_T(i)
+#endif
+  double fx = ((double)q.x - g.ox) * g.inv_cell - (double)un.cx;
+  double fy = ((double)q.y - g.oy) * g.inv_cell - (double)un.cy;
+  double fz = ((double)q.z - g.oz) * g.inv_cell - (double)un.cz;
+  double fmn = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
+  fmn = fmax(0.0, fmn);
+  best.init();
+  const int ox_ = max(max(-un.cx, un.cx - (g.dimx - 1)), 0), oy_ = max(max(-un.cy, un.cy - (g.dimy - 1)), 0),
+            oz_ = max(max(-un.cz, un.cz - (g.dimz - 1)), 0);
+  const int s_lo = max(1, max(ox_, max(oy_, oz_)));
+  const int s_hi = min(R, max(max(max(un.cx, g.dimx - 1 - un.cx), max(un.cy, g.dimy - 1 - un.cy)), max(un.cz, g.dimz - 1 - un.cz)));
+  const bool own_in_grid = un.cx >= 0 && un.cx < g.dimx && un.cy >= 0 && un.cy < g.dimy && un.cz >= 0 && un.cz < g.dimz;
+  for (int s = s_lo; s <= s_hi; s++) {
+    const int y0 = max(un.cy - s, 0), y1 = min(un.cy + s, g.dimy - 1);
+    const int z0 = max(un.cz - s, 0), z1 = min(un.cz + s, g.dimz - 1);
+    const int nz = z1 - z0 + 1;
+    const int nrows = (y1 >= y0 && nz > 0) ? (y1 - y0 + 1) * nz : 0;
+    // own_in_grid implies s_lo = 1: at most 9 rows, the own row's index fits the first batch
+    const int t_own = (s == s_lo && own_in_grid) ? (un.cy - y0) * nz + (un.cz - z0) : 0;
+    for (int rb = 0; rb < nrows; rb += 32) {
+      int t = rb + lane;
+      if (rb == 0)
+        t = (t == 0) ? t_own : (t == t_own ? 0 : t); // the own row goes first
+      uint32_t begA = 0, lenA = 0, begB = 0, lenB = 0;
+      if (t < nrows) {
+        const int y = y0 + t / nz, z = z0 + (t - (t / nz) * nz);
+        const int dy = y - un.cy, dz = z - un.cz;
+        const int rowbase = (z * g.dimy + y) * g.dimx;
+        const bool outer = (s == s_lo) || (abs(dy) == s) || (abs(dz) == s);
+        if (outer) {
+          const int x0 = max(un.cx - s, 0), x1 = min(un.cx + s, g.dimx - 1);
+          if (x0 <= x1) {
+            begA = cell_start[rowbase + x0];
+            lenA = cell_start[rowbase + x1 + 1] - begA;
+          }
+        } else {
+          const int xa = un.cx - s, xb = un.cx + s;
+          if (xa >= 0 && xa < g.dimx) {
+            begA = cell_start[rowbase + xa];
+            lenA = cell_start[rowbase + xa + 1] - begA;
+          }
+          if (xb >= 0 && xb < g.dimx) {
+            begB = cell_start[rowbase + xb];
+            lenB = cell_start[rowbase + xb + 1] - begB;
+          }
+        }
+      }
+      // flat candidate list of the batch: lane order, A before B
+      uint32_t incl = lenA + lenB;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o)
+          incl += v;
+      }
+      const uint32_t T = __shfl_sync(0xffffffffu, incl, 31);
+      KW_T(0); // rows set up: cell_start loads + scan
+      const uint32_t offA = incl - lenA - lenB, offB = offA + lenA;
+      const int nch = (int)((T + KW_CH - 1) / KW_CH);
+      auto issue = [&](int c) {
+        const int h = c & 1;
+        const uint32_t lo = (uint32_t)c * KW_CH, hi = min(T, lo + (uint32_t)KW_CH);
+        if (lane == 0)
+          mbar_expect_tx(&bar[h], (hi - lo) * (uint32_t)sizeof(float4));
+        __syncwarp();
+        {
+          const uint32_t a = max(offA, lo), b = min(offA + lenA, hi);
+          if (a < b)
+            bulk_g2s(buf + h * KW_CH + (a - lo), cell_pts + begA + (a - offA), (b - a) * (uint32_t)sizeof(float4), &bar[h]);
+        }
+        {
+          const uint32_t a = max(offB, lo), b = min(offB + lenB, hi);
+          if (a < b)
+            bulk_g2s(buf + h * KW_CH + (a - lo), cell_pts + begB + (a - offB), (b - a) * (uint32_t)sizeof(float4), &bar[h]);
+        }
+      };
+      if (nch > 0)
+        issue(0);
+      if (nch > 1)
+        issue(1);
+      for (int c = 0; c < nch; c++) {
+        const int h = c & 1;
+        mbar_wait(&bar[h], (par >> h) & 1u);
+        par ^= 1u << h;
+        KW_T(1); // candidates staged
+        const int cnt = (int)min(T - (uint32_t)c * KW_CH, (uint32_t)KW_CH);
+        const float4 *p = buf + h * KW_CH;
+        int j = 0;
+        for (; j + 4 <= cnt; j += 4) {
+          const float4 c0 = p[j], c1 = p[j + 1], c2 = p[j + 2], c3 = p[j + 3];
+          best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+          best.offer(dist2_ref(c1.x, c1.y, c1.z, q.x, q.y, q.z), __float_as_int(c1.w));
+          best.offer(dist2_ref(c2.x, c2.y, c2.z, q.x, q.y, q.z), __float_as_int(c2.w));
+          best.offer(dist2_ref(c3.x, c3.y, c3.z, q.x, q.y, q.z), __float_as_int(c3.w));
+        }
+        for (; j < cnt; j++) {
+          const float4 c0 = p[j];
+          best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+        }
+        __syncwarp(); // every lane has read the half before it is handed back to the copy engine
+        KW_T(2); // candidates tested
+        if (c + 2 < nch)
+          issue(c + 2);
+      }
+    }
+    const double gs = (fmn + (double)s) * g.cell;
+    const bool done = !active || ((double)best.d[K - 1] < gs * gs * (1.0 - 1e-6));
+    if (__all_sync(0xffffffffu, done))
+      break;
+  }
+}
+
 // What one query hands on (all outputs optional): the parity export (indices, squared distances), get_neighbors' verdict
 // (LidarHelper.cpp:280-285) and - what KD_TREE::Nearest_Search hands to compute_plane - the neighbours' COORDINATES
 // (ikd_Tree.cpp:383-387) in scan order (16 K contiguous bytes per query), so that the rows kernel reads them coalesced instead of

@@ -36,7 +36,7 @@ def sass_rows(rep, kernel):
 
 
 def line_table(mangled_hint):
-    so = os.path.join(ROOT, "mins_b200", "libmins_lidar.so")
+    so = os.environ.get("MINS_LIDAR_LIB") or os.path.join(ROOT, "mins_b200", "libmins_lidar.so")
     with tempfile.TemporaryDirectory() as d:
         subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=d, capture_output=True)
         cub = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
