@@ -280,6 +280,22 @@ int ml_debug_timeline(ml_handle *h, int on, unsigned long long *out, int cap);
  * ml_linsys / ml_scan_update also return ml_counters.sum_res - the first moment of the projected residuals in the reference's own
  * nullspace basis (StateHelper::Givens_Rotation, StateHelper.cpp:660-680), run per point on the device. Default off. */
 int ml_set_stats(ml_handle *h, int on);
+/* ---- allocation-free range filter -------------------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it). The range filter of ml_scan_upload (LiDARData's
+ * constructor, fp32 norm in [rmin, rmax], intensity = t_rel, order kept) without a handle: the call allocates nothing and frees
+ * nothing; its only scratch (one count per 2048-point tile) is a static device array of ML_STATIC_MAX_POINTS / 2048 words (8 KB)
+ * that every GPU loading the library holds until the process exits. n > ML_STATIC_MAX_POINTS returns ML_ERR_CAPACITY.
+ * xyz_dev: n points, `stride` floats apart (3 or 4), memory the CURRENT device can read; xyzi_out_dev: room for n points of 4
+ * floats, 16-byte aligned, device memory; n_kept_dev: one int in device memory. Two kernels are queued on `stream` (a
+ * cudaStream_t, NULL = the default stream) and the call returns without synchronising. Every call on a device shares the scratch
+ * array, which keeps the previous call's contents (nothing in it needs clearing: a call overwrites what it reads): calls that
+ * overlap on the GPU - different streams, concurrent graph launches - race. The first call on a device looks the array's
+ * address up (cudaGetSymbolAddress): make it before a stream capture begins. Errors: ml_global_error(). */
+#define ML_STATIC_MAX_POINTS (1 << 22)
+int ml_range_filter_static(const float *xyz_dev, int stride, int n, float t_rel, float rmin, float rmax, float *xyzi_out_dev,
+                           int *n_kept_dev, void *stream);
+
 /* sizeof of {ml_scan_consts, ml_point_row, ml_counters, ml_config} as compiled, for FFI layout checks */
 void ml_abi_sizes(int out[4]);
 /* number of kernel launches issued by this handle so far */

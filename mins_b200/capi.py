@@ -80,6 +80,7 @@ SYMBOLS = [
     "ml_knn", "ml_linsys", "ml_scan_update", "ml_point_rows", "ml_info_to_sqrt", "ml_last_timing", "ml_set_timing",
     "ml_abi_sizes", "ml_launch_count", "ml_sim_set_world", "ml_sim_set_rays", "ml_sim_raycast", "ml_sim_raycast_sweep", "ml_sim_scan_device",
     "ml_icp_default_options", "ml_scan_icp", "ml_debug_timeline", "ml_host_alloc", "ml_host_free", "ml_set_stats",
+    "ml_range_filter_static",
 ]
 
 _lib = None
@@ -138,6 +139,7 @@ def load():
     lib.ml_host_alloc.restype = vp
     lib.ml_host_free.argtypes = [vp]
     lib.ml_host_free.restype = None
+    lib.ml_range_filter_static.argtypes = [vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, vp, vp, vp]
     lib.ml_sim_set_world.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_set_rays.argtypes = [vp, vp, C.c_int]
     lib.ml_sim_raycast.argtypes = [vp, vp, vp, C.c_double, C.c_double, C.c_float, C.c_uint64, vp, C.c_int, ip]

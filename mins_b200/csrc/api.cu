@@ -12,6 +12,7 @@
 #include "icp.cuh"
 
 #include <algorithm>
+#include <mutex>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -1734,5 +1735,152 @@ int ml_info_to_sqrt(const double *HtH, const double *Htr, int n, double *Rc, dou
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// ml_range_filter_static: the range filter of ml_scan_upload (LiDARData's constructor as a stable two-launch compaction,
+// k_range_count + k_range_compact in scan.cuh) for callers that cannot allocate - CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc. No handle: the per-tile counts that the handle path keeps in its `tile_sums` buffer live in
+// a file-scope device array of fixed size; inputs and outputs are the caller's. No counterpart in the
+// reference.
+//   * the array holds one count per 2048-point tile: ML_STATIC_MAX_POINTS / 2048 words = 8 KB on every GPU that loads the
+//     library, until the process exits;
+//   * in HOST code `g_static_tile_sums` is only a stand-in for the symbol: its device address comes from
+//     cudaGetSymbolAddress, once per device with that device current (static_scratch below), and is what the kernels get;
+//   * every call on a device shares the array and finds the previous call's counts in it. Nothing has to start at zero: the
+//     count kernel overwrites exactly the words [0, ceil(n / 2048)) that the compaction kernel of the same call reads. Two calls
+//     that overlap on the GPU (different streams, or concurrent graph launches) race on it.
+// ------------------------------------------------------------------------------------------------
+namespace ml {
+constexpr int STATIC_MAX_TILES = ML_STATIC_MAX_POINTS / RF_TILE;
+static __device__ __align__(256) unsigned int g_static_tile_sums[STATIC_MAX_TILES];
+
+template <bool VEC4>
+__global__ void __launch_bounds__(RF_BLOCK) k_range_count_static(const float *__restrict__ raw, int stride, int n, double rmin, double rmax,
+                                                                 unsigned int *__restrict__ tile_sums) {
+  __shared__ uint32_t wsum[RF_BLOCK / 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int wbase = blockIdx.x * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
+  uint32_t cnt = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int i = wbase + r * 32 + lane;
+    const bool k = i < n && range_keep(load_raw<VEC4>(raw, stride, i), rmin, rmax);
+    cnt += __popc(__ballot_sync(0xffffffffu, k));
+  }
+  if (lane == 0)
+    wsum[wid] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < RF_BLOCK / 32; w++)
+      s += wsum[w];
+    tile_sums[blockIdx.x] = s;
+  }
+}
+
+// the body of k_range_compact with one output cloud and the count delivered to the caller's device word
+template <bool VEC4>
+__global__ void __launch_bounds__(RF_BLOCK)
+    k_range_compact_static(const float *__restrict__ raw, int stride, int n, float t_rel, double rmin, double rmax,
+                           const unsigned int *__restrict__ tile_sums, float4 *__restrict__ out, int *__restrict__ n_kept) {
+  __shared__ uint32_t wsum[RF_BLOCK / 32];
+  __shared__ uint32_t tile_prefix;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid == 0) { // counts of the tiles before this one, fixed order
+    uint32_t s = 0;
+    for (int b = lane; b < (int)blockIdx.x; b += 32)
+      s += tile_sums[b];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0)
+      tile_prefix = s;
+  }
+  const int wbase = blockIdx.x * RF_TILE + wid * (RF_TILE / (RF_BLOCK / 32));
+  float4 pt[8];
+  uint32_t bal[8];
+  uint32_t cnt = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    const int i = wbase + r * 32 + lane;
+    pt[r] = i < n ? load_raw<VEC4>(raw, stride, i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool k = i < n && range_keep(pt[r], rmin, rmax);
+    bal[r] = __ballot_sync(0xffffffffu, k);
+    cnt += __popc(bal[r]);
+  }
+  if (lane == 0)
+    wsum[wid] = cnt;
+  __syncthreads();
+  uint32_t pos = tile_prefix;
+  for (int w = 0; w < wid; w++)
+    pos += wsum[w];
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    uint32_t tot = tile_prefix;
+#pragma unroll
+    for (int w = 0; w < RF_BLOCK / 32; w++)
+      tot += wsum[w];
+    *n_kept = (int)tot;
+  }
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    if ((bal[r] >> lane) & 1u)
+      out[pos + __popc(bal[r] & lt)] = make_float4(pt[r].x, pt[r].y, pt[r].z, t_rel);
+    pos += __popc(bal[r]);
+  }
+}
+} // namespace ml
+
+// device address of the scratch array on the CURRENT device; looked up once per device
+static int static_scratch(unsigned int **out) {
+  ml_handle *h = nullptr; // CK reports through ml_global_error
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static unsigned int *addr[MAX_DEV] = {};
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MAX_DEV)
+    return fail(nullptr, ML_ERR_ARG, "ml_range_filter_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    unsigned int *p = nullptr;
+    CK(cudaGetSymbolAddress((void **)&p, ml::g_static_tile_sums));
+    if (!p)
+      return fail(nullptr, ML_ERR_CUDA, "ml_range_filter_static: cudaGetSymbolAddress returned no address");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return ML_OK;
+}
+
+extern "C" int ml_range_filter_static(const float *xyz_dev, int stride, int n, float t_rel, float rmin, float rmax, float *xyzi_out_dev,
+                                      int *n_kept_dev, void *stream) {
+  ml_handle *h = nullptr;
+  if (n < 0 || (stride != 3 && stride != 4) || !n_kept_dev || (n > 0 && (!xyz_dev || !xyzi_out_dev)))
+    return fail(nullptr, ML_ERR_ARG, "ml_range_filter_static: bad argument (stride must be 3 or 4, pointers must not be NULL)");
+  if (n > ML_STATIC_MAX_POINTS)
+    return fail(nullptr, ML_ERR_CAPACITY, "ml_range_filter_static: n exceeds ML_STATIC_MAX_POINTS (4194304 points): the scratch array "
+                                          "is static; use ml_scan_upload for larger scans");
+  if ((((uintptr_t)xyzi_out_dev) & 15u) != 0)
+    return fail(nullptr, ML_ERR_ARG, "ml_range_filter_static: xyzi_out_dev must be 16-byte aligned");
+  unsigned int *sums = nullptr;
+  if (int rc = static_scratch(&sums))
+    return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int tiles = std::max(1, cdiv(n, RF_TILE)); // n == 0: one CTA that keeps nothing and writes n_kept = 0
+  const bool vec4 = stride == 4 && (((uintptr_t)xyz_dev) & 15u) == 0;
+  if (vec4) {
+    k_range_count_static<true><<<tiles, RF_BLOCK, 0, s>>>(xyz_dev, stride, n, (double)rmin, (double)rmax, sums);
+    k_range_compact_static<true><<<tiles, RF_BLOCK, 0, s>>>(xyz_dev, stride, n, t_rel, (double)rmin, (double)rmax, sums,
+                                                            (float4 *)xyzi_out_dev, n_kept_dev);
+  } else {
+    k_range_count_static<false><<<tiles, RF_BLOCK, 0, s>>>(xyz_dev, stride, n, (double)rmin, (double)rmax, sums);
+    k_range_compact_static<false><<<tiles, RF_BLOCK, 0, s>>>(xyz_dev, stride, n, t_rel, (double)rmin, (double)rmax, sums,
+                                                             (float4 *)xyzi_out_dev, n_kept_dev);
+  }
+  CK(cudaGetLastError());
+  return ML_OK;
+}
 
 #include "icp_host.inl"
