@@ -519,7 +519,11 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
         fused = stage.get("upload_filter", 0.0) == 0.0 and stage.get("bin", 0.0) == 0.0
-        kern = {"knn": "k_front_knn<5> (range filter + transform + cell grouping + exact kNN, one persistent kernel)" if fused else "k_knn<5>",
+        one_kernel = fused and stage.get("rows_reduce", 0.0) == 0.0  # tile.cuh: the whole update is one launch, timed under "knn"
+        n_parts = min(-(-n // 448), 296) if one_kernel else 148
+        kern = {"knn": ("k_scan_tile<5,3> (range filter + transform + exact kNN + plane fit + residual/Jacobian + chi2 + reduction: the whole "
+                        "scan update, one kernel)" if one_kernel else
+                        "k_front_knn<5> (range filter + transform + cell grouping + exact kNN, one persistent kernel)") if fused else "k_knn<5>",
                 "rows_reduce": "k_rows_reduce<5,3> (plane fit + residual/Jacobian + chi2 + reduction)",
                 "bin": "k_unit_alloc + k_query_scatter", "upload_filter": "k_range_filter_bin (range filter + transform + query binning)"}
         cand = {k_: stage.get(k_, 0.0) / args.steps for k_ in kern}
@@ -528,7 +532,8 @@ def main():
         traffic = None
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))
-            traffic = prof.get({"upload_filter": "front"}.get(dom, dom), {}).get("dram_bytes_per_launch")
+            key = "scan_tile" if (one_kernel and dom == "knn") else {"upload_filter": "front"}.get(dom, dom)
+            traffic = prof.get(key, {}).get("dram_bytes_per_launch")
         except Exception:
             pass
         line = {
@@ -538,12 +543,12 @@ def main():
             "config": workload_desc(w, world, n, n_acc),
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(n * 16 + C.sizeof(capi.ml_scan_consts) + hx * hx * 8 + 32),
-                    "d2h_bytes_per_step": int(148 * (8 * 57 + 24)), "ms_per_step": e2e_ms_max / args.steps,
+                    "d2h_bytes_per_step": int(n_parts * (8 * 57 + 32)), "ms_per_step": e2e_ms_max / args.steps,
                     "step_ms_min_median_max": [float(np.min(e2e_steps) * 1e3), float(np.median(e2e_steps) * 1e3), float(np.max(e2e_steps) * 1e3)],
                     "ms_mean_max_argmax_by_rank": by_rank, "host_cpu_affinity_rank0": affinity, "by_input": by_input,
-                    "h2d": "none as a copy: the fused front kernel reads the pinned scan over PCIe itself (TMA bulk copies, tile by tile)",
-                    "d2h": "none as a copy: every CTA of the rows kernel writes its reduced system into pinned host memory over PCIe; "
-                           "the library's host tail adds them in CTA order and applies the chain rule T^T G T"},
+                    "h2d": "none as a copy: the kernel reads the pinned scan over PCIe itself (TMA bulk copies, one 7 KB tile per CTA)",
+                    "d2h": "none as a copy: every CTA writes its reduced system and a stamp into pinned host memory over PCIe; the "
+                           "library's host tail waits for the stamps, adds the systems in CTA order and applies the chain rule T^T G T"},
             "gpu_launches": int(launches),
             "stage_ms_per_step": {k_: v / args.steps for k_, v in stage.items()},
             "wall_ms_total_incl_l2_flush": wall_total * 1e3,

@@ -9,9 +9,12 @@
 #include "sim.cuh"
 #include "update.cuh"
 #include "fused.cuh"
+#include "tile.cuh"
 #include "icp.cuh"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <mutex>
 #include <cmath>
 #include <cstddef>
@@ -119,6 +122,17 @@ struct ml_handle {
   FusedCtl *d_fctl = nullptr;
   uint32_t *units_tag = nullptr;
   bool use_fused_knn = true; // MINS_FUSED_KNN=0: the separate kernels (A/B)
+  // the one-kernel path (tile.cuh)
+  bool use_tile = true;      // MINS_SCAN_TILE=0: front + kNN kernel followed by the rows kernel (A/B)
+  bool tile_keep_nbr = true; // MINS_TILE_NBR=0: do not leave the neighbours' coordinates in `nbr` (ml_point_rows then fails)
+  bool tile_poll = true;     // MINS_TILE_POLL=0: wait with cudaStreamSynchronize instead of polling the parts' stamps
+  int tile_grid[ML_MAX_K + 1][2][2] = {}; // co-resident CTAs per (k, NB, VEC4), 0 = attribute not set yet
+  uint32_t tile_stamp = 0;
+  int parts_n = 0;           // parts of the last reduction (rows_host_tail)
+  bool parts_nscan_by_max = false;
+  bool host_prof = false; // MINS_HOST_PROF=1
+  double host_prof_us[4] = {0, 0, 0, 0};
+  long host_prof_n = 0;
   int fused_producers = 0;   // MINS_FUSED_PRODUCERS: 0 = by input kind
   bool fused_attr[ML_MAX_K + 1][2] = {};
   bool rows_exported = false;
@@ -353,6 +367,14 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     h->use_fused_knn = !(e[0] == '0');
   if (const char *e = getenv("MINS_FUSED_PRODUCERS"))
     h->fused_producers = atoi(e);
+  if (const char *e = getenv("MINS_SCAN_TILE"))
+    h->use_tile = !(e[0] == '0');
+  if (const char *e = getenv("MINS_TILE_NBR"))
+    h->tile_keep_nbr = !(e[0] == '0');
+  if (const char *e = getenv("MINS_TILE_POLL"))
+    h->tile_poll = !(e[0] == '0');
+  if (const char *e = getenv("MINS_HOST_PROF"))
+    h->host_prof = e[0] == '1';
   if (const char *e = getenv("MINS_NO_FUSED_FRONT"))
     h->use_fused_front = !(e[0] == '1');
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -455,6 +477,10 @@ void ml_destroy(ml_handle *h) {
     return;
   use_device(h);
   cudaStreamSynchronize(h->stream);
+  if (h->host_prof && h->host_prof_n)
+    fprintf(stderr, "[mins host prof] %ld one-kernel scan updates: consts %.1f us, resolve+launch %.1f us, wait %.1f us, host tail %.1f us\n",
+            h->host_prof_n, h->host_prof_us[0] / h->host_prof_n, h->host_prof_us[1] / h->host_prof_n, h->host_prof_us[2] / h->host_prof_n,
+            h->host_prof_us[3] / h->host_prof_n);
   if (h->h_merge)
     cudaFreeHost(h->h_merge);
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
@@ -1039,6 +1065,8 @@ template <int K, int NB, int BLOCK, bool EXPORT> static int launch_rows_cfg(ml_h
     attr_set = true;
   }
   h->rows_nb = nb;
+  h->parts_n = nb;
+  h->parts_nscan_by_max = false;
   launch_pdl(h, k_rows_reduce<K, NB, BLOCK, EXPORT>, nb, BLOCK, smem, h->rowc, (const ScanState *)h->d_st, h->n_raw,
              (const float4 *)h->scan_pts, (const float4 *)h->nbr, rows_out, h->h_parts /* pinned host memory */,
              h->tl_on ? h->tl_rows : (unsigned long long *)nullptr);
@@ -1279,7 +1307,7 @@ static int consts_host(ml_handle *h, const ml_scan_consts *c, const double *P) {
 // HtH = T^T G T, Htr = T^T b (T is block sparse: zero entries are skipped), and the counters.
 static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
   const ml_scan_consts &c = h->consts;
-  const int hx = c.total_hx, nb = h->rows_nb;
+  const int hx = c.total_hx, nb = h->parts_n;
   const int NG = c.calib_col >= 0 ? ML_G : 9, NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 4;
   double sum[ML_NRED];
   int cs[5] = {0, 0, 0, 0, 0};
@@ -1293,6 +1321,9 @@ static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *c
       cs[q] += p.c[q];
   }
   h->last_n_scan = h->h_parts[0].n_scan;
+  if (h->parts_nscan_by_max) // k_scan_tile: only the CTA that owned the last tile knows the size, the others wrote -1
+    for (int b = 1; b < nb; b++)
+      h->last_n_scan = std::max(h->last_n_scan, h->h_parts[b].n_scan);
   if (cnt) {
     cnt->n_points = h->last_n_scan;
     cnt->n_acc = cs[0], cnt->n_knn_fail = cs[1], cnt->n_plane_fail = cs[2], cnt->n_badmatch = cs[3], cnt->n_chi_rej = cs[4];
@@ -1482,6 +1513,95 @@ static int scan_front_knn_async(ml_handle *h, const float *xyz, int stride, int 
   }
 }
 
+// ---- the one-kernel path (tile.cuh): a thread owns a ray, a CTA a 448-ray tile down to its share of the reduced system ---------
+template <int K, int NB, bool VEC4>
+static int launch_scan_tile(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2) {
+  using LY = STLayout<NB>;
+  int &cap = h->tile_grid[K][NB == 5 ? 1 : 0][VEC4 ? 1 : 0];
+  if (!cap) {
+    CK(cudaFuncSetAttribute(k_scan_tile<K, NB, VEC4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LY::BYTES));
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_scan_tile<K, NB, VEC4>, ST_BLOCK, LY::BYTES));
+    if (per_sm < 1)
+      return fail(h, ML_ERR_CUDA, "ml_scan_update: k_scan_tile does not fit an SM");
+    // every CTA must be resident: tiles are owned statically and a tile waits for the counts of the tiles before it
+    cap = std::min(per_sm * h->n_sm, ML_NPART_MAX);
+  }
+  const int grid = std::max(1, std::min(cdiv(n, ST_TILE), cap));
+  h->tile_stamp = h->tile_stamp + 1u ? h->tile_stamp + 1u : 1u;
+  h->parts_n = grid;
+  h->parts_nscan_by_max = true;
+  launch_pdl(h, k_scan_tile<K, NB, VEC4>, grid, ST_BLOCK, LY::BYTES, h->rowc, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st,
+             h->scan_pts, h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, lb_next_epoch(h), (const GridDesc *)h->d_grid,
+             (const uint32_t *)h->cell_start, (const float4 *)h->cell_pts, (const float4 *)h->map_pts[h->cur], max_d2,
+             h->tile_keep_nbr ? h->nbr : (float4 *)nullptr, h->h_parts, h->tile_stamp,
+             h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
+  return check_launch(h);
+}
+template <int K>
+static int launch_scan_tile_k(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2) {
+  const bool vec4 = stride == 4 && (((uintptr_t)raw_src) & 15u) == 0;
+  if (h->consts.calib_col >= 0)
+    return vec4 ? launch_scan_tile<K, 5, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2)
+                : launch_scan_tile<K, 5, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  return vec4 ? launch_scan_tile<K, 3, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2)
+              : launch_scan_tile<K, 3, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+}
+// consts_host must have been called (the kernel takes the row constants as a parameter)
+static int scan_tile_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM,
+                           int k, float max_d2) {
+  if (n < 0 || (n > 0 && !xyz) || (stride != 3 && stride != 4))
+    return fail(h, ML_ERR_ARG, "ml_scan_update: bad argument (stride must be 3 or 4)");
+  if (n > h->cap_scan)
+    return fail(h, ML_ERR_CAPACITY, "ml_scan_update: more points than max_scan_points");
+  drop_stale_bins(h);
+  h->n_raw = n;
+  h->rows_valid = false;
+  h->vg_ready = false;
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 4; c++)
+      h->T_LtoM.m[4 * r + c] = T_LtoM[4 * r + c];
+  h->have_T = true;
+  const float *raw_src = nullptr;
+  bool over_pcie = false;
+  if (int rc = resolve_input(h, xyz, stride, n, &raw_src, &over_pcie))
+    return rc;
+  switch (k) {
+  case 3: return launch_scan_tile_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 4: return launch_scan_tile_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 5: return launch_scan_tile_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 6: return launch_scan_tile_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 7: return launch_scan_tile_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 8: return launch_scan_tile_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 9: return launch_scan_tile_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  default: return launch_scan_tile_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  }
+}
+// Wait for the parts of the launch in flight: every CTA stamps its RRPart after a system-scope fence, so the host can watch pinned
+// memory instead of paying a stream synchronisation's wake-up. Falls back to the stream when the stamps do not show up (a faulting
+// kernel never writes them).
+static int scan_tile_wait(ml_handle *h) {
+  if (h->tile_poll && !h->timing) {
+    const int nb = h->parts_n;
+    const uint32_t want = h->tile_stamp;
+    const auto t0 = std::chrono::steady_clock::now();
+    int b = 0;
+    for (unsigned spins = 0;; spins++) {
+      while (b < nb && *(volatile unsigned int *)&h->h_parts[b].stamp == want)
+        b++;
+      if (b == nb) {
+        std::atomic_thread_fence(std::memory_order_acquire);
+        return ML_OK;
+      }
+      if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20))
+        break;
+    }
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaGetLastError());
+  return ML_OK;
+}
+
 extern "C" {
 
 int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, float leaf,
@@ -1505,6 +1625,50 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     }
     return ms;
   };
+  if (!ds && h->use_tile && !h->stats_on && h->use_fused_front && n > 0) {
+    // ONE launch (tile.cuh). The row constants are a kernel parameter, so the host folds them first (~2 us).
+    const bool hp = h->host_prof;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto us = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+      return std::chrono::duration<double, std::micro>(b - a).count();
+    };
+    const auto t0 = hp ? now() : std::chrono::steady_clock::time_point();
+    rc = consts_host(h, c, P);
+    if (rc)
+      return rc;
+    const auto t1 = hp ? now() : t0;
+    rc = scan_tile_async(h, xyz, stride, n, t_rel, rmin, rmax, T_LtoM, c->map_ngbr_num, (float)c->map_ngbr_max_d);
+    if (rc)
+      return rc;
+    if (h->timing)
+      cudaEventRecord(h->ev[8], h->stream);
+    const auto t2 = hp ? now() : t0;
+    rc = scan_tile_wait(h);
+    if (rc)
+      return rc;
+    if (hp) { // MINS_HOST_PROF=1: where the calling thread spends the call (printed by ml_destroy)
+      const auto t3 = now();
+      h->rows_valid = h->tile_keep_nbr;
+      h->rows_exported = false;
+      h->rows_k = c->map_ngbr_num;
+      rc = rows_host_tail(h, HtH, Htr, cnt);
+      const auto t4 = now();
+      h->host_prof_us[0] += us(t0, t1), h->host_prof_us[1] += us(t1, t2), h->host_prof_us[2] += us(t2, t3), h->host_prof_us[3] += us(t3, t4);
+      h->host_prof_n++;
+      return rc;
+    }
+    h->rows_valid = h->tile_keep_nbr; // ml_point_rows re-runs the export instantiation of the rows kernel on `nbr`
+    h->rows_exported = false;
+    h->rows_k = c->map_ngbr_num;
+    rc = rows_host_tail(h, HtH, Htr, cnt);
+    if (h->timing && rc >= 0) {
+      for (int q = 0; q < 7; q++)
+        h->last_ms[q] = 0.f;
+      h->last_ms[7] = el(0, 8);
+      h->last_ms[4] = h->last_ms[7]; // reported under the search stage: one kernel
+    }
+    return rc;
+  }
   if (!ds && h->use_fused_knn && h->use_fused_front && n > 0) {
     // two launches: front end + kNN (fused.cuh), rows + reduction (rows.cuh). The host folds the scan constants while the first
     // one runs; nothing sits between the two kernels in the stream (programmatic dependent launch).

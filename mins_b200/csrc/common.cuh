@@ -132,7 +132,7 @@ struct PointRow {
   int pad;
 };
 
-#define ML_NPART_MAX 256 // >= number of CTAs of the fused rows+reduce kernel (one per SM)
+#define ML_NPART_MAX 512 // >= CTAs of the kernels that return one reduced system each (k_rows_reduce: one per SM; k_scan_tile: two)
 #define ML_GSYM (ML_G * (ML_G + 1) / 2) // 120
 
 // result block copied back to the host in one D2H

@@ -367,7 +367,9 @@ constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diago
 struct RRPart {
   double v[ML_NRED];
   int c[5];
-  int n_scan; // written by CTA 0: the device-side size of the scan
+  int n_scan;         // the device-side size of the scan (k_scan_tile: only the CTA that owned the last tile knows it, the others write -1)
+  unsigned int stamp; // k_scan_tile: written last, after a system-scope fence: the host polls it instead of synchronising the stream
+  int pad;
 };
 // per-warp slab: g rows (odd stride: conflict-free stores) | W | V | running sums (one slot per lane) | statistics
 template <int NB> struct RRLayout {

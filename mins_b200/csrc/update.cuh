@@ -783,6 +783,121 @@ __device__ __forceinline__ void knn_walk_staged(const KnnUnit &un, const float4 
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// The cube walk of ONE query by ONE thread (no grouping, no shared memory): every lane of a warp walks the cube of its own
+// query's cell. Same levels, same rows, same completeness rule, same arithmetic and (d2, index) order as knn_walk: identical
+// results. Lanes whose queries share a cell run in lock step and their loads coalesce into one broadcast; lanes in different
+// cells differ in trip counts only. The ranges of the next row are requested before the candidates of the current row are
+// tested, so a level costs (rows + 1) dependent round trips.
+// Used by k_scan_tile (tile.cuh), where a warp's 32 queries are 32 consecutive rays: a warp-per-cell unit of the grouped walk
+// holds 15 queries and 26 candidates on average on the 64-beam workload, and its cost was all latency and queueing
+// (profiles/r2_ncu.md).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+template <int K, bool PREFETCH = false>
+__device__ __forceinline__ void knn_walk_lane(const float4 q, const int cx, const int cy, const int cz, const GridDesc &g, const int R,
+                                              const uint32_t *__restrict__ cell_start, const float4 *__restrict__ cell_pts,
+                                              TopK<K> &best) {
+  double fx = ((double)q.x - g.ox) * g.inv_cell - (double)cx;
+  double fy = ((double)q.y - g.oy) * g.inv_cell - (double)cy;
+  double fz = ((double)q.z - g.oz) * g.inv_cell - (double)cz;
+  double fmn = fmin(fmin(fmin(fx, 1.0 - fx), fmin(fy, 1.0 - fy)), fmin(fz, 1.0 - fz));
+  fmn = fmax(0.0, fmn);
+  best.init();
+  const int ox_ = max(max(-cx, cx - (g.dimx - 1)), 0), oy_ = max(max(-cy, cy - (g.dimy - 1)), 0), oz_ = max(max(-cz, cz - (g.dimz - 1)), 0);
+  const int s_lo = max(1, max(ox_, max(oy_, oz_)));
+  const int s_hi = min(R, max(max(max(cx, g.dimx - 1 - cx), max(cy, g.dimy - 1 - cy)), max(cz, g.dimz - 1 - cz)));
+  for (int s = s_lo; s <= s_hi; s++) {
+    const int y0 = max(cy - s, 0), y1 = min(cy + s, g.dimy - 1);
+    const int z0 = max(cz - s, 0), z1 = min(cz + s, g.dimz - 1);
+    const int x0 = max(cx - s, 0), x1 = min(cx + s, g.dimx - 1);
+    const int xa = cx - s, xb = cx + s;
+    // row (y, z) -> up to two ranges of cell_pts: the whole x-run on the faces of the cube (and at the first level), else the
+    // two end cells
+    auto row_ranges = [&](int y, int z, uint32_t &bA, uint32_t &eA, uint32_t &bB, uint32_t &eB) {
+      bA = eA = bB = eB = 0u;
+      const int rowbase = (z * g.dimy + y) * g.dimx;
+      const bool outer = (s == s_lo) || (abs(y - cy) == s) || (abs(z - cz) == s);
+      if (outer) {
+        if (x0 <= x1) {
+          bA = __ldg(&cell_start[rowbase + x0]);
+          eA = __ldg(&cell_start[rowbase + x1 + 1]);
+        }
+      } else {
+        if (xa >= 0 && xa < g.dimx) {
+          bA = __ldg(&cell_start[rowbase + xa]);
+          eA = __ldg(&cell_start[rowbase + xa + 1]);
+        }
+        if (xb >= 0 && xb < g.dimx) {
+          bB = __ldg(&cell_start[rowbase + xb]);
+          eB = __ldg(&cell_start[rowbase + xb + 1]);
+        }
+      }
+    };
+    if (y1 >= y0 && z1 >= z0) {
+      // Latency: a thread's walk is a chain of dependent loads (ranges of a row, then its candidates), ~2 round trips per row.
+      // Two prefetch passes turn that into ~2 round trips per LEVEL: first the cell_start lines of every row (their addresses
+      // need no load), then - reading the ranges from L1 - the cell_pts lines of every row; the walk proper then hits L1.
+      // Only for the small cubes of the first levels (9 to 25 rows). MEASURED SLOWER and therefore off: on the 64-beam workload
+      // the walk took 29 us instead of 16.5 us per tile (device step 73.8 us against 61.7 us) - the prefetches queue behind the
+      // same load pipe the walk needs and most of a tile's lines are in L1 already.
+      if (PREFETCH && (y1 - y0 + 1) * (z1 - z0 + 1) <= 25) {
+        for (int y = y0; y <= y1; y++)
+          for (int z = z0; z <= z1; z++) {
+            const int rowbase = (z * g.dimy + y) * g.dimx;
+            prefetch_l1(&cell_start[rowbase + max(xa, 0)]);
+            prefetch_l1(&cell_start[rowbase + min(xb, g.dimx - 1) + 1]);
+          }
+        for (int y = y0; y <= y1; y++)
+          for (int z = z0; z <= z1; z++) {
+            uint32_t bA, eA, bB, eB;
+            row_ranges(y, z, bA, eA, bB, eB);
+            for (uint32_t a = bA & ~7u; a < eA; a += 8u) // 8 float4 per 128-byte line
+              prefetch_l1(&cell_pts[a]);
+            for (uint32_t a = bB & ~7u; a < eB; a += 8u)
+              prefetch_l1(&cell_pts[a]);
+          }
+      }
+      int y = y0, z = z0;
+      uint32_t nbA, neA, nbB, neB;
+      row_ranges(y, z, nbA, neA, nbB, neB);
+      for (;;) {
+        const uint32_t bA = nbA, eA = neA, bB = nbB, eB = neB;
+        // the next row's ranges are requested before this row's candidates are tested
+        bool more = true;
+        if (++z > z1) {
+          z = z0;
+          if (++y > y1)
+            more = false;
+        }
+        if (more)
+          row_ranges(y, z, nbA, neA, nbB, neB);
+        uint32_t j = bA;
+        for (; j + 4 <= eA; j += 4) {
+          const float4 c0 = __ldg(&cell_pts[j]), c1 = __ldg(&cell_pts[j + 1]), c2 = __ldg(&cell_pts[j + 2]), c3 = __ldg(&cell_pts[j + 3]);
+          best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+          best.offer(dist2_ref(c1.x, c1.y, c1.z, q.x, q.y, q.z), __float_as_int(c1.w));
+          best.offer(dist2_ref(c2.x, c2.y, c2.z, q.x, q.y, q.z), __float_as_int(c2.w));
+          best.offer(dist2_ref(c3.x, c3.y, c3.z, q.x, q.y, q.z), __float_as_int(c3.w));
+        }
+        for (; j < eA; j++) {
+          const float4 c0 = __ldg(&cell_pts[j]);
+          best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+        }
+        for (j = bB; j < eB; j++) {
+          const float4 c0 = __ldg(&cell_pts[j]);
+          best.offer(dist2_ref(c0.x, c0.y, c0.z, q.x, q.y, q.z), __float_as_int(c0.w));
+        }
+        if (!more)
+          break;
+      }
+    }
+    const double gs = (fmn + (double)s) * g.cell;
+    if ((double)best.d[K - 1] < gs * gs * (1.0 - 1e-6))
+      break;
+  }
+}
+
 // What one query hands on (all outputs optional): the parity export (indices, squared distances), get_neighbors' verdict
 // (LidarHelper.cpp:280-285) and - what KD_TREE::Nearest_Search hands to compute_plane - the neighbours' COORDINATES
 // (ikd_Tree.cpp:383-387) in scan order (16 K contiguous bytes per query), so that the rows kernel reads them coalesced instead of

@@ -64,7 +64,7 @@ def main():
         if "l2_bytes" not in d and "l2_sectors" in d:  # `--set full` carries the sector count, not lts__t_bytes: 32 B per sector
             d["l2_bytes"] = 32.0 * d["l2_sectors"]
     out = {"all": acc, "source": os.path.basename(rep)}
-    for alias, pat in (("knn", "k_knn<5>"), ("knn", "k_front_knn<5"), ("rows_reduce", "k_rows_reduce<5"), ("front", "k_range_filter_bin")):
+    for alias, pat in (("knn", "k_knn<5>"), ("knn", "k_front_knn<5"), ("rows_reduce", "k_rows_reduce<5"), ("scan_tile", "k_scan_tile<5"), ("front", "k_range_filter_bin")):
         for name, d in acc.items():
             if name.startswith(pat):
                 out[alias] = d

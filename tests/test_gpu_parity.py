@@ -583,10 +583,20 @@ def test_one_launch_front_end_equals_the_multi_call_path(make_map, po, workload)
         pinned = torch.from_numpy(sub).pin_memory()
         dev = torch.from_numpy(sub).cuda()
         xyz3 = np.ascontiguousarray(sub[:, :3])
+        first = None
         for ptr, stride in ((sub.ctypes.data, 4), (pinned.data_ptr(), 4), (dev.data_ptr(), 4), (xyz3.ctypes.data, 3)):
             for _ in range(3):
                 HtH, Htr, cnt, a, b, c = one_call(ptr, stride, n)
                 assert np.array_equal(a, s0[0]) and np.array_equal(b, s0[1]) and np.array_equal(c, s0[2])
-                assert cnt == cnt0.as_dict() and np.array_equal(HtH, HtH0) and np.array_equal(Htr, Htr0)
+                # the one-kernel path adds the same per-point rows in another (fixed) order than the multi-call path's rows
+                # kernel: integer counters identical, floating-point sums equal to rounding ...
+                ref = cnt0.as_dict()
+                for key, v in cnt.items():
+                    assert v == ref[key] if isinstance(ref[key], int) else abs(v - ref[key]) <= 1e-12 * max(1.0, abs(ref[key])), key
+                assert rel(HtH, HtH0) < 1e-12 and rel(Htr, Htr0) < 1e-12
+                # ... and bit-identical from call to call, whatever kind of buffer the scan arrives in
+                if first is None:
+                    first = (HtH, Htr, cnt)
+                assert cnt == first[2] and np.array_equal(HtH, first[0]) and np.array_equal(Htr, first[1])
             idx, d2, ok = m.get_neighbors(op.map_ngbr_num, op.map_ngbr_max_d)
             assert np.array_equal(idx, idx0) and np.array_equal(d2, d20) and np.array_equal(ok, ok0)
