@@ -123,13 +123,13 @@ struct ml_handle {
   uint32_t *units_tag = nullptr;
   bool use_fused_knn = true; // MINS_FUSED_KNN=0: the separate kernels (A/B)
   // the one-kernel path (tile.cuh)
-  bool use_tile = true;      // MINS_SCAN_TILE=0: front + kNN kernel followed by the rows kernel (A/B)
+  bool use_tile = true;      // MINS_SCAN_TILE=0: front + kNN kernel followed by the rows kernel (A/B); 2: always (see ml_scan_update)
+  bool tile_force = false;
   bool tile_keep_nbr = true; // MINS_TILE_NBR=0: do not leave the neighbours' coordinates in `nbr` (ml_point_rows then fails)
   bool tile_poll = true;     // MINS_TILE_POLL=0: wait with cudaStreamSynchronize instead of polling the parts' stamps
   int tile_grid[ML_MAX_K + 1][2][2] = {}; // co-resident CTAs per (k, NB, VEC4), 0 = attribute not set yet
-  uint32_t tile_stamp = 0;
+  int parts_armed = 0, parts_armed_nred = 0; // parts [0, parts_armed) hold the sentinel in their first parts_armed_nred doubles and counters
   int parts_n = 0;           // parts of the last reduction (rows_host_tail)
-  bool parts_nscan_by_max = false;
   bool host_prof = false; // MINS_HOST_PROF=1
   double host_prof_us[4] = {0, 0, 0, 0};
   long host_prof_n = 0;
@@ -367,8 +367,10 @@ int ml_create(const ml_config *cfg, ml_handle **out) {
     h->use_fused_knn = !(e[0] == '0');
   if (const char *e = getenv("MINS_FUSED_PRODUCERS"))
     h->fused_producers = atoi(e);
-  if (const char *e = getenv("MINS_SCAN_TILE"))
+  if (const char *e = getenv("MINS_SCAN_TILE")) {
     h->use_tile = !(e[0] == '0');
+    h->tile_force = e[0] == '2';
+  }
   if (const char *e = getenv("MINS_TILE_NBR"))
     h->tile_keep_nbr = !(e[0] == '0');
   if (const char *e = getenv("MINS_TILE_POLL"))
@@ -478,9 +480,8 @@ void ml_destroy(ml_handle *h) {
   use_device(h);
   cudaStreamSynchronize(h->stream);
   if (h->host_prof && h->host_prof_n)
-    fprintf(stderr, "[mins host prof] %ld one-kernel scan updates: consts %.1f us, resolve+launch %.1f us, wait %.1f us, host tail %.1f us\n",
-            h->host_prof_n, h->host_prof_us[0] / h->host_prof_n, h->host_prof_us[1] / h->host_prof_n, h->host_prof_us[2] / h->host_prof_n,
-            h->host_prof_us[3] / h->host_prof_n);
+    fprintf(stderr, "[mins host prof] %ld one-kernel scan updates: consts %.1f us, resolve+launch %.1f us, wait+host tail %.1f us\n",
+            h->host_prof_n, h->host_prof_us[0] / h->host_prof_n, h->host_prof_us[1] / h->host_prof_n, h->host_prof_us[2] / h->host_prof_n);
   if (h->h_merge)
     cudaFreeHost(h->h_merge);
   void *dev[] = {h->map_pts[0], h->map_pts[1], h->d_map_n, h->d_grid, h->d_bbox, h->cell_cnt, h->cell_start, h->cell_pts, h->pt_cell,
@@ -1066,7 +1067,7 @@ template <int K, int NB, int BLOCK, bool EXPORT> static int launch_rows_cfg(ml_h
   }
   h->rows_nb = nb;
   h->parts_n = nb;
-  h->parts_nscan_by_max = false;
+  h->parts_armed = 0; // this kernel overwrites the parts: nothing is armed afterwards
   launch_pdl(h, k_rows_reduce<K, NB, BLOCK, EXPORT>, nb, BLOCK, smem, h->rowc, (const ScanState *)h->d_st, h->n_raw,
              (const float4 *)h->scan_pts, (const float4 *)h->nbr, rows_out, h->h_parts /* pinned host memory */,
              h->tl_on ? h->tl_rows : (unsigned long long *)nullptr);
@@ -1305,25 +1306,73 @@ static int consts_host(ml_handle *h, const ml_scan_consts *c, const double *P) {
 
 // Host tail of the rows kernel: add the CTAs' reduced systems in CTA order (fixed: bit-reproducible), then the chain rule
 // HtH = T^T G T, Htr = T^T b (T is block sparse: zero entries are skipped), and the counters.
-static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
+typedef unsigned long long __attribute__((may_alias)) u64_alias; // the bit patterns of doubles
+static int rows_host_tail(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt, bool armed = false) {
   const ml_scan_consts &c = h->consts;
   const int hx = c.total_hx, nb = h->parts_n;
   const int NG = c.calib_col >= 0 ? ML_G : 9, NSYM = NG * (NG + 1) / 2, NE = NSYM + NG, NRED = NE + 4;
   double sum[ML_NRED];
   int cs[5] = {0, 0, 0, 0, 0};
+  int nscan_max = -1;
   for (int e = 0; e < NRED; e++)
     sum[e] = 0.0;
+  // armed (one-kernel path): the parts were armed before the launch; a word is taken as soon as it differs from the sentinel, in
+  // CTA order all the same, so the sum runs beside the kernel's tail instead of after it, and the part is re-armed on the way.
+  // A word that does not come within 20 ms means a faulted kernel: ask the stream.
+  bool synced = false;
+  const auto t0 = std::chrono::steady_clock::now();
+  if (armed)
+    h->parts_armed = 0; // until every part has been consumed and re-armed
+  // a part is complete when none of its words is the sentinel any more (checked without an early exit: the loop vectorises)
+  auto part_ready = [&](const RRPart &p) {
+    const u64_alias *w = reinterpret_cast<const u64_alias *>(p.v);
+    unsigned long long missing = 0;
+    for (int e = 0; e < NRED; e++)
+      missing += (w[e] == RR_ARMED_F64);
+    for (int q = 0; q < 5; q++)
+      missing += (p.c[q] == RR_ARMED_I32);
+    missing += (p.n_scan == RR_ARMED_I32);
+    return missing == 0;
+  };
   for (int b = 0; b < nb; b++) {
-    const RRPart &p = h->h_parts[b];
+    RRPart &p = h->h_parts[b];
+    if (armed) {
+      for (unsigned spins = 1; !part_ready(p); spins++) {
+        asm volatile("" ::: "memory"); // re-read pinned memory
+        if (synced)
+          return fail(h, ML_ERR_CUDA, "ml_scan_update: the kernel finished without delivering its reduced system");
+        if ((spins & 1023u) == 0u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) {
+          CK(cudaStreamSynchronize(h->stream));
+          CK(cudaGetLastError());
+          synced = true;
+        }
+      }
+      std::atomic_thread_fence(std::memory_order_acquire);
+      for (int e = 0; e < NRED; e++)
+        sum[e] += p.v[e];
+      for (int q = 0; q < 5; q++)
+        cs[q] += p.c[q];
+      nscan_max = std::max(nscan_max, p.n_scan);
+      u64_alias *w = reinterpret_cast<u64_alias *>(p.v);
+      for (int e = 0; e < NRED; e++)
+        w[e] = RR_ARMED_F64;
+      for (int q = 0; q < 5; q++)
+        p.c[q] = RR_ARMED_I32;
+      p.n_scan = RR_ARMED_I32;
+      continue;
+    }
     for (int e = 0; e < NRED; e++)
       sum[e] += p.v[e];
     for (int q = 0; q < 5; q++)
       cs[q] += p.c[q];
   }
-  h->last_n_scan = h->h_parts[0].n_scan;
-  if (h->parts_nscan_by_max) // k_scan_tile: only the CTA that owned the last tile knows the size, the others wrote -1
-    for (int b = 1; b < nb; b++)
-      h->last_n_scan = std::max(h->last_n_scan, h->h_parts[b].n_scan);
+  if (armed) {
+    h->last_n_scan = nscan_max;
+    h->parts_armed = nb;
+    h->parts_armed_nred = NRED;
+  } else {
+    h->last_n_scan = h->h_parts[0].n_scan;
+  }
   if (cnt) {
     cnt->n_points = h->last_n_scan;
     cnt->n_acc = cs[0], cnt->n_knn_fail = cs[1], cnt->n_plane_fail = cs[2], cnt->n_badmatch = cs[3], cnt->n_chi_rej = cs[4];
@@ -1513,6 +1562,23 @@ static int scan_front_knn_async(ml_handle *h, const float *xyz, int stride, int 
   }
 }
 
+// Arm the parts a k_scan_tile launch will fill (see RR_ARMED_F64 in rows.cuh). rows_host_tail re-arms a part as it consumes it, so in
+// steady state this finds everything armed and does nothing.
+static void arm_parts(ml_handle *h, int nb, int nred) {
+  if (h->parts_armed >= nb && h->parts_armed_nred == nred)
+    return;
+  for (int b = 0; b < nb; b++) {
+    RRPart &p = h->h_parts[b];
+    for (int e = 0; e < nred; e++)
+      memcpy(&p.v[e], &RR_ARMED_F64, sizeof(double));
+    for (int q = 0; q < 5; q++)
+      p.c[q] = RR_ARMED_I32;
+    p.n_scan = RR_ARMED_I32;
+  }
+  h->parts_armed = nb;
+  h->parts_armed_nred = nred;
+}
+
 // ---- the one-kernel path (tile.cuh): a thread owns a ray, a CTA a 448-ray tile down to its share of the reduced system ---------
 template <int K, int NB, bool VEC4>
 static int launch_scan_tile(ml_handle *h, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2) {
@@ -1528,13 +1594,12 @@ static int launch_scan_tile(ml_handle *h, const float *raw_src, int stride, int 
     cap = std::min(per_sm * h->n_sm, ML_NPART_MAX);
   }
   const int grid = std::max(1, std::min(cdiv(n, ST_TILE), cap));
-  h->tile_stamp = h->tile_stamp + 1u ? h->tile_stamp + 1u : 1u;
   h->parts_n = grid;
-  h->parts_nscan_by_max = true;
-  launch_pdl(h, k_scan_tile<K, NB, VEC4>, grid, ST_BLOCK, LY::BYTES, h->rowc, raw_src, stride, n, t_rel, (double)rmin, (double)rmax, h->d_st,
-             h->scan_pts, h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, lb_next_epoch(h), (const GridDesc *)h->d_grid,
+  arm_parts(h, grid, LY::NRED);
+  launch_pdl(h, k_scan_tile<K, NB, VEC4>, grid, ST_BLOCK, LY::BYTES, h->rowc, raw_src, stride, n, t_rel, (double)rmin, (double)rmax,
+             h->d_st, h->scan_pts, h->scan_orig, h->T_LtoM, h->scan_map, h->lb_state, lb_next_epoch(h), (const GridDesc *)h->d_grid,
              (const uint32_t *)h->cell_start, (const float4 *)h->cell_pts, (const float4 *)h->map_pts[h->cur], max_d2,
-             h->tile_keep_nbr ? h->nbr : (float4 *)nullptr, h->h_parts, h->tile_stamp,
+             h->tile_keep_nbr ? h->nbr : (float4 *)nullptr, h->h_parts,
              h->tl_on ? h->tl_knn : (unsigned long long *)nullptr);
   return check_launch(h);
 }
@@ -1546,6 +1611,18 @@ static int launch_scan_tile_k(ml_handle *h, const float *raw_src, int stride, in
                 : launch_scan_tile<K, 5, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
   return vec4 ? launch_scan_tile<K, 3, true>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2)
               : launch_scan_tile<K, 3, false>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+}
+static int launch_scan_tile_any(ml_handle *h, int k, const float *raw_src, int stride, int n, float t_rel, float rmin, float rmax, float max_d2) {
+  switch (k) {
+  case 3: return launch_scan_tile_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 4: return launch_scan_tile_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 5: return launch_scan_tile_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 6: return launch_scan_tile_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 7: return launch_scan_tile_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 8: return launch_scan_tile_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  case 9: return launch_scan_tile_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  default: return launch_scan_tile_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
+  }
 }
 // consts_host must have been called (the kernel takes the row constants as a parameter)
 static int scan_tile_async(ml_handle *h, const float *xyz, int stride, int n, float t_rel, float rmin, float rmax, const float *T_LtoM,
@@ -1566,40 +1643,16 @@ static int scan_tile_async(ml_handle *h, const float *xyz, int stride, int n, fl
   bool over_pcie = false;
   if (int rc = resolve_input(h, xyz, stride, n, &raw_src, &over_pcie))
     return rc;
-  switch (k) {
-  case 3: return launch_scan_tile_k<3>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 4: return launch_scan_tile_k<4>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 5: return launch_scan_tile_k<5>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 6: return launch_scan_tile_k<6>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 7: return launch_scan_tile_k<7>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 8: return launch_scan_tile_k<8>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  case 9: return launch_scan_tile_k<9>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  default: return launch_scan_tile_k<10>(h, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
-  }
+  return launch_scan_tile_any(h, k, raw_src, stride, n, t_rel, rmin, rmax, max_d2);
 }
-// Wait for the parts of the launch in flight: every CTA stamps its RRPart after a system-scope fence, so the host can watch pinned
-// memory instead of paying a stream synchronisation's wake-up. Falls back to the stream when the stamps do not show up (a faulting
-// kernel never writes them).
-static int scan_tile_wait(ml_handle *h) {
-  if (h->tile_poll && !h->timing) {
-    const int nb = h->parts_n;
-    const uint32_t want = h->tile_stamp;
-    const auto t0 = std::chrono::steady_clock::now();
-    int b = 0;
-    for (unsigned spins = 0;; spins++) {
-      while (b < nb && *(volatile unsigned int *)&h->h_parts[b].stamp == want)
-        b++;
-      if (b == nb) {
-        std::atomic_thread_fence(std::memory_order_acquire);
-        return ML_OK;
-      }
-      if ((spins & 1023u) == 1023u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20))
-        break;
-    }
+// The parts of the launch in flight are consumed by rows_host_tail as their words arrive in pinned memory, so the calling thread
+// pays no stream synchronisation (measured: 12 us per call). MINS_TILE_POLL=0 or event timing: synchronise first, then read.
+static int scan_tile_finish(ml_handle *h, double *HtH, double *Htr, ml_counters *cnt) {
+  if (!h->tile_poll || h->timing) {
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
   }
-  CK(cudaStreamSynchronize(h->stream));
-  CK(cudaGetLastError());
-  return ML_OK;
+  return rows_host_tail(h, HtH, Htr, cnt, true);
 }
 
 extern "C" {
@@ -1625,7 +1678,13 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     }
     return ms;
   };
-  if (!ds && h->use_tile && !h->stats_on && h->use_fused_front && n > 0) {
+  // The one-kernel path pays when a query's walk is at most three levels deep (one thread walks one cube; the level count is that
+  // of the kernels: the squared distance is compared with the UNSQUARED option, LidarHelper.cpp:284) and the scan fills the device
+  // (a tile per CTA). Measured otherwise: KAIST options (map_ngbr_max_d 10 m = 7 levels on a thinned map) 241 us against
+  // 109 us for the grouped walk; a 32 000-ray scan (72 tiles on 148 SMs) 108 us against 93 us. MINS_SCAN_TILE=2 forces it (tests).
+  const bool tile_fits =
+      h->tile_force || ((int)std::ceil(std::sqrt(c->map_ngbr_max_d) / h->grid_cell * (1.0 + 1e-5)) <= 3 && n >= ST_TILE * h->n_sm);
+  if (!ds && h->use_tile && tile_fits && !h->stats_on && h->use_fused_front && n > 0) {
     // ONE launch (tile.cuh). The row constants are a kernel parameter, so the host folds them first (~2 us).
     const bool hp = h->host_prof;
     auto now = [] { return std::chrono::steady_clock::now(); };
@@ -1643,24 +1702,14 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     if (h->timing)
       cudaEventRecord(h->ev[8], h->stream);
     const auto t2 = hp ? now() : t0;
-    rc = scan_tile_wait(h);
-    if (rc)
-      return rc;
-    if (hp) { // MINS_HOST_PROF=1: where the calling thread spends the call (printed by ml_destroy)
-      const auto t3 = now();
-      h->rows_valid = h->tile_keep_nbr;
-      h->rows_exported = false;
-      h->rows_k = c->map_ngbr_num;
-      rc = rows_host_tail(h, HtH, Htr, cnt);
-      const auto t4 = now();
-      h->host_prof_us[0] += us(t0, t1), h->host_prof_us[1] += us(t1, t2), h->host_prof_us[2] += us(t2, t3), h->host_prof_us[3] += us(t3, t4);
-      h->host_prof_n++;
-      return rc;
-    }
     h->rows_valid = h->tile_keep_nbr; // ml_point_rows re-runs the export instantiation of the rows kernel on `nbr`
     h->rows_exported = false;
     h->rows_k = c->map_ngbr_num;
-    rc = rows_host_tail(h, HtH, Htr, cnt);
+    rc = scan_tile_finish(h, HtH, Htr, cnt);
+    if (hp) { // MINS_HOST_PROF=1: where the calling thread spends the call (printed by ml_destroy)
+      h->host_prof_us[0] += us(t0, t1), h->host_prof_us[1] += us(t1, t2), h->host_prof_us[2] += us(t2, now());
+      h->host_prof_n++;
+    }
     if (h->timing && rc >= 0) {
       for (int q = 0; q < 7; q++)
         h->last_ms[q] = 0.f;

@@ -367,10 +367,12 @@ constexpr int RR_RACC = 12;           // 9 block entries + 3 entries of b (diago
 struct RRPart {
   double v[ML_NRED];
   int c[5];
-  int n_scan;         // the device-side size of the scan (k_scan_tile: only the CTA that owned the last tile knows it, the others write -1)
-  unsigned int stamp; // k_scan_tile: written last, after a system-scope fence: the host polls it instead of synchronising the stream
-  int pad;
+  int n_scan; // the device-side size of the scan (k_scan_tile: only the CTA that owned the last tile knows it, the others write -1)
 };
+// k_scan_tile's parts are ARMED by the host before the launch: every word the CTA will write holds a pattern no result can be (a
+// quiet NaN with a payload; INT_MIN for the counters), so the host can consume a part word by word as the posted writes land.
+constexpr unsigned long long RR_ARMED_F64 = 0x7ff8dead5eed0001ull;
+constexpr int RR_ARMED_I32 = (int)0x80000000;
 // per-warp slab: g rows (odd stride: conflict-free stores) | W | V | running sums (one slot per lane) | statistics
 template <int NB> struct RRLayout {
   static constexpr int NG = 3 * NB;

@@ -545,13 +545,18 @@ def test_one_call_downsampling_path_equals_the_separate_calls(make_map, po, work
                     assert cnt.as_dict() == cnt0.as_dict() and np.array_equal(HtH, HtH0) and np.array_equal(Htr, Htr0)
 
 
-def test_one_launch_front_end_equals_the_multi_call_path(make_map, po, workload):
+@pytest.mark.parametrize("path", ["auto", "one_kernel"])
+def test_one_launch_front_end_equals_the_multi_call_path(make_map, po, workload, path, monkeypatch):
     """ml_scan_update's fused front end (single-pass compaction + transform + binning, zero-copy pinned input) must leave
     exactly the state the separate calls leave: same clouds, same kNN, same reduced system - for packed xyz (stride 3),
     PointXYZ (stride 4), pageable and pinned host buffers, device buffers, ragged sizes, and over many consecutive scans."""
     import ctypes as C
     import torch
     from mins_b200 import capi
+    # "auto": ml_scan_update picks the path by scan size and search depth (here: front + kNN kernel, then the rows kernel);
+    # "one_kernel": k_scan_tile forced (MINS_SCAN_TILE=2 is read when the handle is created), on ragged sizes down to one point
+    if path == "one_kernel":
+        monkeypatch.setenv("MINS_SCAN_TILE", "2")
     w = workload("G-vlp")
     op = w["op"]
     m = make_map(max_map_points=1 << 19)
