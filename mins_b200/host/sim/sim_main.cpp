@@ -1,5 +1,5 @@
 // mins_sim_run: one closed-loop IMU + LiDAR simulation run in host C++ (see harness.hpp). Prints one JSON line.
-//   mins_sim_run --bspline F --floorplan F [--seed S] [--duration T] [--icp 0|1] [--no-lidar] [--no-noise] [--no-gt-map]
+//   mins_sim_run --bspline F --floorplan F [--seed S | --seeds S0,S1,...] [--duration T] [--icp 0|1] [--no-lidar] [--no-noise] [--no-gt-map]
 //                [--device D] [--traj out.txt] [--deskew 0|1]
 // Without --no-lidar a CUDA device is required (the LiDAR updater has no CPU path); --no-lidar runs the IMU + clone-window core
 // alone (the CPU tests use it to pin this file against the Python harness it replaces).
@@ -203,6 +203,7 @@ static SimResult run(const SimConfig &cfg) {
 
 int main(int argc, char **argv) {
   SimConfig cfg;
+  std::vector<unsigned long long> seeds;
   // simulation option set (mins/config/simulation/config_lidar.yaml:11-29)
   cfg.op.max_n = 1, cfg.op.max_range = 100.0, cfg.op.min_range = 1.0, cfg.op.chi2_mult = 1.0;
   cfg.op.raw_do_downsample = true, cfg.op.raw_downsample_size = 0.3, cfg.op.raw_noise = 0.01;
@@ -224,6 +225,14 @@ int main(int argc, char **argv) {
       cfg.floorplan_path = next();
     else if (a == "--seed")
       cfg.seed = strtoull(next(), nullptr, 10);
+    else if (a == "--seeds") { // several runs in ONE process (one CUDA context): a Monte-Carlo worker
+      std::string list = next();
+      for (size_t pos = 0; pos < list.size();) {
+        const size_t comma = list.find(',', pos);
+        seeds.push_back(strtoull(list.substr(pos, comma - pos).c_str(), nullptr, 10));
+        pos = comma == std::string::npos ? list.size() : comma + 1;
+      }
+    }
     else if (a == "--duration")
       cfg.duration = atof(next());
     else if (a == "--icp")
@@ -249,8 +258,12 @@ int main(int argc, char **argv) {
     std::fprintf(stderr, "usage: mins_sim_run --bspline F --floorplan F [--seed S] [--duration T] [--icp 0|1] [--no-lidar] [--no-noise]\n");
     return 2;
   }
-  cfg.op.icp_seed = cfg.seed << 20;
+  if (seeds.empty())
+    seeds.push_back(cfg.seed);
+  for (unsigned long long seed : seeds)
   try {
+    cfg.seed = seed;
+    cfg.op.icp_seed = cfg.seed << 20;
     const SimResult r = run(cfg);
     if (!cfg.traj_out.empty()) {
       FILE *f = std::fopen(cfg.traj_out.c_str(), "w");
@@ -263,6 +276,7 @@ int main(int argc, char **argv) {
                 "\"wall_s\": %.4f, \"ldr_wall_s\": %.4f, \"raycast_wall_s\": %.4f}\n",
                 cfg.seed, cfg.op.map_use_icp ? 1 : 0, r.rmse_ori_deg, r.rmse_pos_m, r.nees_pos, r.final_pos_err, r.n_updates, r.n_scans,
                 r.n_clones, r.n_acc, r.n_meas, r.map_points, r.wall_s, r.ldr_wall_s, r.raycast_wall_s);
+    std::fflush(stdout);
   } catch (const std::exception &e) {
     std::fprintf(stderr, "mins_sim_run: %s\n", e.what());
     return 1;

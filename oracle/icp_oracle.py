@@ -104,15 +104,33 @@ def point_to_plane_step(read_c, ref_c, nrm, w):
     return T.astype(F)
 
 
+def knn_surface_normal(pts, rng, ratio=0.5, knn=7):
+    """The DEVICE's variant of the reference filter (mins_b200/csrc/icp.cuh k_icp_ref_select + k_icp_normals): every point kept with
+    probability `ratio`, normal = PCA of its `knn` nearest points of the unfiltered cloud (itself included), rank-deficient
+    neighbourhoods dropped. Same support size as the reference's bins, no sequential recursion. Returns (kept indices, normals)."""
+    pts = np.ascontiguousarray(pts, F)
+    keep = np.where(rng.random(len(pts)) < ratio)[0]
+    _, nn = cKDTree(pts.astype(np.float64)).query(pts[keep].astype(np.float64), k=knn)
+    d = pts[nn].astype(np.float64)                                   # (m, knn, 3)
+    d = d - d.mean(1, keepdims=True)
+    C = np.einsum("mki,mkj->mij", d, d) / knn
+    w, v = np.linalg.eigh(C)
+    ok = w[:, 1] > 1e-12 * np.maximum(w[:, 2], 1e-300)               # rank >= 2
+    return keep[ok], v[ok, :, 0].astype(F)
+
+
 def icp(reading_xyz, map_xyz, T_init, map_icp_dist, seed=0, read_prob=0.75, ref_ratio=0.5, knn=7, trim=0.85, max_iter=40,
-        min_rot=1e-3, min_trans=1e-3, smooth=3):
+        min_rot=1e-3, min_trans=1e-3, smooth=3, normals="bins", max_match_dist=None, stats=None):
+    # normals = "bins": the reference's median-split bins; "knn": the device's 7-NN variant. max_match_dist = None: the reference's
+    # unbounded matcher (MatchersImpl.h:83-86); a number: the device's bound (reading points without a reference point within it
+    # are dropped before the trimmed filter). stats: optional dict that receives per-iteration match statistics.
     """PointMatcher<float>::ICP::compute (ICP.cpp:265-449) + the success rule of LidarHelper.cpp:176-184.
     Returns dict(T_LtoM, T_icp, success, iterations, max_iter_reached, n_reading, n_reference)."""
     rng = np.random.default_rng(seed)
     T_init = np.asarray(T_init, F).reshape(4, 4)
     ref = np.ascontiguousarray(map_xyz, F)[:, :3]
     ref = ref[max_dist_filter(ref, map_icp_dist)]
-    kidx, nrm = sampling_surface_normal(ref, rng, ref_ratio, knn)
+    kidx, nrm = (sampling_surface_normal if normals == "bins" else knn_surface_normal)(ref, rng, ref_ratio, knn)
     ref = ref[kidx]
     mean = (ref.sum(0, dtype=F) / F(len(ref))).astype(F)               # ICP.cpp:292-294
     ref_c = ref - mean                                                 # :300
@@ -130,6 +148,13 @@ def icp(reading_xyz, map_xyz, T_init, map_icp_dist, seed=0, read_prob=0.75, ref_
         step = (reading @ T_iter[:3, :3].T + T_iter[:3, 3]).astype(F)                                 # :387
         d, j = tree.query(step.astype(np.float64), k=1)                                              # :391 exact 1-NN
         d2 = (d * d).astype(F)
+        if stats is not None:
+            stats.setdefault("max_match", []).append(float(d.max()))
+            stats.setdefault("beyond_2m", []).append(int((d > 2.0).sum()))
+            stats.setdefault("trim_limit", []).append(float(np.sqrt(np.partition(d2, int(F(len(d2)) * F(trim)))[int(F(len(d2)) * F(trim))])))
+        if max_match_dist is not None:
+            inb = d <= max_match_dist
+            step, j, d2 = step[inb], j[inb], d2[inb]
         q = int(F(len(d2)) * F(trim))                                                                # Matches.cpp:85-86
         limit = np.partition(d2, q)[q] if trim < 1.0 else d2.max()
         w = (d2 <= limit).astype(F)                                                                  # OutlierFiltersImpl.cpp:146
