@@ -88,6 +88,47 @@ def test_g64_every_query_against_the_reference_tree(make_map, po, workload):
     assert n == len(sc) > 120000 and cnt.n_acc > 0.4 * n
 
 
+def test_g64_one_kernel_path_against_the_two_kernel_path(make_map, workload, monkeypatch):
+    """k_scan_tile (one thread per ray, tile.cuh) against k_front_knn + k_rows_reduce (one warp per cell) on the headline scan: same
+    clouds, same neighbours (the rows export re-reads them), same counters; the reduced system equal to rounding (the two add the same
+    rows in different fixed orders) and bit-identical from call to call on either path. The KAIST option set on the same scan
+    (7 levels deep) must take the two-kernel path by itself."""
+    w = workload("G-64")
+    op = w["op"]
+    n_rays, M = w["n_rays"], len(w["map"])
+    res = {}
+    for path, env in (("one", "2"), ("two", "0")):
+        monkeypatch.setenv("MINS_SCAN_TILE", env)
+        m = make_map(max_scan_points=n_rays, max_map_points=M + 2 * n_rays)
+        m.Build(w["map"])
+        l0 = m.lib.ml_launch_count(m.h)
+        rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
+        launches = m.lib.ml_launch_count(m.h) - l0
+        rc2, HtH2, Htr2, cnt2 = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
+        assert rc == 0 and rc2 == 0 and launches == (1 if path == "one" else 2)
+        assert np.array_equal(HtH, HtH2) and np.array_equal(Htr, Htr2) and cnt.as_dict() == cnt2.as_dict()
+        rows, _ = m.point_rows(want_h=False)
+        res[path] = (HtH, Htr, cnt.as_dict(), m.scan(0), m.scan(1), m.scan(2), rows)
+    monkeypatch.delenv("MINS_SCAN_TILE")
+    a, b = res["one"], res["two"]
+    for k in (3, 4, 5):
+        assert np.array_equal(a[k], b[k])
+    assert np.array_equal(a[6]["status"], b[6]["status"]) and np.array_equal(a[6]["plane"], b[6]["plane"])
+    assert np.array_equal(a[6]["chi2"], b[6]["chi2"], equal_nan=True)
+    for key, v in a[2].items():
+        assert v == b[2][key] if isinstance(v, int) else abs(v - b[2][key]) <= 1e-12 * max(1.0, abs(v)), key
+    assert rel(a[0], b[0]) < 1e-12 and rel(a[1], b[1]) < 1e-12
+    # automatic choice: the headline scan takes one launch, the same scan with the KAIST search radius two
+    m = make_map(max_scan_points=n_rays, max_map_points=M + 2 * n_rays)
+    m.Build(w["map"])
+    for max_d, want in ((op.map_ngbr_max_d, 1), (10.0, 2)):
+        c = type(w["consts"]).from_buffer_copy(w["consts"])
+        c.map_ngbr_max_d = max_d
+        l0 = m.lib.ml_launch_count(m.h)
+        rc, _, _, _ = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], c, w["P"])
+        assert rc == 0 and m.lib.ml_launch_count(m.h) - l0 == want
+
+
 def test_g64_mode_b_downsampled_scan(make_map, po, workload):
     """raw_do_downsample: true, leaf 0.3 (mins/config/simulation/config_lidar.yaml:14-15) at the headline size"""
     w = workload("G-64", downsample=True)

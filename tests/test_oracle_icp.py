@@ -38,3 +38,32 @@ def test_oracle_icp_reports_failure_when_capped():
     sc = make_scene(seed=1)
     r = io.icp(sc["reading"], sc["map"], sc["T_init"], 50.0, seed=1, max_iter=2)
     assert r["max_iter_reached"] and not r["success"] and np.array_equal(r["T_LtoM"], sc["T_init"])
+
+
+def test_device_variants_of_the_chain_do_not_degrade_the_alignment():
+    """The device chain (mins_b200/csrc/icp.cuh) deviates from libpointmatcher in two places: normals from the 7 nearest map points
+    instead of median-split bins, and a matcher bounded at 2 m. On UD_Warehouse scenes (scripts/icp_ablation.py, 64 of them in
+    profiles/r2_icp_ablation.md) the bound changes nothing - the trimmed-distance filter cuts far below it - and the 7-NN normals
+    align at least as well as the bins."""
+    import importlib.util
+    import os
+    from conftest import ROOT
+    from oracle import icp_oracle as io
+    spec = importlib.util.spec_from_file_location("icp_ablation", os.path.join(ROOT, "scripts", "icp_ablation.py"))
+    ab = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ab)
+    world = ab.PlaneWorld(ab.load_floorplan(os.path.join(ab.G, "UD_Warehouse_floorplan.txt")))
+    knots = ab.load_bspline_dataset(os.path.join(ab.G, "UD_Warehouse_bspline.txt"))
+    for seed in (0, 4):
+        sc = ab.make_scene(world, knots, seed)
+        e0 = ab.pose_error(sc["T_init"], sc["T_true"])
+        st = {}
+        ref = io.icp(sc["reading"], sc["map"], sc["T_init"], 50.0, seed=seed, stats=st)
+        bound = io.icp(sc["reading"], sc["map"], sc["T_init"], 50.0, seed=seed, max_match_dist=2.0)
+        dev = io.icp(sc["reading"], sc["map"], sc["T_init"], 50.0, seed=seed, normals="knn", max_match_dist=2.0)
+        e_ref, e_bound, e_dev = (ab.pose_error(r["T_icp"], sc["T_true"]) for r in (ref, bound, dev))
+        assert ref["success"] and bound["success"] and dev["success"]
+        assert e_ref[0] < e0[0] and e_dev[0] < e0[0]                      # both improve on the 0.5 deg / 3 cm guess in rotation
+        assert max(st["trim_limit"]) < 1.0 < 2.0                          # the 85 % quantile of the match distances is far below 2 m
+        assert abs(e_bound[0] - e_ref[0]) < 0.08 and abs(e_bound[1] - e_ref[1]) < 0.01
+        assert e_dev[0] < e_ref[0] + 0.1 and e_dev[1] < e_ref[1] + 0.02
