@@ -104,19 +104,13 @@ struct KnnUnit {
   int cx, cy, cz;
 };
 
-// Derived per-scan constants living in device memory (built by k_prep_consts from ml_scan_consts + P).
 // Per-point Jacobian direction g (UpdaterLidar.cpp:320-329), folded: the reference's 18 numbers
 // [n dpfinM_dI (6) | n dpfinM_dA (6) | n dpfinM_dcalib (6)] contain n^T RGtoM twice with opposite signs (position block of I,
 // position block of A), so 15 independent numbers remain:
 //   [ I rotation (3) | n^T RGtoM (3; multiplies dTdxI position rows MINUS dTdxA position rows) | A rotation (3) | calib (6) ]
-// and only the first 9 are non-zero without extrinsic calibration.
+// and only the first 9 are non-zero without extrinsic calibration. The per-scan constants derived from ml_scan_consts + P
+// (T: h = g^T T; Q = T P T^T) are folded on the host: RowConsts (rows.cuh), consts_host (api.cu).
 #define ML_G 15
-struct DevConsts {
-  ml_scan_consts c;
-  double T[ML_G * ML_MAX_HX]; // h = g^T T   (rows: the 15 folded pose-space directions, cols: state columns)
-  double Q[ML_G * ML_G];      // Q = T P T^T  =>  h^T P h = g^T Q g
-  double Qu[ML_G * (ML_G + 1) / 2]; // packed upper triangle of Q by rows, off-diagonal entries doubled
-};
 
 // Per-point result of point_row (k_rows_reduce), consumed by the fixed-order reduction.
 struct PointRow {
@@ -134,13 +128,5 @@ struct PointRow {
 
 #define ML_NPART_MAX 512 // >= CTAs of the kernels that return one reduced system each (k_rows_reduce: one per SM; k_scan_tile: two)
 #define ML_GSYM (ML_G * (ML_G + 1) / 2) // 120
-
-// result block copied back to the host in one D2H
-struct LinsysOut {
-  double HtH[ML_MAX_HX * ML_MAX_HX];
-  double Htr[ML_MAX_HX];
-  ml_counters cnt;
-  ScanState st;
-};
 
 } // namespace ml
