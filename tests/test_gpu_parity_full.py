@@ -129,6 +129,35 @@ def test_g64_one_kernel_path_against_the_two_kernel_path(make_map, workload, mon
         assert rc == 0 and m.lib.ml_launch_count(m.h) - l0 == want
 
 
+def test_one_kernel_path_with_more_tiles_than_ctas(make_map, workload, monkeypatch):
+    """A scan of 262 144 rays is 586 tiles for at most 296 resident CTAs: every CTA of k_scan_tile walks two tiles (second TMA copy
+    into the reused staging area, look-back across rounds, the CTA's running system over both). Checked against the two-kernel path
+    on the same scan: clouds and counters identical, reduced system equal to rounding, repeatable bit for bit."""
+    w = workload("G-64")
+    op = w["op"]
+    raw = np.ascontiguousarray(np.concatenate([w["raw"], w["raw"][::-1]]))
+    n_rays, M = len(raw), len(w["map"])
+    assert n_rays == 262144
+    res = {}
+    for path, env in (("one", "2"), ("two", "0")):
+        monkeypatch.setenv("MINS_SCAN_TILE", env)
+        m = make_map(max_scan_points=n_rays, max_map_points=M + 8)
+        m.Build(w["map"])
+        rc, HtH, Htr, cnt = m.scan_update(raw, w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
+        rc2, HtH2, Htr2, cnt2 = m.scan_update(raw, w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
+        assert rc == 0 and rc2 == 0
+        assert np.array_equal(HtH, HtH2) and np.array_equal(Htr, Htr2) and cnt.as_dict() == cnt2.as_dict()
+        res[path] = (HtH, Htr, cnt.as_dict(), m.scan(0), m.scan(1), m.scan(2))
+    monkeypatch.delenv("MINS_SCAN_TILE")
+    a, b = res["one"], res["two"]
+    assert len(a[3]) > 240000
+    for k in (3, 4, 5):
+        assert np.array_equal(a[k], b[k])
+    for key, v in a[2].items():
+        assert v == b[2][key] if isinstance(v, int) else abs(v - b[2][key]) <= 1e-12 * max(1.0, abs(v)), key
+    assert rel(a[0], b[0]) < 1e-12 and rel(a[1], b[1]) < 1e-12
+
+
 def test_g64_mode_b_downsampled_scan(make_map, po, workload):
     """raw_do_downsample: true, leaf 0.3 (mins/config/simulation/config_lidar.yaml:14-15) at the headline size"""
     w = workload("G-64", downsample=True)
