@@ -9,8 +9,9 @@ configuration the metric's target is quoted on; it fits one GPU.
   value : whole-job points/s with the raw scan already resident in HBM (device-pointer input), device time from CUDA
           events on the handle's own stream (ml_last_timing), L2 flushed between steps.
   e2e   : the same through the C-ABI call with PINNED HOST input and HOST output inside the timed region (wall clock of the
-          blocking call). The bytes cross PCIe inside the call: the front-end kernel reads the pinned scan directly
-          (zero-copy, each point once) and the last CTA of the rows kernel writes the result block to pinned host memory.
+          blocking call). The bytes cross PCIe inside the call: every CTA of the scan kernel reads its tile of the pinned scan
+          directly (TMA bulk copy, each point once) and writes its reduced system into pinned host memory, where the library's
+          host tail adds the parts as they land.
   N > 1 : independent Monte-Carlo replicas, one process per GPU, no data-path collective: weak scaling.
   --impl reference : the reference CPU path on the host cores (reference ikd-Tree compiled unmodified + restated rows).
 """
