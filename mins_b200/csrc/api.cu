@@ -126,7 +126,7 @@ struct ml_handle {
   bool use_tile = true;      // MINS_SCAN_TILE=0: front + kNN kernel followed by the rows kernel (A/B); 2: always (see ml_scan_update)
   bool tile_force = false;
   bool tile_keep_nbr = true; // MINS_TILE_NBR=0: do not leave the neighbours' coordinates in `nbr` (ml_point_rows then fails)
-  bool tile_poll = true;     // MINS_TILE_POLL=0: wait with cudaStreamSynchronize instead of polling the parts' stamps
+  bool tile_poll = true;     // MINS_TILE_POLL=0: cudaStreamSynchronize before the parts are read, instead of watching their words land
   int tile_grid[ML_MAX_K + 1][2][2] = {}; // co-resident CTAs per (k, NB, VEC4), 0 = attribute not set yet
   int parts_armed = 0, parts_armed_nred = 0; // parts [0, parts_armed) hold the sentinel in their first parts_armed_nred doubles and counters
   int parts_n = 0;           // parts of the last reduction (rows_host_tail)
