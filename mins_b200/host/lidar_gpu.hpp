@@ -21,6 +21,7 @@
 #include <cstring>
 #include <deque>
 #include <map>
+#include <algorithm>
 #include <memory>
 #include <vector>
 
@@ -49,12 +50,14 @@ struct ml_api {
   decltype(&ml_scan_icp) scan_icp;
   decltype(&ml_host_alloc) host_alloc;
   decltype(&ml_host_free) host_free;
+  decltype(&ml_map_build) map_build;
+  decltype(&ml_map_add) map_add;
 #ifndef MINS_GPU_NO_LINK
   static ml_api real() {
     return ml_api{&ml_create,      &ml_destroy,         &ml_last_error,  &ml_map_reset,   &ml_map_initialized, &ml_map_build_from_scan,
                   &ml_map_add_scan, &ml_map_reanchor,   &ml_map_flatten, &ml_map_size,    &ml_scan_upload,     &ml_scan_deskew,
                   &ml_scan_downsample, &ml_scan_transform, &ml_scan_update, &ml_info_to_sqrt, &ml_linsys, &ml_icp_default_options,
-                  &ml_scan_icp, &ml_host_alloc, &ml_host_free};
+                  &ml_scan_icp, &ml_host_alloc, &ml_host_free, &ml_map_build, &ml_map_add};
   }
 #endif
 };
@@ -141,12 +144,66 @@ struct LiDARData {
   int size() const { return n; }
 };
 
+// ---- KD_TREE (ikd_Tree.h:92-160) as MINS code OUTSIDE the updater sees it: Initializer.cpp:191-201,330-338 asks
+// `tree->initialized()`, ROSPublisher.cpp:432-470 calls `tree->flatten(tree->Root_Node, pts, NOT_RECORD)`. A facade over one
+// ml_handle with the same member names, so those call sites compile unchanged; the points are PointXYZI's four fields.
+struct PointXYZI {
+  float x, y, z, intensity;
+};
+typedef PointXYZI PointType;
+typedef std::vector<PointType> PointVector;
+enum delete_point_storage_set { NOT_RECORD, DELETE_POINTS_REC, MULTI_THREAD_REC };
+struct KD_TREE_NODE; // opaque: Root_Node is only ever handed back to flatten()
+struct KD_TREE {
+  ml_api api;
+  ml_handle *h = nullptr;
+  float downsample_size = 0.3f;
+  KD_TREE_NODE *Root_Node = nullptr; // non-null while the map is initialised (refreshed by every member below)
+  KD_TREE(const ml_api &a, ml_handle *handle) : api(a), h(handle) {}
+  bool initialized() { return refresh(); }                                  // ikd_Tree.h `initialized()`
+  void reset() {                                                            // KD_TREE::reset
+    api.map_reset(h);
+    refresh();
+  }
+  void set_downsample_param(float ds) { downsample_size = ds; }             // ikd_Tree.cpp:125-127
+  void Build(const PointVector &pts) {                                      // KD_TREE::Build (ikd_Tree.cpp:344-356)
+    api.map_build(h, pts.empty() ? nullptr : &pts[0].x, (int)pts.size());
+    refresh();
+  }
+  int Add_Points(PointVector &pts, bool downsample_on) {                    // KD_TREE::Add_Points (ikd_Tree.cpp:401-479)
+    int n_live = 0;
+    api.map_add(h, pts.empty() ? nullptr : &pts[0].x, (int)pts.size(), downsample_on ? 1 : 0, downsample_size, &n_live);
+    refresh();
+    return n_live;
+  }
+  void flatten(KD_TREE_NODE *, PointVector &Storage, delete_point_storage_set) { // KD_TREE::flatten (ikd_Tree.cpp:1359-1386)
+    int n = 0;
+    api.map_size(h, &n);
+    Storage.resize((size_t)std::max(n, 0));
+    if (n > 0)
+      api.map_flatten(h, &Storage[0].x, n, &n);
+  }
+  int size() {
+    int n = 0;
+    api.map_size(h, &n);
+    return n;
+  }
+  int validnum() { return size(); }
+
+private:
+  bool refresh() {
+    const bool init = h && api.map_initialized(h) > 0;
+    Root_Node = init ? reinterpret_cast<KD_TREE_NODE *>(h) : nullptr;
+    return init;
+  }
+};
+
 // ---- iKDDATA (LidarTypes.h:71-81): one local map = one ml_handle ---------------------------------------------------
 struct iKDDATA {
   int id = -1;
   double time = -1;         // anchor time of the map
   double last_up_time = -1; // last successful registration
-  ml_handle *tree = nullptr;
+  std::shared_ptr<KD_TREE> tree; // tree->h is the handle the updater drives
 };
 
 // statistics the reference keeps in UpdaterStatistics (UpdaterStatistics.cpp:47-83), accumulated from ml_counters

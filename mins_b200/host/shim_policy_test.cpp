@@ -44,13 +44,28 @@ static int m_reanchor(ml_handle *h, const double T[16], double now, double dtime
   std::printf("h%d map_reanchor tx=%.3f now=%.3f decay=%.1f/%.1f ds=%d size=%.2f\n", h->id, T[3], now, dtime, ddist, ds, size);
   return ML_OK;
 }
-static int m_flatten(ml_handle *, float *, int, int *n) {
+static int m_flatten(ml_handle *h, float *out, int cap, int *n) {
+  for (int i = 0; i < cap && i < h->n_map; i++)
+    out[4 * i] = (float)i, out[4 * i + 1] = out[4 * i + 2] = 0.f, out[4 * i + 3] = 0.25f;
   if (n)
-    *n = 0;
+    *n = h->n_map;
   return ML_OK;
 }
-static int m_size(ml_handle *, int *n) {
-  *n = 0;
+static int m_size(ml_handle *h, int *n) {
+  *n = h->n_map;
+  return ML_OK;
+}
+static int m_map_build(ml_handle *h, const float *, int n) {
+  h->init = n > 0;
+  h->n_map = n;
+  std::printf("h%d map_build n=%d\n", h->id, n);
+  return ML_OK;
+}
+static int m_map_add(ml_handle *h, const float *, int n, int ds, float size, int *n_live) {
+  h->n_map += n;
+  if (n_live)
+    *n_live = h->n_map;
+  std::printf("h%d map_add n=%d downsample=%d size=%.2f\n", h->id, n, ds, size);
   return ML_OK;
 }
 static int m_upload(ml_handle *h, const float *, int stride, int n, float t_rel, float rmin, float rmax, int *) {
@@ -221,7 +236,7 @@ struct MockState : StateView {
 int main() {
   ml_api api{m_create, m_destroy, m_err,    m_reset, m_inited, m_build,     m_add_scan, m_reanchor,
              m_flatten, m_size,   m_upload, m_deskew, m_down,  m_transform, m_update,   m_sqrt,
-             m_linsys,  m_icp_defaults, m_icp, m_host_alloc, m_host_free};
+             m_linsys,  m_icp_defaults, m_icp, m_host_alloc, m_host_free, m_map_build, m_map_add};
   OptionsLidar op;
   op.max_n = 1, op.raw_do_downsample = true, op.raw_downsample_size = 0.3, op.map_downsample_size = 0.3, op.min_range = 1.0;
   op.do_calib_ext = true;
@@ -294,5 +309,20 @@ int main() {
   up.try_update();
   state_of();
   std::printf("host_allocs=%d\n", g_host_allocs);
+  std::printf("# KD_TREE facade: the members Initializer.cpp:191-201,330-338 and ROSPublisher.cpp:432-470 use on ikd->tree\n");
+  {
+    auto tree = up.ikd_data[0]->tree;
+    tree->reset();
+    std::printf("initialized=%d root=%d\n", (int)tree->initialized(), tree->Root_Node != nullptr);
+    PointVector cloud(7, PointXYZI{1.f, 2.f, 3.f, 0.5f});
+    tree->set_downsample_param(0.25f);
+    tree->Build(cloud);
+    std::printf("initialized=%d root=%d size=%d validnum=%d\n", (int)tree->initialized(), tree->Root_Node != nullptr, tree->size(), tree->validnum());
+    PointVector more(3, PointXYZI{4.f, 5.f, 6.f, 0.75f});
+    const int live = tree->Add_Points(more, true);
+    PointVector pts_out;
+    tree->flatten(tree->Root_Node, pts_out, NOT_RECORD);
+    std::printf("live=%d flattened=%zu x_last=%.1f intensity=%.2f\n", live, pts_out.size(), pts_out.back().x, pts_out.back().intensity);
+  }
   return 0;
 }

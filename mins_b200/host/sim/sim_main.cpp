@@ -193,7 +193,7 @@ static SimResult run(const SimConfig &cfg) {
   if (upd) {
     res.n_updates = upd->n_updates;
     res.n_acc = upd->Chi[0].n_acp, res.n_meas = upd->Chi[0].n_meas;
-    ml_map_size(upd->ikd_data[0]->tree, &res.map_points);
+    res.map_points = upd->ikd_data[0]->tree->size();
     upd.reset();
     ml_destroy(caster);
   }

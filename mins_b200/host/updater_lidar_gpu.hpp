@@ -18,8 +18,11 @@ public:
       ml_config cfg;
       cfg.device = device, cfg.max_scan_points = max_scan_points, cfg.max_map_points = max_map_points;
       cfg.max_grid_cells = 0, cfg.grid_cell = 0.f;
-      if (api.create(&cfg, &ikd->tree) != ML_OK)
+      ml_handle *h = nullptr;
+      if (api.create(&cfg, &h) != ML_OK)
         die("ml_create", nullptr);
+      ikd->tree = std::make_shared<KD_TREE>(api, h);
+      ikd->tree->set_downsample_param((float)op.map_downsample_size);
       ikd_data.push_back(ikd);
     }
   }
@@ -28,7 +31,7 @@ public:
     for (float *b : pool)
       api.host_free(b);
     for (auto &ikd : ikd_data)
-      api.destroy(ikd->tree);
+      api.destroy(ikd->tree->h);
   }
   UpdaterLidar(const UpdaterLidar &) = delete;
   UpdaterLidar &operator=(const UpdaterLidar &) = delete;
@@ -84,7 +87,7 @@ public:
       }
       auto &ikd = ikd_data.at((*it)->id);
       // map not initialised, or no successful registration for more than 1 s: (re)build it from this scan
-      if (!api.map_initialized(ikd->tree) || ikd->last_up_time + 1 < (*it)->time) {
+      if (!api.map_initialized(ikd->tree->h) || ikd->last_up_time + 1 < (*it)->time) {
         if (!init_map_local(*it, ikd)) { // de-skew poses not available yet: keep it (UpdaterLidar.cpp:82-85)
           ++it;
           continue;
@@ -106,11 +109,11 @@ public:
       FT = stamp;
     auto scan = make_scan(id, stamp, xyz, n, stride);
     auto &ikd = ikd_data.at(id);
-    ck(api.scan_upload(ikd->tree, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
+    ck(api.scan_upload(ikd->tree->h, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
                        nullptr),
-       "ml_scan_upload", ikd->tree);
+       "ml_scan_upload", ikd->tree->h);
     resident[ikd->id] = nullptr;
-    ck(api.map_build_from_scan(ikd->tree), "ml_map_build_from_scan", ikd->tree);
+    ck(api.map_build_from_scan(ikd->tree->h), "ml_map_build_from_scan", ikd->tree->h);
     ikd->time = stamp;
     ikd->last_up_time = stamp;
   }
@@ -134,7 +137,7 @@ public:
   // UpdaterLidar::propagate_map_frame (UpdaterLidar.cpp:147-160)
   void propagate_map_frame() {
     for (auto &ikd : ikd_data) {
-      if (!api.map_initialized(ikd->tree))
+      if (!api.map_initialized(ikd->tree->h))
         continue;
       if ((int)state->n_clones() < state->intr_order() + 1)
         continue;
@@ -175,7 +178,7 @@ private:
   bool init_map_local(const std::shared_ptr<LiDARData> &scan, std::shared_ptr<iKDDATA> &ikd) {
     if (!upload(scan, ikd, /*downsample=*/op.raw_do_downsample))
       return false;
-    ck(api.map_build_from_scan(ikd->tree), "ml_map_build_from_scan", ikd->tree);
+    ck(api.map_build_from_scan(ikd->tree->h), "ml_map_build_from_scan", ikd->tree->h);
     ikd->time = scan->time;
     ikd->last_up_time = scan->time;
     return true;
@@ -187,13 +190,13 @@ private:
     std::vector<float> knots;
     if (op.raw_remove_motion_blur && !deskew_knots(scan, knots))
       return false;
-    ck(api.scan_upload(ikd->tree, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
+    ck(api.scan_upload(ikd->tree->h, scan->xyz, 4, scan->size(), (float)(scan->time - FT), (float)op.min_range, (float)op.max_range,
                        nullptr),
-       "ml_scan_upload", ikd->tree);
+       "ml_scan_upload", ikd->tree->h);
     if (!knots.empty())
-      ck(api.scan_deskew(ikd->tree, knots.data(), (int)(knots.size() / 12), sweep_points(scan)), "ml_scan_deskew", ikd->tree);
+      ck(api.scan_deskew(ikd->tree->h, knots.data(), (int)(knots.size() / 12), sweep_points(scan)), "ml_scan_deskew", ikd->tree->h);
     if (downsample)
-      ck(api.scan_downsample(ikd->tree, (float)op.raw_downsample_size, nullptr), "ml_scan_downsample", ikd->tree);
+      ck(api.scan_downsample(ikd->tree->h, (float)op.raw_downsample_size, nullptr), "ml_scan_downsample", ikd->tree->h);
     resident[ikd->id] = scan.get();
     return true;
   }
@@ -255,8 +258,8 @@ private:
     io.max_dist = op.map_icp_dist;
     io.seed = op.icp_seed++;
     ml_icp_result ir;
-    const int irc = api.scan_icp(ikd->tree, T, &io, &ir);
-    ck(irc, "ml_scan_icp", ikd->tree);
+    const int irc = api.scan_icp(ikd->tree->h, T, &io, &ir);
+    ck(irc, "ml_scan_icp", ikd->tree->h);
     if (irc == ML_OK)
       std::memcpy(T, ir.T_LtoM, sizeof(float) * 16);
     return irc == ML_OK && ir.success;
@@ -293,16 +296,16 @@ private:
         std::memcpy(pd.T_LtoM, T, sizeof(T));
         pd.icp_success = ok;
         if (resident[ikd->id] == scan.get()) // uploaded for the ICP: pointcloud_in_map with the new transform
-          ck(api.scan_transform(ikd->tree, pd.T_LtoM), "ml_scan_transform", ikd->tree);
+          ck(api.scan_transform(ikd->tree->h, pd.T_LtoM), "ml_scan_transform", ikd->tree->h);
       }
     }
     if (pd.icp_success) {
       if (resident[ikd->id] != scan.get()) { // another scan of this LiDAR was processed in between: bring this one back
         if (upload(scan, ikd, false))
-          ck(api.scan_transform(ikd->tree, pd.T_LtoM), "ml_scan_transform", ikd->tree);
+          ck(api.scan_transform(ikd->tree->h, pd.T_LtoM), "ml_scan_transform", ikd->tree->h);
       }
       if (resident[ikd->id] == scan.get()) {
-        ck(api.map_add_scan(ikd->tree, op.map_do_downsample ? 1 : 0, (float)op.map_downsample_size, nullptr), "ml_map_add_scan", ikd->tree);
+        ck(api.map_add_scan(ikd->tree->h, op.map_do_downsample ? 1 : 0, (float)op.map_downsample_size, nullptr), "ml_map_add_scan", ikd->tree->h);
         ikd->last_up_time = scan->time;
       }
     }
@@ -326,9 +329,9 @@ private:
       d[i] = pLoldinG[i] - pLnewinG[i];
     mv3(RGtoLnew, d, p);
     double T[16] = {R[0], R[1], R[2], p[0], R[3], R[4], R[5], p[1], R[6], R[7], R[8], p[2], 0, 0, 0, 1};
-    ck(api.map_reanchor(ikd->tree, T, state->time() - FT, op.map_decay_time, op.map_decay_dist, op.map_do_downsample ? 1 : 0,
+    ck(api.map_reanchor(ikd->tree->h, T, state->time() - FT, op.map_decay_time, op.map_decay_dist, op.map_do_downsample ? 1 : 0,
                         (float)op.map_downsample_size, nullptr),
-       "ml_map_reanchor", ikd->tree);
+       "ml_map_reanchor", ikd->tree->h);
     ikd->time = state->newest_clone_time() - dt; // init_map_local(prop = true) keeps last_up_time
   }
 
@@ -442,7 +445,7 @@ private:
     std::memset(&cnt, 0, sizeof(cnt));
     int rc;
     if (!op.map_use_icp && !op.raw_remove_motion_blur) {
-      rc = api.scan_update(ikd->tree, lidar->xyz, 4, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
+      rc = api.scan_update(ikd->tree->h, lidar->xyz, 4, lidar->size(), (float)(lidar->time - FT), (float)op.min_range,
                            (float)op.max_range, op.raw_do_downsample ? (float)op.raw_downsample_size : 0.f, pend.T_LtoM, &c,
                            P.data(), HtH.data(), Htr.data(), &cnt);
     } else {
@@ -455,10 +458,10 @@ private:
       if (op.map_use_icp)
         pend.icp_success = run_icp(ikd, pend.T_LtoM); // lidar->icp_success
       last_icp_success = pend.icp_success;
-      ck(api.scan_transform(ikd->tree, pend.T_LtoM), "ml_scan_transform", ikd->tree);
-      rc = api.linsys(ikd->tree, &c, P.data(), HtH.data(), Htr.data(), &cnt);
+      ck(api.scan_transform(ikd->tree->h, pend.T_LtoM), "ml_scan_transform", ikd->tree->h);
+      rc = api.linsys(ikd->tree->h, &c, P.data(), HtH.data(), Htr.data(), &cnt);
     }
-    ck(rc, "ml_scan_update", ikd->tree);
+    ck(rc, "ml_scan_update", ikd->tree->h);
     resident[ikd->id] = lidar.get();
     last_counters = cnt;
     chi.add(cnt);

@@ -14,7 +14,7 @@ def run(name, *args):
 
 
 def test_shim_links_against_the_real_abi():
-    assert "ml_api bound: 21 entries" in run("shim_link_check")
+    assert "ml_api bound: 23 entries" in run("shim_link_check")
 
 
 def test_queueing_policy_trace():
@@ -96,3 +96,15 @@ def test_queueing_policy_trace():
     # queued scans live in pooled pinned buffers, PointXYZ layout: few allocations for the ten scans fed, and the device is
     # handed stride-4 points
     assert int(expect("host_allocs=").split("=")[1]) <= 3 and "stride=3" not in out and "stride=4" in out
+
+
+def test_kd_tree_facade_keeps_the_members_other_mins_code_uses():
+    """Initializer.cpp:191-201,330-338 asks `ikd->tree->initialized()`, ROSPublisher.cpp:432-470 calls
+    `ikd->tree->flatten(ikd->tree->Root_Node, pts, NOT_RECORD)`. mins_gpu::KD_TREE (host/lidar_gpu.hpp) offers those members over one
+    ml_handle: traced here against the recording mock of the ABI."""
+    out = run("shim_policy_test")
+    tail = out[out.index("# KD_TREE facade"):]
+    assert "initialized=0 root=0" in tail                                # after reset(): no map, Root_Node null
+    assert "h0 map_build n=7" in tail and "initialized=1 root=1 size=7 validnum=7" in tail
+    assert "h0 map_add n=3 downsample=1 size=0.25" in tail               # Add_Points(pts, true) with set_downsample_param(0.25)
+    assert "live=10 flattened=10 x_last=9.0 intensity=0.25" in tail      # flatten() fills a PointVector of PointXYZI
