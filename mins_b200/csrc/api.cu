@@ -125,7 +125,9 @@ struct ml_handle {
   // the one-kernel path (tile.cuh)
   bool use_tile = true;      // MINS_SCAN_TILE=0: front + kNN kernel followed by the rows kernel (A/B); 2: always (see ml_scan_update)
   bool tile_force = false;
-  bool tile_keep_nbr = true; // MINS_TILE_NBR=0: do not leave the neighbours' coordinates in `nbr` (ml_point_rows then fails)
+  bool tile_keep_nbr = false; // MINS_TILE_NBR=1: k_scan_tile also leaves the neighbours' coordinates in `nbr` (10 MB of stores per
+                              // 131 072-ray scan, 2.6 us); by default ml_point_rows regenerates them with the multi-call search
+  bool rows_need_knn = false; // the resident scan's rows are exportable but `nbr` has to be produced first (ml_point_rows)
   bool tile_poll = true;     // MINS_TILE_POLL=0: cudaStreamSynchronize before the parts are read, instead of watching their words land
   int tile_grid[ML_MAX_K + 1][2][2] = {}; // co-resident CTAs per (k, NB, VEC4), 0 = attribute not set yet
   int parts_armed = 0, parts_armed_nred = 0; // parts [0, parts_armed) hold the sentinel in their first parts_armed_nred doubles and counters
@@ -1445,6 +1447,7 @@ static int rows_and_wait(ml_handle *h, double *HtH, double *Htr, ml_counters *cn
   CK(cudaStreamSynchronize(h->stream));
   CK(cudaGetLastError());
   h->rows_valid = true;
+  h->rows_need_knn = false;
   h->rows_k = k;
   return rows_host_tail(h, HtH, Htr, cnt);
 }
@@ -1704,7 +1707,8 @@ int ml_scan_update(ml_handle *h, const float *xyz, int stride, int n, float t_re
     if (h->timing)
       cudaEventRecord(h->ev[8], h->stream);
     const auto t2 = hp ? now() : t0;
-    h->rows_valid = h->tile_keep_nbr; // ml_point_rows re-runs the export instantiation of the rows kernel on `nbr`
+    h->rows_valid = true; // ml_point_rows re-runs the export instantiation of the rows kernel on `nbr` ...
+    h->rows_need_knn = !h->tile_keep_nbr; // ... after the multi-call search has produced it, if this kernel did not
     h->rows_exported = false;
     h->rows_k = c->map_ngbr_num;
     rc = scan_tile_finish(h, HtH, Htr, cnt);
@@ -1789,6 +1793,13 @@ int ml_point_rows(ml_handle *h, ml_point_row *rows, double *h_rows, int cap, int
   if (!h->rows_valid)
     return fail(h, ML_ERR_ARG, "ml_point_rows: no ml_linsys result for the current scan and map (the export must follow "
                                "ml_linsys / ml_scan_update directly)");
+  if (h->rows_need_knn) {
+    // the one-kernel path kept no neighbour coordinates: the multi-call search on the resident scan and map writes them (the
+    // same neighbours: every walk has one arithmetic and one order), then the export runs as after ml_linsys
+    if (int rc = knn_async(h, h->rows_k, (float)h->consts.map_ngbr_max_d))
+      return rc;
+    h->rows_need_knn = false;
+  }
   const int cnt = h->last_n_scan;
   const int hx = h->consts.total_hx;
   const int m = std::min(cap, cnt);

@@ -22,8 +22,8 @@
 //   3 neighbour coordinates gathered from the map, plane fit, residual, folded Jacobian, chi2 gate (point_row, rows.cuh); the
 //     warp's 32 rows reduced through its shared-memory slab (phase 2 of k_rows_reduce), the CTA's 14 warp partials added in
 //     warp order into the CTA's running system;
-//   4 clouds (pointcloud, pointcloud_original, pointcloud_in_map) and, on request, the neighbours' coordinates in scan order
-//     (what the export instantiation of k_rows_reduce re-reads for ml_point_rows).
+//   4 clouds (pointcloud, pointcloud_original, pointcloud_in_map) and, on request (MINS_TILE_NBR=1), the neighbours' coordinates in
+//     scan order; by default ml_point_rows regenerates them with the multi-call search before it re-runs the rows export.
 // At the end a CTA writes its reduced system into its RRPart in pinned host memory; the host, which armed the parts with a
 // sentinel pattern, adds them in CTA order as their words turn up (rows_host_tail): no stream synchronisation, no flag, no fence.
 #pragma once

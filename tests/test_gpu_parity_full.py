@@ -97,24 +97,30 @@ def test_g64_one_kernel_path_against_the_two_kernel_path(make_map, workload, mon
     op = w["op"]
     n_rays, M = w["n_rays"], len(w["map"])
     res = {}
-    for path, env in (("one", "2"), ("two", "0")):
+    for path, env in (("one", "2"), ("one_lazy", "2"), ("two", "0")):
         monkeypatch.setenv("MINS_SCAN_TILE", env)
+        # "one": k_scan_tile also stores the neighbours it found (MINS_TILE_NBR=1), so the rows export below reads the one-thread-per-
+        # query walk's own neighbours; "one_lazy": the default, the export regenerates them with the multi-call search
+        monkeypatch.setenv("MINS_TILE_NBR", "1" if path == "one" else "0")
         m = make_map(max_scan_points=n_rays, max_map_points=M + 2 * n_rays)
         m.Build(w["map"])
         l0 = m.lib.ml_launch_count(m.h)
         rc, HtH, Htr, cnt = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
         launches = m.lib.ml_launch_count(m.h) - l0
         rc2, HtH2, Htr2, cnt2 = m.scan_update(w["raw"], w["t_rel"], op, w["T_LtoM"], w["consts"], w["P"])
-        assert rc == 0 and rc2 == 0 and launches == (1 if path == "one" else 2)
+        assert rc == 0 and rc2 == 0 and launches == (2 if path == "two" else 1)
         assert np.array_equal(HtH, HtH2) and np.array_equal(Htr, Htr2) and cnt.as_dict() == cnt2.as_dict()
         rows, _ = m.point_rows(want_h=False)
         res[path] = (HtH, Htr, cnt.as_dict(), m.scan(0), m.scan(1), m.scan(2), rows)
     monkeypatch.delenv("MINS_SCAN_TILE")
-    a, b = res["one"], res["two"]
+    monkeypatch.delenv("MINS_TILE_NBR")
+    a, b, lazy = res["one"], res["two"], res["one_lazy"]
+    assert np.array_equal(a[0], lazy[0]) and np.array_equal(a[1], lazy[1]) and a[2] == lazy[2]   # storing the neighbours changes nothing
     for k in (3, 4, 5):
-        assert np.array_equal(a[k], b[k])
-    assert np.array_equal(a[6]["status"], b[6]["status"]) and np.array_equal(a[6]["plane"], b[6]["plane"])
-    assert np.array_equal(a[6]["chi2"], b[6]["chi2"], equal_nan=True)
+        assert np.array_equal(a[k], b[k]) and np.array_equal(lazy[k], b[k])
+    for r in (a[6], lazy[6]):
+        assert np.array_equal(r["status"], b[6]["status"]) and np.array_equal(r["plane"], b[6]["plane"])
+        assert np.array_equal(r["chi2"], b[6]["chi2"], equal_nan=True)
     for key, v in a[2].items():
         assert v == b[2][key] if isinstance(v, int) else abs(v - b[2][key]) <= 1e-12 * max(1.0, abs(v)), key
     assert rel(a[0], b[0]) < 1e-12 and rel(a[1], b[1]) < 1e-12
