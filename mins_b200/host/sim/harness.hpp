@@ -151,7 +151,7 @@ struct SimConfig {
   double h_resolution = 2.0;
   double init_ori_err = 0.01, init_pos_err = 0.02;
   bool use_lidar = true, use_gt_lidar = true, no_noise = false;
-  std::string bspline_path, floorplan_path, traj_out;
+  std::string bspline_path, floorplan_path, traj_out, state_log_out;
   mins_gpu::OptionsLidar op;
   int device = 0;
 };
@@ -162,11 +162,12 @@ struct SimResult {
   long n_acc = 0, n_meas = 0;
   double wall_s = 0, ldr_wall_s = 0, raycast_wall_s = 0;
   int map_points = 0;
-  std::vector<std::vector<double>> traj; // [t, p, q_jpl]
+  std::vector<std::vector<double>> traj; // [t, p, q_jpl, 12 covariance entries]
 };
 
 struct PoseSample {
   double t, R[9], p[3];
+  double cov[12] = {0}; // upper triangles of the orientation and the position block of the IMU pose covariance (State_Logger.h:333-339)
 };
 
 // ov_eval AlignTrajectory se3 + ResultTrajectory::calculate_ate (ResultTrajectory.cpp:70-97)

@@ -1,6 +1,6 @@
 // mins_sim_run: one closed-loop IMU + LiDAR simulation run in host C++ (see harness.hpp). Prints one JSON line.
 //   mins_sim_run --bspline F --floorplan F [--seed S | --seeds S0,S1,...] [--duration T] [--icp 0|1] [--no-lidar] [--no-noise] [--no-gt-map]
-//                [--device D] [--traj out.txt] [--deskew 0|1]
+//                [--device D] [--traj out.txt] [--state-log out.txt] [--deskew 0|1]
 // Without --no-lidar a CUDA device is required (the LiDAR updater has no CPU path); --no-lidar runs the IMU + clone-window core
 // alone (the CPU tests use it to pin this file against the Python harness it replaces).
 #include "harness.hpp"
@@ -152,6 +152,13 @@ static SimResult run(const SimConfig &cfg) {
       e.t = g.t = t;
       std::memcpy(e.R, st.R, sizeof(e.R)), std::memcpy(e.p, st.p, sizeof(e.p));
       spline.get_pose(t, g.R, g.p);
+      {
+        int q = 0;
+        for (int blk = 0; blk < 2; blk++) // orientation block, then position block: entries 00 01 02 11 12 22
+          for (int a = 0; a < 3; a++)
+            for (int b = a; b < 3; b++)
+              e.cov[q++] = st.P(3 * blk + a, 3 * blk + b);
+      }
       est.push_back(e), gt.push_back(g);
       double Pp[9], Pi[9], d[3], Pd[3];
       for (int a = 0; a < 3; a++)
@@ -188,7 +195,9 @@ static SimResult run(const SimConfig &cfg) {
   for (auto &e : est) {
     double q[4];
     rot_to_quat_jpl(e.R, q);
-    res.traj.push_back({e.t, e.p[0], e.p[1], e.p[2], q[0], q[1], q[2], q[3]});
+    std::vector<double> row = {e.t, e.p[0], e.p[1], e.p[2], q[0], q[1], q[2], q[3]};
+    row.insert(row.end(), e.cov, e.cov + 12);
+    res.traj.push_back(row);
   }
   if (upd) {
     res.n_updates = upd->n_updates;
@@ -243,6 +252,8 @@ int main(int argc, char **argv) {
       cfg.device = atoi(next());
     else if (a == "--traj")
       cfg.traj_out = next();
+    else if (a == "--state-log") // the estimate in State_Logger::save_trajectory_to_file's format (what mins_eval reads)
+      cfg.state_log_out = next();
     else if (a == "--no-lidar")
       cfg.use_lidar = false;
     else if (a == "--no-noise")
@@ -269,6 +280,18 @@ int main(int argc, char **argv) {
       FILE *f = std::fopen(cfg.traj_out.c_str(), "w");
       for (auto &row : r.traj)
         std::fprintf(f, "%.9f %.12g %.12g %.12g %.12g %.12g %.12g %.12g\n", row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]);
+      std::fclose(f);
+    }
+    if (!cfg.state_log_out.empty()) {
+      // mins/src/utils/State_Logger.h:323-340: time px py pz qx qy qz qw (6 significant digits), then the upper triangles of the
+      // orientation and the position covariance blocks (10 significant digits): the file mins_eval's run_comparison loads
+      FILE *f = std::fopen(cfg.state_log_out.c_str(), "w");
+      for (auto &row : r.traj) {
+        for (int c = 0; c < 8; c++)
+          std::fprintf(f, "%.6g ", row[c]);
+        for (int c = 8; c < 20; c++)
+          std::fprintf(f, c < 19 ? "%.10g " : "%.10g\n", row[c]);
+      }
       std::fclose(f);
     }
     std::printf("{\"seed\": %llu, \"icp\": %d, \"rmse_ori_deg\": %.9g, \"rmse_pos_m\": %.9g, \"nees_pos\": %.6g, \"final_pos_err\": %.6g, "

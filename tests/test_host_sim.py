@@ -52,6 +52,22 @@ def test_cpp_core_matches_the_python_harness_imu_only(tmp_path):
     assert r["nees_pos"] == pytest.approx(py["nees_pos"], rel=1e-6)     # same covariance propagation and cloning
 
 
+def test_cpp_harness_writes_the_state_logger_trajectory_format(tmp_path):
+    """`--state-log`: one line per clone in the format of State_Logger::save_trajectory_to_file (mins/src/utils/State_Logger.h:323-340),
+    which mins_eval's trajectory tools load: time, position, JPL quaternion (6 significant digits), the upper triangles of the
+    orientation and the position blocks of the IMU pose covariance (10 significant digits) - 20 columns."""
+    traj, log = str(tmp_path / "traj.txt"), str(tmp_path / "state.txt")
+    run_cpp("--no-lidar", "--duration", 3, "--seed", 2, "--state-log", log, traj=traj)
+    t, s = np.loadtxt(traj), np.loadtxt(log)
+    assert s.shape == (len(t), 20) and len(t) == 60
+    assert np.abs(s[:, :8] - t).max() < 5e-6 * np.abs(t).max()                      # the same poses at the reference's precision
+    ori, pos = s[:, 8:14], s[:, 14:20]
+    for blk in (ori, pos):                                                          # [00 01 02 11 12 22] of a covariance block
+        C = np.stack([blk[:, [0, 1, 2]], blk[:, [1, 3, 4]], blk[:, [2, 4, 5]]], 1)
+        assert (np.linalg.eigvalsh(C) > 0).all()
+    assert pos[-1, 0] > pos[0, 0] and pos[-1, 5] > pos[0, 5]                        # IMU only: the position uncertainty grows
+
+
 def test_cpp_harness_needs_a_device_for_lidar():
     """no CPU fallback: without a CUDA device the LiDAR run fails loudly"""
     import torch
