@@ -11,7 +11,9 @@ from . import pyoracle as po
 
 
 class OracleBackend:
-    def __init__(self, threads=8):
+    def __init__(self, threads=8, icp_normals="bins", icp_max_match_dist=None):
+        # icp_*: variants of the restated libpointmatcher chain (icp_oracle.icp): the defaults are the reference's
+        self.icp_normals, self.icp_max_match_dist = icp_normals, icp_max_match_dist
         self.map = np.zeros((0, 4), np.float32)
         self.init = False
         self.threads = threads
@@ -52,7 +54,8 @@ class OracleBackend:
 
     def _icp(self, scan, sc, op, T_init):
         from . import icp_oracle
-        r = icp_oracle.icp(sc[:, :3], self.map, T_init, op.map_icp_dist, seed=scan["key"] + 1000003 * scan.get("icp_tries", 0))
+        r = icp_oracle.icp(sc[:, :3], self.map, T_init, op.map_icp_dist, seed=scan["key"] + 1000003 * scan.get("icp_tries", 0),
+                           normals=self.icp_normals, max_match_dist=self.icp_max_match_dist)
         scan["icp_tries"] = scan.get("icp_tries", 0) + 1
         self.icp_runs += 1
         self.icp_ok += int(r["success"])
