@@ -1269,9 +1269,10 @@ static void build_T(const ml_scan_consts &c, double *T) {
       T[r * ML_MAX_HX + c.calib_col + (r - 9)] += 1.0;
 }
 
-// Per-scan constants, all on the host (~20 k multiply-adds; they are computed while the device runs the front end and the
-// kNN, so they cost the scan nothing): the folded rows-kernel parameter incl. Q = T P T^T (h^T P h = g^T Q g), and T for the
-// host tail. There is no constants kernel, no side stream and no event between the kNN and the rows kernel.
+// Per-scan constants, all on the host (~20 k multiply-adds, ~7 us): the folded rows parameter incl. Q = T P T^T (h^T P h = g^T Q g),
+// and T for the host tail. On the two-kernel path they are computed while the device runs the front end and the kNN, so they cost
+// the scan nothing; on the one-kernel path they are a parameter of the only kernel and precede its launch. There is no constants
+// kernel, no side stream and no event anywhere.
 static int consts_host(ml_handle *h, const ml_scan_consts *c, const double *P) {
   const int hx = c->total_hx;
   h->consts = *c;
