@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--duration", type=float, default=50.0)
     ap.add_argument("--icp", type=int, default=0)
     ap.add_argument("--seed0", type=int, default=0)
+    ap.add_argument("--no-lidar", action="store_true", help="IMU-only runs (no device needed): exercises the launcher on a CPU box")
     args = ap.parse_args()
     # One WORKER process per (gpu, slot): it creates its CUDA context once and runs its share of the seeds one after the other
     # (seed s goes to worker s mod workers). A process per run was measured on an 8-GPU box: context creation is serialised
@@ -42,6 +43,8 @@ def main():
         mine = seeds[w::len(slots)]
         cmd = [BIN, "--bspline", os.path.join(G, "UD_Warehouse_bspline.txt"), "--floorplan", os.path.join(G, "UD_Warehouse_floorplan.txt"),
                "--seeds", ",".join(map(str, mine)), "--duration", str(args.duration), "--icp", str(args.icp), "--device", "0"]
+        if args.no_lidar:
+            cmd.append("--no-lidar")
         # one visible device per process (a process that sees every GPU of an 8-GPU box spends seconds in cuInit)
         env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(slot[0]))
         procs.append((slot, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env)))

@@ -68,6 +68,22 @@ def test_cpp_harness_writes_the_state_logger_trajectory_format(tmp_path):
     assert pos[-1, 0] > pos[0, 0] and pos[-1, 5] > pos[0, 5]                        # IMU only: the position uncertainty grows
 
 
+def test_monte_carlo_launcher_shards_seeds_over_persistent_workers():
+    """scripts/mc_sim_cpp.py (BASELINE config "64 independent runs sharded over 1/2/4/8 B200"): one worker process per (GPU, slot),
+    seed s on worker s mod workers, every worker runs its seeds in one process. IMU-only here (no device): 7 runs over 2 x 2 workers."""
+    import sys
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "mc_sim_cpp.py"), "--gpus", "2", "--per-gpu", "2", "--runs", "7",
+                        "--duration", "1", "--seed0", "10", "--no-lidar"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    summary = json.loads(p.stdout.strip().splitlines()[-1])
+    runs = [json.loads(line) for line in p.stderr.splitlines() if line.startswith("{")]
+    assert summary["runs"] == 7 and summary["gpus"] == 2 and summary["per_gpu"] == 2
+    assert sorted(r["seed"] for r in runs) == list(range(10, 17))                    # every seed exactly once
+    by_gpu = {g: sorted(r["seed"] for r in runs if r["gpu"] == g) for g in (0, 1)}
+    assert by_gpu[0] == [10, 12, 14, 16] and by_gpu[1] == [11, 13, 15]                # workers 0..3 = (gpu0,s0) (gpu1,s0) (gpu0,s1) (gpu1,s1)
+    assert all(r["n_scans"] == 0 and r["n_clones"] == 20 for r in runs)
+
+
 def test_cpp_harness_needs_a_device_for_lidar():
     """no CPU fallback: without a CUDA device the LiDAR run fails loudly"""
     import torch
