@@ -46,7 +46,9 @@ def main():
         if args.no_lidar:
             cmd.append("--no-lidar")
         # one visible device per process (a process that sees every GPU of an 8-GPU box spends seconds in cuInit)
-        env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(slot[0]))
+        # (GPU g of this job = the g-th device the parent may see, if the parent is restricted itself)
+        parent = [d for d in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if d]
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=parent[slot[0] % len(parent)] if parent else str(slot[0]))
         procs.append((slot, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env)))
     results = []
     for slot, p in procs:
